@@ -1,0 +1,125 @@
+/*
+ * nldsc_ld.h -- C ABI of the B200-native LD-score engine (libnldsc_ld.so).
+ *
+ * Drop-in boundary for the reference's `_ldscore.calculate`
+ * (reference: nldsc/ldscore/_ldscore/ldscore.cpp:53 -> ldscalc.h:8-65, called from
+ * nldsc/ldscore/routine.py:77-89).  Plain pointers and sizes only; no torch, no
+ * C++ types.  Every entry point returns 0 on success, NLDSC_ERR_INVALID for what
+ * the reference raises as std::invalid_argument (-> Python ValueError; e.g. the
+ * PLINK magic check, stream.h:88-102) and NLDSC_ERR_RUNTIME for everything the
+ * reference would surface as std::runtime_error (-> RuntimeError): CUDA failures,
+ * I/O errors, a missing GPU.  There is NO CPU fallback: without a usable sm_100
+ * device the calls fail with NLDSC_ERR_RUNTIME and a message.
+ *
+ * Result conventions are the reference's (data.h:21-31, ldscalc.h:13-21,49-54,
+ * stream.h:165-179): seven arrays of length n_snp aligned with the .bim; SNPs
+ * dropped by the MAF filter keep l2 = l2d = NaN, l2_ws = l2d_ws = l2d_wse = -1,
+ * residuals_std = NaN and carry their computed maf.
+ */
+#ifndef NLDSC_LD_H
+#define NLDSC_LD_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NLDSC_OK 0
+#define NLDSC_ERR_INVALID 1 /* std::invalid_argument in the reference -> ValueError */
+#define NLDSC_ERR_RUNTIME 2 /* std::runtime_error -> RuntimeError */
+
+/* Mirrors LDScoreParams (reference data.h:33-66); same field meaning and order. */
+typedef struct nldsc_ld_params {
+    const char* bedfile;     /* absolute path of the .bed (UTF-8); ignored by *_packed / session calls */
+    int32_t n_snp;           /* number of SNPs (rows of the .bim) */
+    int32_t n_org;           /* number of organisms (rows of the .fam) */
+    double ld_wind;          /* window half-width, in the unit of `positions` (cM or bp) */
+    const double* positions; /* n_snp coordinates; must be >= 0 and non-decreasing */
+    double maf;              /* drop SNP iff (double)maf_float <= maf        (encoder.h:120) */
+    double std_thr;          /* dominance usable iff residual std > std_thr  (tools.h:31-33) */
+    double rsq_thr;          /* WSDE counts r2adj_dom > rsq_thr, strict      (tools.h:36-38) */
+} nldsc_ld_params;
+
+/* Mirrors LDScoreResult (reference data.h:21-31).  Caller-allocated arrays. */
+typedef struct nldsc_ld_result {
+    double* l2;            /* additive LD score                 (ldscalc.h:49) */
+    double* l2d;           /* dominance LD score                (ldscalc.h:50) */
+    double* maf;           /* float MAF widened to double       (stream.h:165-171) */
+    double* residuals_std; /* std of the dominance residual     (stream.h:173-179) */
+    int32_t* l2_ws;        /* WSA  (ldscalc.h:52) */
+    int32_t* l2d_ws;       /* WSD  (ldscalc.h:53) */
+    int32_t* l2d_wse;      /* WSDE (ldscalc.h:54) */
+} nldsc_ld_result;
+
+/* Replaces calculate(LDScoreParams&) (ldscalc.h:8): opens and validates the .bed
+ * (magic 6c 1b 01 and, unlike the reference, the exact size 3 + n_snp*ceil(n_org/4)),
+ * streams it to the GPU(s) and fills `out` (arrays of length n_snp).
+ * GPUs: environment NLDSC_GPUS (default 1) contiguous SNP shards with a window
+ * halo, one host thread per GPU, no collective; results gathered host-side. */
+int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char* err, size_t errlen);
+
+/* Same computation from a host buffer holding the genotype bytes of the .bed
+ * WITHOUT its 3-byte magic: n_snp rows of ceil(n_org/4) bytes (what
+ * BedStreamReader::read consumes, stream.h:43-69). */
+int nldsc_ld_calculate_packed(const uint8_t* packed, const nldsc_ld_params* params,
+                              nldsc_ld_result* out, char* err, size_t errlen);
+
+/* ---- session API: one shard on one GPU, device-resident between calls ------------- */
+typedef struct nldsc_ld_session nldsc_ld_session;
+
+typedef struct nldsc_ld_stats {
+    int64_t pairs;            /* sum of WSA over owned rows = ordered window SNP pairs scored */
+    int64_t tiles;            /* 64x64 SNP-pair tiles issued to the band kernel */
+    int32_t chunks;           /* plane-ring refills */
+    int32_t kernel_launches;  /* kernels launched by the last run() */
+    int32_t load_begin;       /* first SNP row the shard needs (owned range minus halo, 64-aligned) */
+    int32_t load_end;         /* one past the last SNP row needed */
+    int32_t npad;             /* padded organisms per plane row (bytes) */
+    int32_t band_impl;        /* 1 = tcgen05 kernel, 0 = SIMT yardstick (NLDSC_BAND=simt) */
+    float ms_count;           /* CUDA-event times of the last run(), per kernel family */
+    float ms_stats;
+    float ms_unpack;
+    float ms_band;
+    float ms_finalize;
+    float ms_total;
+} nldsc_ld_stats;
+
+/* Shard = SNP rows [row_begin,row_end) of the bfile described by `params`
+ * (bedfile ignored).  Plans windows, tiles and the halo from `positions`. */
+int nldsc_ld_session_create(nldsc_ld_session** out, int device, const nldsc_ld_params* params,
+                            int32_t row_begin, int32_t row_end, char* err, size_t errlen);
+/* Host -> device copy of packed rows [load_begin,load_end) (see stats), asynchronous
+ * on `stream` (a cudaStream_t, or NULL for the session's own stream). */
+int nldsc_ld_session_upload(nldsc_ld_session* s, const uint8_t* packed_rows, void* stream,
+                            char* err, size_t errlen);
+/* Count -> per-SNP stats -> unpack -> banded int8 GEMM + FP64 epilogue -> finalize,
+ * all asynchronous on `stream`.  Inputs must be resident (upload done). */
+int nldsc_ld_session_run(nldsc_ld_session* s, void* stream, char* err, size_t errlen);
+/* Device -> host copy of the owned rows' seven arrays (length row_end-row_begin),
+ * then synchronises `stream`. */
+int nldsc_ld_session_download(nldsc_ld_session* s, nldsc_ld_result* out, void* stream,
+                              char* err, size_t errlen);
+int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* out);
+void nldsc_ld_session_destroy(nldsc_ld_session* s);
+
+/* ---- parity hooks (used by tests/ only; they run the same kernels as the session) -- */
+/* Unpack + count `n_snp` packed rows: planes_out = int8 [4][n_snp][npad] in plane order
+ * g,m,h,a (npad returned), counts_out = int32 [n_snp][3] = n_het, n_hom2, n_missing. */
+int nldsc_ld_debug_unpack(const uint8_t* packed, int32_t n_snp, int32_t n_org, int8_t* planes_out,
+                          int32_t* counts_out, int32_t* npad_out, char* err, size_t errlen);
+/* Raw band-kernel accumulators for SNP block pair (i_block, j_block) (64 SNPs each):
+ * acc_out = int32 [128][192]; row 32*(s/16) + 16*p + s%16 is SNP s of the i block,
+ * left plane p (0 = g, 1 = m); column 64*q + t is SNP t of the j block, right plane q
+ * (0 = m, 1 = h, 2 = a). */
+int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_org,
+                                int32_t i_block, int32_t j_block, int32_t* acc_out,
+                                char* err, size_t errlen);
+/* Number of usable CUDA devices (0 and an error message when none). */
+int nldsc_ld_device_count(int32_t* count, char* err, size_t errlen);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NLDSC_LD_H */

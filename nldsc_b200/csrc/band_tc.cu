@@ -1,0 +1,335 @@
+// Banded int8 cross-count GEMM on the 5th-gen tensor cores + fused FP64 epilogue.
+//
+// Replaces the pair loop of calculate() (reference ldscalc.h:34-47) and the two
+// arma::dot calls per ordered pair in Math::r2_adjusted (tools.h:87-92).
+//
+// One CTA per SM, persistent over a host-built list of 64x64 SNP-pair tiles that covers
+// only the band |pos_j - pos_i| <= window.  Per tile, a full-K (= organisms) int8 GEMM
+//     D[128 x 192] (int32, TMEM) = A[128 x K] * B[192 x K]^T
+//   A rows: per group of 16 i-SNPs, 16 rows of g (dosage 0/1/2) then 16 rows of m (missing)
+//   B rows: 64 rows of m_j, 64 of h_j (het), 64 of a_j (hom-second)
+// gives the six exact cross-counts of every pair.  Warp roles:
+//   warp 0   TMA producer  (cp.async.bulk.tensor, 128B-swizzled K-major tiles, 5-stage ring)
+//   warp 1   MMA issuer    (tcgen05.mma.kind::i8, M=128 N=192 K=32; 2 TMEM accumulators)
+//   warps 2-5 epilogue     (tcgen05.ld -> FP64 correlations -> r2adj -> row sums)
+// The accumulators are double-buffered in TMEM so the FP64 epilogue of tile t overlaps
+// the MMAs of tile t+1.
+#include "common.cuh"
+#include "epilogue.cuh"
+
+#include <cuda.h>
+
+namespace nldsc {
+
+namespace {
+
+constexpr int kStages = 5;
+constexpr int kKStep = 128;                 // organisms (bytes) per pipeline stage
+constexpr int kARows = 128, kBRows = 192;
+constexpr int kABytes = kARows * kKStep;    // 16 KB
+constexpr int kBBytes = kBRows * kKStep;    // 24 KB
+constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kTmemCols = 512;              // 2 accumulators of 192 columns at 0 and 256
+constexpr int kThreads = 192;
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+
+// ---- PTX wrappers -------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done = 0;
+    // bounded spin: a protocol bug must trap, not hang the GPU box
+    for (uint32_t spins = 0; !done; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+        if (spins > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar,
+                                            int32_t c0, int32_t c1, int32_t c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)),
+          "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T, int8 x int8 -> int32
+__device__ __forceinline__ void tc_mma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// K-major, 128-byte swizzle: rows at a 128 B pitch, 8-row atoms 1024 B apart.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);   // start address
+    d |= static_cast<uint64_t>(1024u >> 4) << 32;              // stride byte offset (8 rows)
+    d |= 1ull << 46;                                           // descriptor version (sm_100)
+    d |= 2ull << 61;                                           // SWIZZLE_128B
+    return d;
+}
+// instruction descriptor, kind::i8: D = s32, A/B = u8, both K-major, M = 128, N = 192
+constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (0u << 10) | ((kBRows >> 3) << 17) | ((kARows >> 4) << 24);
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, int32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+}  // namespace
+
+__global__ void __launch_bounds__(kThreads, 1)
+band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+               const BandArgs args) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
+    uint64_t* empty = full + kStages;
+    uint64_t* tfull = empty + kStages;
+    uint64_t* tempty = tfull + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < args.n_tiles; t += gridDim.x) {
+                const Tile tl = args.tiles[t];
+                for (int k = 0; k < args.k_steps; ++k) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    mbar_expect_tx(&full[stage], kStageBytes);
+                    uint8_t* sa = smem + stage * kStageBytes;
+                    uint8_t* sb = sa + kABytes;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)   // 16 SNPs x {g, m} = 32 rows per box
+                        tma_load_3d(sa + u * 4096, &map_a, &full[stage], k * kKStep, tl.a_row + 16 * u, kPlaneG);
+                    tma_load_3d(sb, &map_b, &full[stage], k * kKStep, tl.b_row, kPlaneM);   // 64 SNPs x {m, h, a}
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int n = 0;
+            for (int t = blockIdx.x; t < args.n_tiles; t += gridDim.x, ++n) {
+                const int buf = n & 1;
+                mbar_wait(&tempty[buf], ((n >> 1) & 1) ^ 1);       // epilogue drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * 256;
+                for (int k = 0; k < args.k_steps; ++k) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+                    const uint64_t a_desc = make_smem_desc(sa);
+                    const uint64_t b_desc = make_smem_desc(sa + kABytes);
+#pragma unroll
+                    for (int kk = 0; kk < kKStep / 32; ++kk)       // +32 B along K inside the swizzle atom
+                        tc_mma_i8(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (k | kk) != 0);
+                    tc_commit(&empty[stage]);                       // smem slot free once these MMAs retire
+                    if (++stage == kStages) { stage = 0; phase ^= 1; }
+                }
+                tc_commit(&tfull[buf]);                             // accumulator complete
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue: 4 warps, warp q owns TMEM lanes 32q..32q+31 =====
+        const int q = warp & 3;
+        const bool is_g = lane < 16;                 // lanes 0-15 hold g rows, 16-31 the m rows of the same SNPs
+        const int s = 16 * q + (lane & 15);          // SNP within the i-block
+        int n = 0;
+        for (int t = blockIdx.x; t < args.n_tiles; t += gridDim.x, ++n) {
+            const int buf = n & 1;
+            const Tile tl = args.tiles[t];
+            const RowCtx row = load_row_ctx(args, tl.i0 + s);
+            RowAcc acc;
+            mbar_wait(&tfull[buf], (n >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(32 * q) << 16);
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {            // 16 j-SNPs per pass
+                int32_t vm[16], vh[16], va[16];
+                tmem_ld16(taddr + 16 * c, vm);
+                tmem_ld16(taddr + 64 + 16 * c, vh);
+                tmem_ld16(taddr + 128 + 16 * c, va);
+                tmem_ld_wait();
+                if (args.dump != nullptr) {
+                    int32_t* drow = args.dump + (static_cast<int64_t>(t) * kARows + 32 * q + lane) * kBRows;
+#pragma unroll
+                    for (int e = 0; e < 16; ++e) {
+                        drow[16 * c + e] = vm[e];
+                        drow[64 + 16 * c + e] = vh[e];
+                        drow[128 + 16 * c + e] = va[e];
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    // g-lane scores even j, its partner m-lane scores odd j; swap what the other needs
+                    const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
+                    const int32_t sh_ = is_g ? vh[2 * u + 1] : vh[2 * u];
+                    const int32_t sa_ = is_g ? va[2 * u + 1] : va[2 * u];
+                    const int32_t rm = __shfl_xor_sync(0xFFFFFFFFu, sm_, 16);
+                    const int32_t rh = __shfl_xor_sync(0xFFFFFFFFu, sh_, 16);
+                    const int32_t ra = __shfl_xor_sync(0xFFFFFFFFu, sa_, 16);
+                    const int jl = 16 * c + 2 * u + (is_g ? 0 : 1);
+                    const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
+                    const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
+                    const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
+                    pair_eval(args, row, tl.j0 + jl, Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
+                }
+            }
+            // accumulator fully read: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[buf]);
+            // even-j and odd-j halves of the row
+            acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
+            acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);
+            acc.wsa += __shfl_xor_sync(0xFFFFFFFFu, acc.wsa, 16);
+            acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
+            acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
+            if (is_g) {
+                const int64_t o = static_cast<int64_t>(t) * kBlk + s;
+                args.part.add[o] = acc.add;
+                args.part.dom[o] = acc.dom;
+                args.part.wsa[o] = acc.wsa;
+                args.part.wsd[o] = acc.wsd;
+                args.part.wsde[o] = acc.wsde;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                     : "memory");
+    }
+}
+
+// ---- host side: TMA descriptors + launch ------------------------------------------------
+struct BandMaps {
+    CUtensorMap a;   // box {128 B, 16 rows, 2 planes}
+    CUtensorMap b;   // box {128 B, 64 rows, 3 planes}
+};
+
+namespace {
+using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                              const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                              CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeFn get_encode() {
+    static EncodeFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+        if (qres != cudaDriverEntryPointSuccess || !p) throw CudaError("cuTensorMapEncodeTiled not available in this driver");
+        fn = reinterpret_cast<EncodeFn>(p);
+    }
+    return fn;
+}
+
+void encode(CUtensorMap* m, const int8_t* planes, int64_t plane_rows, int32_t npad, uint32_t box_rows,
+            uint32_t box_planes) {
+    const cuuint64_t dims[3] = {(cuuint64_t)npad, (cuuint64_t)plane_rows, (cuuint64_t)kPlanes};
+    const cuuint64_t strides[2] = {(cuuint64_t)npad, (cuuint64_t)npad * (cuuint64_t)plane_rows};
+    const cuuint32_t box[3] = {(cuuint32_t)kKStep, box_rows, box_planes};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, const_cast<int8_t*>(planes), dims, strides,
+                                    box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[160];
+        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled failed (CUresult %d; rows %lld npad %d)", (int)r,
+                 (long long)plane_rows, npad);
+        throw CudaError(buf);
+    }
+}
+}  // namespace
+
+BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npad) {
+    BandMaps* m = new BandMaps;
+    try {
+        encode(&m->a, planes, plane_rows, npad, 16, 2);
+        encode(&m->b, planes, plane_rows, npad, 64, 3);
+    } catch (...) {
+        delete m;
+        throw;
+    }
+    return m;
+}
+void band_maps_destroy(BandMaps* m) { delete m; }
+
+void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
+    if (args.n_tiles <= 0) return;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+        attr_set = true;
+    }
+    const int grid = args.n_tiles < sm_count ? args.n_tiles : sm_count;
+    band_tc_kernel<<<grid, kThreads, kSmemBytes, st>>>(maps->a, maps->b, args);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace nldsc

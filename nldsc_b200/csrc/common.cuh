@@ -1,0 +1,120 @@
+// Shared definitions for the LD-score CUDA path (sm_100a only).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <stdexcept>
+#include <string>
+
+namespace nldsc {
+
+// ---- geometry -------------------------------------------------------------------
+// SNP blocks are 64 wide and aligned on ORIGINAL .bim indices (multiples of 64), so the
+// FP64 summation order of every row is independent of where shard boundaries fall.
+constexpr int kBlk = 64;           // SNPs per i-block and per j-block
+constexpr int kPlanes = 4;         // plane order in HBM: g, m, h, a
+constexpr int kPlaneG = 0, kPlaneM = 1, kPlaneH = 2, kPlaneA = 3;
+constexpr int kKAlign = 128;       // plane rows are padded to a multiple of 128 organisms
+
+// Per-SNP constants the epilogue needs (derived from the three genotype counts only;
+// reference: encoder.h:91-133, tools.h:54-85).  64 bytes, one cache-line half.
+struct __align__(16) SnpCoef {
+    double mu;       // float-rounded additive imputation mean, widened   (encoder.h:114)
+    double xbar;     // mean of the imputed additive vector               (tools.h:81)
+    double inv_sd;   // 1 / population std of the imputed additive vector (tools.h:82)
+    double ch;       // dominance residual value for a het genotype: 2 - beta
+    double ca;       // ... hom-second: 2 - 2 beta
+    double cm;       // ... missing: mu_d - beta * mu_a
+    double rbar;     // mean of the residual vector
+    double inv_rsd;  // 1 / population std of the residual vector
+};
+
+constexpr uint8_t kFlagKeep = 1;   // passed the MAF filter (encoder.h:120-122)
+constexpr uint8_t kFlagDom = 2;    // residual std > std_thr (tools.h:31-33, ldscalc.h:40)
+
+// One 64x64 SNP-pair tile of the band.
+struct Tile {
+    int32_t a_row;   // row of the i-block inside the plane ring
+    int32_t b_row;   // row of the j-block inside the plane ring
+    int32_t i0;      // first SNP (shard-local index) of the i-block
+    int32_t j0;      // first SNP (shard-local index) of the j-block
+};
+
+// Per-row partial sums a tile contributes (SoA, index = tile * 64 + row).
+struct Partials {
+    double* add;     // sum of r2adj(A_i, A_j)
+    double* dom;     // sum of r2adj(A_i, D_j) over dominance-usable j
+    int32_t* wsa;    // in-window kept j
+    int32_t* wsd;    // ... that are dominance-usable
+    int32_t* wsde;   // ... with r2adj_dom > rsq_thr
+};
+
+struct BandArgs {
+    const Tile* tiles;
+    int32_t n_tiles;
+    int32_t k_steps;            // ceil(npad / 128)
+    const SnpCoef* coef;        // [n_load]
+    const uint8_t* flags;       // [n_load]
+    const int32_t* win_lo;      // [n_load] inclusive shard-local window bounds
+    const int32_t* win_hi;
+    int32_t n_load;
+    double n;                   // n_org
+    double inv_n;
+    double adj_c;               // (n - 1) / (n - 2)
+    double rsq_thr;
+    Partials part;
+    int32_t* dump;              // optional raw accumulators [tile][128][192] (parity hook)
+};
+
+// ---- error plumbing ----------------------------------------------------------------
+struct CudaError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+inline void cuda_check(cudaError_t e, const char* what, const char* file, int line) {
+    if (e != cudaSuccess) {
+        char buf[512];
+        snprintf(buf, sizeof(buf), "CUDA error %s at %s:%d: %s", what, file, line, cudaGetErrorString(e));
+        throw CudaError(buf);
+    }
+}
+#define CUDA_CHECK(x) ::nldsc::cuda_check((x), #x, __FILE__, __LINE__)
+
+// ---- kernel launchers (defined in the .cu files) -------------------------------------
+void launch_count(const uint8_t* packed, int64_t bps, int32_t n_rows, int32_t n_org,
+                  int32_t* counts, cudaStream_t st);
+void launch_stats(const int32_t* counts, int32_t n_rows, int32_t n_org, double maf_thr,
+                  double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
+                  double* rstd_out, cudaStream_t st);
+void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
+                   int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
+                   int32_t dst_row0, cudaStream_t st);
+void launch_zero_rows(int8_t* planes, int64_t plane_stride, int32_t npad, int32_t row0,
+                      int32_t n_rows, cudaStream_t st);
+
+// tcgen05 band kernel: needs the two TMA descriptors over the plane ring.
+struct BandMaps;   // opaque: 2 x CUtensorMap
+BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npad);
+void band_maps_destroy(BandMaps*);
+void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);
+void launch_band_simt(const int8_t* planes, int64_t plane_stride, int32_t npad,
+                      const BandArgs& args, cudaStream_t st);
+
+struct FinalizeArgs {
+    const int32_t* tile_begin;  // [n_iblocks + 1] tile range of every owned i-block
+    int32_t iblock0;            // shard-local block index of the first owned block in this chunk
+    int32_t n_iblocks;
+    int32_t own_begin;          // shard-local first owned row
+    int32_t own_end;
+    Partials part;
+    const uint8_t* flags;
+    double* l2;                 // outputs, indexed by (local row - own_begin)
+    double* l2d;
+    int32_t* wsa;
+    int32_t* wsd;
+    int32_t* wsde;
+};
+void launch_finalize(const FinalizeArgs& a, cudaStream_t st);
+
+}  // namespace nldsc

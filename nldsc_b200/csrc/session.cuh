@@ -1,0 +1,77 @@
+// Host-side shard state: plan (windows, halo, plane-ring chunks, band tiles) + device buffers.
+#pragma once
+#include "common.cuh"
+#include "../../include/nldsc_ld.h"
+
+#include <vector>
+
+namespace nldsc {
+
+struct InvalidArgument : std::invalid_argument {
+    using std::invalid_argument::invalid_argument;
+};
+
+// Inclusive window [lo, hi] of every SNP in ORIGINAL .bim indices:
+// {j : |pos_j - pos_i| <= wind}, the reference's SNPFilter::filter (tools.h:41-49)
+// evaluated with its own expression.  Requires 0 <= pos, non-decreasing.
+void compute_windows(const double* pos, int32_t n_snp, double wind, std::vector<int32_t>& lo,
+                     std::vector<int32_t>& hi);
+
+struct Chunk {
+    int32_t iblock0;      // first owned i-block (shard-local block index)
+    int32_t n_iblocks;
+    int32_t col0;         // first shard-local SNP row unpacked into the ring (multiple of 64)
+    int32_t n_cols;       // rows unpacked
+    int32_t tile0;        // offset into the tile list
+    int32_t n_tiles;
+    int32_t tb0;          // offset into tile_begin (n_iblocks + 1 entries)
+};
+
+}  // namespace nldsc
+
+struct nldsc_ld_session {
+    int device = 0;
+    int sm_count = 0;
+    int32_t n_org = 0, n_snp = 0;
+    int32_t row_begin = 0, row_end = 0;       // owned rows, original indices
+    int32_t load_begin = 0, load_end = 0;     // rows resident on the device, original indices
+    int32_t n_load = 0, own_begin = 0, own_end = 0;   // shard-local
+    int64_t bps = 0;
+    int32_t npad = 0;
+    double maf_thr = 0, std_thr = 0, rsq_thr = 0;
+    bool use_simt = false;
+    bool uploaded = false;
+
+    std::vector<nldsc::Chunk> chunks;
+    int64_t total_tiles = 0;
+    int64_t plane_rows = 0;                   // ring capacity in SNP rows
+
+    // device
+    uint8_t* d_packed = nullptr;
+    int32_t* d_counts = nullptr;
+    nldsc::SnpCoef* d_coef = nullptr;
+    uint8_t* d_flags = nullptr;
+    double* d_maf = nullptr;
+    double* d_rstd = nullptr;
+    int32_t* d_win_lo = nullptr;
+    int32_t* d_win_hi = nullptr;
+    int8_t* d_planes = nullptr;
+    nldsc::Tile* d_tiles = nullptr;
+    int32_t* d_tile_begin = nullptr;
+    nldsc::Partials part{};
+    double* d_l2 = nullptr;
+    double* d_l2d = nullptr;
+    int32_t* d_wsa = nullptr;
+    int32_t* d_wsd = nullptr;
+    int32_t* d_wsde = nullptr;
+    nldsc::BandMaps* maps = nullptr;
+    cudaStream_t own_stream = nullptr;
+
+    // timing of the last run(): event pairs per kernel family
+    struct Span { cudaEvent_t a, b; int family; };
+    std::vector<Span> spans;
+    size_t spans_used = 0;
+    cudaEvent_t ev_run0 = nullptr, ev_run1 = nullptr;
+    int32_t launches = 0;
+    bool ran = false;
+};

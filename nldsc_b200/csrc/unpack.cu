@@ -1,0 +1,214 @@
+// PLINK .bed 2-bit decode, per-SNP genotype counts and per-SNP statistics.
+//
+// Replaces (reference, nldsc/ldscore/_ldscore/):
+//   BedStreamReader::read            stream.h:43-69    -> count_kernel / unpack_kernel
+//   SNPInMemory::decode + ctor       encoder.h:54-60,91-133
+//   Math::regression_residuals       tools.h:54-68     -> stats_kernel (closed forms over
+//   Math::var_ / standardise         tools.h:70-85        the three genotype counts)
+//
+// Sample order: the reference assigns sample 4j+i to bit pair (7-2i,6-2i) of byte j and,
+// when n_org % 4 != 0, takes only the first n_org%4 (HIGH) pairs of the last byte
+// (stream.h:60-66).  Every quantity downstream is a sum over samples, so only
+// the SET of (byte, pair) slots matters, not their order: the kernels below keep all four
+// pairs of every full byte and the high n_org%4 pairs of the last byte, and place slot
+// (byte j, LSB-pair k) at organism index 4j+k of the plane row.
+//
+// This translation unit is compiled with -fmad=false: the MAF path must round exactly
+// like the reference's float code, and the closed forms rely on exact power-of-two
+// scaling so that collinear dominance codings give a residual std of exactly zero.
+#include "common.cuh"
+
+namespace nldsc {
+
+__device__ __forceinline__ uint32_t tail_pair_mask(int n_org) {
+    // bits of the LAST byte of a row that hold real samples (high n_org%4 pairs)
+    const int r = n_org & 3;
+    return r == 0 ? 0xFFu : ((0xFFu << (8 - 2 * r)) & 0xFFu);
+}
+
+// One warp per SNP row.  Rows start at arbitrary byte offsets, so the warp walks the
+// aligned 32-bit words that cover [b0, b1) and masks the bytes outside the row.
+__global__ void __launch_bounds__(256)
+count_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t n_rows, int32_t n_org,
+             int32_t* __restrict__ counts) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= n_rows) return;
+    const int64_t b0 = row * bps, b1 = b0 + bps;          // byte range of the row
+    const int64_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;       // covering word range
+    const uint32_t* __restrict__ words = reinterpret_cast<const uint32_t*>(packed);
+    const uint32_t tmask = tail_pair_mask(n_org);
+    int nh = 0, na = 0, nm = 0;
+    for (int64_t w = w0 + lane; w < w1; w += 32) {
+        uint32_t x = __ldg(words + w);
+        const int64_t wb = w << 2;
+        if (wb < b0) x &= 0xFFFFFFFFu << (8 * (int)(b0 - wb));
+        if (wb + 4 > b1) x &= 0xFFFFFFFFu >> (8 * (int)(wb + 4 - b1));
+        if (wb <= b1 - 1 && b1 - 1 < wb + 4) {             // word holds the row's last byte
+            const int sh = 8 * (int)(b1 - 1 - wb);
+            x &= ~(0xFFu << sh) | (tmask << sh);
+        }
+        const uint32_t lo = x & 0x55555555u, hi = (x >> 1) & 0x55555555u;
+        na += __popc(hi & lo);
+        nh += __popc(hi & ~lo);
+        nm += __popc(lo & ~hi);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        nh += __shfl_xor_sync(0xFFFFFFFFu, nh, o);
+        na += __shfl_xor_sync(0xFFFFFFFFu, na, o);
+        nm += __shfl_xor_sync(0xFFFFFFFFu, nm, o);
+    }
+    if (lane == 0) {
+        counts[row * 3 + 0] = nh;
+        counts[row * 3 + 1] = na;
+        counts[row * 3 + 2] = nm;
+    }
+}
+
+// One thread per SNP: everything the filters and the epilogue need, from three counts.
+__global__ void __launch_bounds__(256)
+stats_kernel(const int32_t* __restrict__ counts, int32_t n_rows, int32_t n_org, double maf_thr,
+             double std_thr, SnpCoef* __restrict__ coef, uint8_t* __restrict__ flags,
+             double* __restrict__ maf_out, double* __restrict__ rstd_out) {
+    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= n_rows) return;
+    const double nh = counts[row * 3 + 0], na = counts[row * 3 + 1], nm = counts[row * 3 + 2];
+    const double n = n_org;
+    const double n_obs = n - nm;
+    // encoder.h:104-118 -- double sums, float means, float MAF
+    const double add_sum = nh + 2.0 * na;
+    const double nadd_sum = 2.0 * (nh + na);
+    const float mu_a_f = (float)(add_sum / n_obs);
+    const float mu_d_f = (float)(nadd_sum / n_obs);
+    const float f2 = mu_a_f / 2.0f;
+    const float maf_f = ((double)f2 < 0.5) ? f2 : 1.0f - f2;
+    const bool keep = !((double)maf_f <= maf_thr);         // NaN passes
+    maf_out[row] = (double)maf_f;
+
+    SnpCoef c;
+    uint8_t fl = 0;
+    double rsd_out = __longlong_as_double(0x7FF8000000000000LL);
+    if (keep) {
+        const double mu = (double)mu_a_f, mud = (double)mu_d_f;   // imputed values (encoder.h:124-129)
+        const double n0 = n - nh - na - nm;
+        const double xbar = (nh + 2.0 * na + mu * nm) / n;
+        const double ybar = (2.0 * nh + 2.0 * na + mud * nm) / n;
+        const double sxx = nh + 4.0 * na + (mu * mu) * nm;
+        const double sxy = 2.0 * nh + 4.0 * na + (mu * mud) * nm;
+        const double beta = (sxy / n - xbar * ybar) / (sxx / n - xbar * xbar);   // tools.h:65-66
+        const double ch = 2.0 - beta, ca = 2.0 - 2.0 * beta, cm = mud - beta * mu;
+        // population variance, summed per genotype class (tools.h:70-73)
+        const double d0 = xbar, d1 = 1.0 - xbar, d2 = 2.0 - xbar, dm = mu - xbar;
+        const double var_x = (n0 * (d0 * d0) + nh * (d1 * d1) + na * (d2 * d2) + nm * (dm * dm)) / n;
+        const double sd = sqrt(var_x);
+        const double rbar = (nh * ch + na * ca + nm * cm) / n;
+        const double e1 = ch - rbar, e2 = ca - rbar, em = cm - rbar;
+        const double var_r = (n0 * (rbar * rbar) + nh * (e1 * e1) + na * (e2 * e2) + nm * (em * em)) / n;
+        const double rsd = sqrt(var_r);
+        c.mu = mu; c.xbar = xbar; c.inv_sd = 1.0 / sd;
+        c.ch = ch; c.ca = ca; c.cm = cm; c.rbar = rbar; c.inv_rsd = 1.0 / rsd;
+        fl = kFlagKeep | ((rsd > std_thr) ? kFlagDom : 0);
+        rsd_out = rsd;
+    } else {
+        c.mu = c.xbar = c.inv_sd = c.ch = c.ca = c.cm = c.rbar = c.inv_rsd = 0.0;
+    }
+    coef[row] = c;
+    flags[row] = fl;
+    rstd_out[row] = rsd_out;
+}
+
+// byte with four 2-bit genotype codes -> one 32-bit word per plane, byte k = sample k
+__device__ __forceinline__ void expand_byte(uint32_t b, uint32_t& g, uint32_t& m, uint32_t& h, uint32_t& a) {
+    const uint32_t p = (b | (b << 6) | (b << 12) | (b << 18)) & 0x03030303u;
+    const uint32_t lo = p & 0x01010101u, hi = (p >> 1) & 0x01010101u;
+    a = hi & lo;          // 11 hom-second
+    h = hi ^ a;           // 10 het
+    m = lo ^ a;           // 01 missing
+    g = hi + a;           // additive dosage 0/1/2
+}
+
+// grid.x = rows, grid.y * blockDim.x covers npad/16 sixteen-organism groups.
+// Each thread turns 4 packed bytes into 16 bytes of each of the 4 planes (coalesced 16-B stores).
+__global__ void __launch_bounds__(256)
+unpack_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t row0, int32_t n_org,
+              int32_t npad, int8_t* __restrict__ planes, int64_t plane_stride, int32_t dst_row0) {
+    const int t = blockIdx.y * blockDim.x + threadIdx.x;      // 16-organism group
+    if (t * 16 >= npad) return;
+    const int64_t row = (int64_t)row0 + blockIdx.x;
+    const int64_t rb = (int64_t)t * 4;                         // row-relative first byte
+    uint32_t x = 0;
+    if (rb < bps) {
+        const int64_t addr = row * bps + rb;
+        const uint32_t* __restrict__ words = reinterpret_cast<const uint32_t*>(packed);
+        const int64_t w = addr >> 2;
+        const int sh = (int)(addr & 3) * 8;
+        const uint32_t w0 = __ldg(words + w);
+        const uint32_t w1 = sh ? __ldg(words + w + 1) : 0u;   // buffer carries 8 bytes of slack
+        x = __funnelshift_r(w0, w1, sh);
+        const int64_t left = bps - rb;                          // bytes of this row still ahead
+        if (left < 4) x &= 0xFFFFFFFFu >> (8 * (int)(4 - left));
+        if (left <= 4) {                                        // holds the row's last byte
+            const int s2 = 8 * (int)(left - 1);
+            x &= ~(0xFFu << s2) | (tail_pair_mask(n_org) << s2);
+        }
+    }
+    uint4 g, m, h, a;
+    expand_byte(x & 0xFFu, g.x, m.x, h.x, a.x);
+    expand_byte((x >> 8) & 0xFFu, g.y, m.y, h.y, a.y);
+    expand_byte((x >> 16) & 0xFFu, g.z, m.z, h.z, a.z);
+    expand_byte(x >> 24, g.w, m.w, h.w, a.w);
+    const int64_t off = ((int64_t)dst_row0 + blockIdx.x) * npad + (int64_t)t * 16;
+    *reinterpret_cast<uint4*>(planes + kPlaneG * plane_stride + off) = g;
+    *reinterpret_cast<uint4*>(planes + kPlaneM * plane_stride + off) = m;
+    *reinterpret_cast<uint4*>(planes + kPlaneH * plane_stride + off) = h;
+    *reinterpret_cast<uint4*>(planes + kPlaneA * plane_stride + off) = a;
+}
+
+__global__ void __launch_bounds__(256)
+zero_rows_kernel(int8_t* __restrict__ planes, int64_t plane_stride, int32_t npad, int32_t row0) {
+    const int t = blockIdx.y * blockDim.x + threadIdx.x;
+    if (t * 16 >= npad) return;
+    const int64_t off = ((int64_t)row0 + blockIdx.x) * npad + (int64_t)t * 16;
+    const uint4 z = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int p = 0; p < kPlanes; ++p) *reinterpret_cast<uint4*>(planes + p * plane_stride + off) = z;
+}
+
+void launch_count(const uint8_t* packed, int64_t bps, int32_t n_rows, int32_t n_org,
+                  int32_t* counts, cudaStream_t st) {
+    if (n_rows <= 0) return;
+    const int wpb = 8;
+    count_kernel<<<(n_rows + wpb - 1) / wpb, wpb * 32, 0, st>>>(packed, bps, n_rows, n_org, counts);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_stats(const int32_t* counts, int32_t n_rows, int32_t n_org, double maf_thr,
+                  double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
+                  double* rstd_out, cudaStream_t st) {
+    if (n_rows <= 0) return;
+    stats_kernel<<<(n_rows + 255) / 256, 256, 0, st>>>(counts, n_rows, n_org, maf_thr, std_thr,
+                                                       coef, flags, maf_out, rstd_out);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
+                   int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
+                   int32_t dst_row0, cudaStream_t st) {
+    if (n_rows <= 0) return;
+    const int groups = npad / 16;
+    dim3 grid(n_rows, (groups + 255) / 256);
+    unpack_kernel<<<grid, 256, 0, st>>>(packed, bps, row0, n_org, npad, planes, plane_stride, dst_row0);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_zero_rows(int8_t* planes, int64_t plane_stride, int32_t npad, int32_t row0,
+                      int32_t n_rows, cudaStream_t st) {
+    if (n_rows <= 0) return;
+    const int groups = npad / 16;
+    dim3 grid(n_rows, (groups + 255) / 256);
+    zero_rows_kernel<<<grid, 256, 0, st>>>(planes, plane_stride, npad, row0);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace nldsc
