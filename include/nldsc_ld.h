@@ -66,11 +66,21 @@ int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char
 int nldsc_ld_calculate_packed(const uint8_t* packed, const nldsc_ld_params* params,
                               nldsc_ld_result* out, char* err, size_t errlen);
 
+/* ---- host-side planning (no GPU needed) --------------------------------------------------- */
+/* Inclusive window [lo[i], hi[i]] of every SNP: {j : |pos_j - pos_i| <= ld_wind}, the
+ * reference's SNPFilter::filter (tools.h:41-49) with the sliding-cache bounds of
+ * ChunkwiseReader (stream.h:142-155,182-197) for sorted non-negative positions. */
+int nldsc_ld_plan_windows(const nldsc_ld_params* params, int32_t* lo, int32_t* hi, char* err, size_t errlen);
+/* Contiguous SNP ranges of (roughly) equal band area for `parts` GPUs: shard k owns rows
+ * [cuts[k], cuts[k+1]); cuts has parts + 1 entries, interior cuts on multiples of 64. */
+int nldsc_ld_plan_shards(const nldsc_ld_params* params, int32_t parts, int32_t* cuts, char* err, size_t errlen);
+
 /* ---- session API: one shard on one GPU, device-resident between calls ------------- */
 typedef struct nldsc_ld_session nldsc_ld_session;
 
 typedef struct nldsc_ld_stats {
-    int64_t pairs;            /* sum of WSA over owned rows = ordered window SNP pairs scored */
+    int64_t pairs;            /* ordered in-window SNP pairs of the owned rows BEFORE the MAF filter
+                                 (the scored pairs are the sum of the returned l2_ws >= 0) */
     int64_t tiles;            /* 64x64 SNP-pair tiles issued to the band kernel */
     int32_t chunks;           /* plane-ring refills */
     int32_t kernel_launches;  /* kernels launched by the last run() */
@@ -101,6 +111,8 @@ int nldsc_ld_session_run(nldsc_ld_session* s, void* stream, char* err, size_t er
  * then synchronises `stream`. */
 int nldsc_ld_session_download(nldsc_ld_session* s, nldsc_ld_result* out, void* stream,
                               char* err, size_t errlen);
+/* Waits for the session's own copy and compute streams (upload / run issued with stream = NULL). */
+int nldsc_ld_session_sync(nldsc_ld_session* s, char* err, size_t errlen);
 int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* out);
 void nldsc_ld_session_destroy(nldsc_ld_session* s);
 

@@ -1,0 +1,252 @@
+"""ctypes binding of the C ABI declared in include/nldsc_ld.h (libnldsc_ld.so).
+
+There is no CPU fallback: importing works anywhere, but every compute call needs the
+in-tree CUDA library and a B200; a missing library raises at load time, a missing GPU
+raises RuntimeError from the call (the library reports NLDSC_ERR_RUNTIME).
+Error mapping follows the reference's pybind11 module: NLDSC_ERR_INVALID -> ValueError
+(std::invalid_argument, e.g. the PLINK magic check of stream.h:88-102), anything else ->
+RuntimeError.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libnldsc_ld.so")
+
+EXPORTS = [
+    "nldsc_ld_calculate", "nldsc_ld_calculate_packed", "nldsc_ld_session_create",
+    "nldsc_ld_session_upload", "nldsc_ld_session_run", "nldsc_ld_session_download",
+    "nldsc_ld_session_sync", "nldsc_ld_session_stats", "nldsc_ld_session_destroy",
+    "nldsc_ld_debug_unpack", "nldsc_ld_debug_cross_counts", "nldsc_ld_device_count",
+    "nldsc_ld_plan_windows", "nldsc_ld_plan_shards",
+]
+
+
+class Params(C.Structure):
+    _fields_ = [("bedfile", C.c_char_p), ("n_snp", C.c_int32), ("n_org", C.c_int32),
+                ("ld_wind", C.c_double), ("positions", C.POINTER(C.c_double)),
+                ("maf", C.c_double), ("std_thr", C.c_double), ("rsq_thr", C.c_double)]
+
+
+class Result(C.Structure):
+    _fields_ = [("l2", C.POINTER(C.c_double)), ("l2d", C.POINTER(C.c_double)),
+                ("maf", C.POINTER(C.c_double)), ("residuals_std", C.POINTER(C.c_double)),
+                ("l2_ws", C.POINTER(C.c_int32)), ("l2d_ws", C.POINTER(C.c_int32)),
+                ("l2d_wse", C.POINTER(C.c_int32))]
+
+
+class Stats(C.Structure):
+    _fields_ = [("pairs", C.c_int64), ("tiles", C.c_int64), ("chunks", C.c_int32),
+                ("kernel_launches", C.c_int32), ("load_begin", C.c_int32), ("load_end", C.c_int32),
+                ("npad", C.c_int32), ("band_impl", C.c_int32), ("ms_count", C.c_float),
+                ("ms_stats", C.c_float), ("ms_unpack", C.c_float), ("ms_band", C.c_float),
+                ("ms_finalize", C.c_float), ("ms_total", C.c_float)]
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m nldsc_b200.build` "
+                "(there is no CPU fallback for the LD-score path)")
+        L = C.CDLL(LIB_PATH)
+        for name in EXPORTS:
+            getattr(L, name)
+        L.nldsc_ld_session_destroy.restype = None
+        _lib = L
+    return _lib
+
+
+def _raise(rc: int, err) -> None:
+    if rc == 0:
+        return
+    msg = err.value.decode(errors="replace")
+    if rc == 1:
+        raise ValueError(msg)
+    raise RuntimeError(msg)
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _ip(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int32))
+
+
+def make_params(n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr, bedfile=None):
+    pos = np.ascontiguousarray(positions, dtype=np.float64)
+    if pos.shape != (n_snp,):
+        raise ValueError("positions must hold n_snp coordinates")
+    p = Params(os.fsencode(bedfile) if bedfile is not None else None, int(n_snp), int(n_org),
+               float(ld_wind), _dp(pos), float(maf), float(std_thr), float(rsq_thr))
+    p._keep = pos
+    return p
+
+
+def alloc_result(n):
+    out = {"l2": np.empty(n, np.float64), "l2d": np.empty(n, np.float64),
+           "maf": np.empty(n, np.float64), "residuals_std": np.empty(n, np.float64),
+           "l2_ws": np.empty(n, np.int32), "l2d_ws": np.empty(n, np.int32),
+           "l2d_wse": np.empty(n, np.int32)}
+    r = Result(_dp(out["l2"]), _dp(out["l2d"]), _dp(out["maf"]), _dp(out["residuals_std"]),
+               _ip(out["l2_ws"]), _ip(out["l2d_ws"]), _ip(out["l2d_wse"]))
+    return out, r
+
+
+def _host_ptr(packed) -> int:
+    """Address of a C-contiguous uint8 host buffer (numpy array or torch CPU tensor)."""
+    if hasattr(packed, "data_ptr"):
+        return packed.data_ptr()
+    a = np.ascontiguousarray(packed, dtype=np.uint8)
+    _host_ptr.keep = a
+    return a.ctypes.data
+
+
+def device_count() -> int:
+    n = C.c_int32(0)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_device_count(C.byref(n), err, C.c_size_t(512)), err)
+    return n.value
+
+
+def plan_windows(positions, ld_wind):
+    """Inclusive [lo, hi] window of every SNP (host-only)."""
+    n = len(positions)
+    p = make_params(n, 1, positions, ld_wind, 0.0, 0.0, 0.0)
+    lo, hi = np.empty(n, np.int32), np.empty(n, np.int32)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_plan_windows(C.byref(p), _ip(lo), _ip(hi), err, C.c_size_t(512)), err)
+    return lo, hi
+
+
+def plan_shards(positions, ld_wind, parts):
+    """Row cuts [parts + 1] of the contiguous shards used for `parts` GPUs (host-only)."""
+    n = len(positions)
+    p = make_params(n, 1, positions, ld_wind, 0.0, 0.0, 0.0)
+    cuts = np.empty(parts + 1, np.int32)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_plan_shards(C.byref(p), C.c_int32(parts), _ip(cuts), err, C.c_size_t(512)), err)
+    return cuts
+
+
+def calculate(bedfile, n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr) -> dict:
+    p = make_params(n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr, bedfile)
+    out, r = alloc_result(n_snp)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_calculate(C.byref(p), C.byref(r), err, C.c_size_t(512)), err)
+    return out
+
+
+def calculate_packed(packed, n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr, out=None) -> dict:
+    p = make_params(n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr)
+    if out is None:
+        out, r = alloc_result(n_snp)
+    else:
+        out, r = out
+    err = C.create_string_buffer(512)
+    ptr = C.c_void_p(_host_ptr(packed))
+    _raise(lib().nldsc_ld_calculate_packed(ptr, C.byref(p), C.byref(r), err, C.c_size_t(512)), err)
+    return out
+
+
+class Session:
+    """One shard on one GPU, device-resident between calls (nldsc_ld_session_*)."""
+
+    def __init__(self, device, n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr,
+                 row_begin=0, row_end=None):
+        self._h = C.c_void_p(None)
+        self._p = make_params(n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr)
+        self.n_snp, self.n_org = int(n_snp), int(n_org)
+        self.row_begin = int(row_begin)
+        self.row_end = int(n_snp if row_end is None else row_end)
+        err = C.create_string_buffer(512)
+        _raise(lib().nldsc_ld_session_create(C.byref(self._h), C.c_int(device), C.byref(self._p),
+                                             C.c_int32(self.row_begin), C.c_int32(self.row_end),
+                                             err, C.c_size_t(512)), err)
+        self.bps = (self.n_org + 3) // 4
+
+    def stats(self) -> dict:
+        st = Stats()
+        if lib().nldsc_ld_session_stats(self._h, C.byref(st)) != 0:
+            raise RuntimeError("nldsc_ld_session_stats failed")
+        return {k: getattr(st, k) for k, _ in Stats._fields_}
+
+    def upload(self, packed_all) -> None:
+        """packed_all: the whole bfile's rows [n_snp, bps] on the host; only this shard's
+        rows [load_begin, load_end) are copied (asynchronously, chunk by chunk)."""
+        st = self.stats()
+        base = _host_ptr(packed_all) + st["load_begin"] * self.bps
+        err = C.create_string_buffer(512)
+        _raise(lib().nldsc_ld_session_upload(self._h, C.c_void_p(base), None, err, C.c_size_t(512)), err)
+
+    def run(self) -> None:
+        err = C.create_string_buffer(512)
+        _raise(lib().nldsc_ld_session_run(self._h, None, err, C.c_size_t(512)), err)
+
+    def sync(self) -> None:
+        err = C.create_string_buffer(512)
+        _raise(lib().nldsc_ld_session_sync(self._h, err, C.c_size_t(512)), err)
+
+    def download(self, out=None) -> dict:
+        if out is None:
+            out = alloc_result(self.row_end - self.row_begin)
+        arrays, r = out
+        err = C.create_string_buffer(512)
+        _raise(lib().nldsc_ld_session_download(self._h, C.byref(r), None, err, C.c_size_t(512)), err)
+        return arrays
+
+    def close(self) -> None:
+        if self._h:
+            lib().nldsc_ld_session_destroy(self._h)
+            self._h = C.c_void_p(None)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def debug_unpack(packed, n_org):
+    """-> planes int8 [4, n_snp, npad] (g, m, h, a), counts int32 [n_snp, 3] (het, hom2, missing)."""
+    a = np.ascontiguousarray(packed, dtype=np.uint8)
+    n_snp = a.shape[0]
+    npad = C.c_int32(0)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_unpack(C.c_void_p(a.ctypes.data), C.c_int32(n_snp), C.c_int32(n_org),
+                                       None, None, C.byref(npad), err, C.c_size_t(512)), err)
+    planes = np.empty((4, n_snp, npad.value), np.int8)
+    counts = np.empty((n_snp, 3), np.int32)
+    _raise(lib().nldsc_ld_debug_unpack(C.c_void_p(a.ctypes.data), C.c_int32(n_snp), C.c_int32(n_org),
+                                       C.c_void_p(planes.ctypes.data), C.c_void_p(counts.ctypes.data),
+                                       C.byref(npad), err, C.c_size_t(512)), err)
+    return planes, counts
+
+
+def debug_cross_counts(packed, n_org, i_block, j_block) -> np.ndarray:
+    """Raw band-kernel accumulators for one 64x64 SNP block pair -> int64 [2, 3, 64, 64]
+    ordered (g, m) x (m, h, a), the layout of oracle.ld_oracle.cross_counts."""
+    a = np.ascontiguousarray(packed, dtype=np.uint8)
+    acc = np.empty((128, 192), np.int32)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_cross_counts(C.c_void_p(a.ctypes.data), C.c_int32(a.shape[0]),
+                                             C.c_int32(n_org), C.c_int32(i_block), C.c_int32(j_block),
+                                             C.c_void_p(acc.ctypes.data), err, C.c_size_t(512)), err)
+    # row 32*(s/16) + 16*p + s%16, column 64*q + t
+    r = acc.reshape(4, 2, 16, 3, 64)            # [s/16, p, s%16, q, t]
+    return r.transpose(1, 3, 0, 2, 4).reshape(2, 3, 64, 64).astype(np.int64)

@@ -82,9 +82,10 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 #define CUDA_CHECK(x) ::nldsc::cuda_check((x), #x, __FILE__, __LINE__)
 
 // ---- kernel launchers (defined in the .cu files) -------------------------------------
-void launch_count(const uint8_t* packed, int64_t bps, int32_t n_rows, int32_t n_org,
+// counts / coef / flags / maf / rstd are indexed by shard-local row; rows [row0, row0 + n_rows) are processed
+void launch_count(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows, int32_t n_org,
                   int32_t* counts, cudaStream_t st);
-void launch_stats(const int32_t* counts, int32_t n_rows, int32_t n_org, double maf_thr,
+void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
                   double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
                   double* rstd_out, cudaStream_t st);
 void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,

@@ -1,0 +1,103 @@
+// `_ldscore` -- drop-in replacement for the reference's pybind11 extension of the same name.
+//
+// Same Python surface as reference nldsc/ldscore/_ldscore/ldscore.cpp:17-54 (typed in
+// nldsc/ldscore/_ldscore.pyi): LDScoreParams(bfile, *, n_snp, n_org, ld_wind, maf, std_thr,
+// rsq_thr, positions), LDScoreResult with seven list attributes, calculate(params).  The body
+// forwards to the C ABI in include/nldsc_ld.h; nothing here computes.  Error mapping follows
+// the reference: std::invalid_argument -> ValueError (bad PLINK magic, stream.h:97-101),
+// std::runtime_error -> RuntimeError.  Unlike the reference the GIL is released for the call.
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/nldsc_ld.h"
+
+namespace py = pybind11;
+
+namespace {
+
+// Field names and order of reference data.h:33-66.
+struct LDScoreParams {
+    std::string bedfile;
+    int n_snp = 0;
+    int n_org = 0;
+    double ld_wind = 0;
+    std::vector<double> positions;
+    double maf = 0;
+    double std_thr = 0;
+    double rsq_thr = 0;
+};
+
+// reference data.h:21-31
+struct LDScoreResult {
+    std::vector<double> l2, l2d, maf, residuals_std;
+    std::vector<int> l2_ws, l2d_ws, l2d_wse;
+};
+
+LDScoreResult calculate(LDScoreParams& p) {
+    if (static_cast<long long>(p.positions.size()) != p.n_snp)
+        throw std::invalid_argument("positions must hold n_snp coordinates");
+    LDScoreResult r;
+    const size_t n = static_cast<size_t>(p.n_snp > 0 ? p.n_snp : 0);
+    r.l2.resize(n); r.l2d.resize(n); r.maf.resize(n); r.residuals_std.resize(n);
+    r.l2_ws.resize(n); r.l2d_ws.resize(n); r.l2d_wse.resize(n);
+    nldsc_ld_params cp{};
+    cp.bedfile = p.bedfile.c_str();
+    cp.n_snp = p.n_snp;
+    cp.n_org = p.n_org;
+    cp.ld_wind = p.ld_wind;
+    cp.positions = p.positions.data();
+    cp.maf = p.maf;
+    cp.std_thr = p.std_thr;
+    cp.rsq_thr = p.rsq_thr;
+    static_assert(sizeof(int) == sizeof(int32_t), "int32 result arrays");
+    nldsc_ld_result cr{r.l2.data(), r.l2d.data(), r.maf.data(), r.residuals_std.data(),
+                       r.l2_ws.data(), r.l2d_ws.data(), r.l2d_wse.data()};
+    char err[512] = {0};
+    int rc;
+    {
+        py::gil_scoped_release nogil;
+        rc = nldsc_ld_calculate(&cp, &cr, err, sizeof(err));
+    }
+    if (rc == NLDSC_ERR_INVALID) throw std::invalid_argument(err);
+    if (rc != NLDSC_OK) throw std::runtime_error(err);
+    return r;
+}
+
+}  // namespace
+
+PYBIND11_MODULE(_ldscore, m) {
+    m.doc() = "B200-native LD-score engine behind the reference's _ldscore interface";
+    py::class_<LDScoreParams>(m, "LDScoreParams")
+        .def(py::init<>())
+        .def(py::init([](const std::string& bfile, int n_snp, int n_org, double ld_wind, double maf, double std_thr,
+                         double rsq_thr, const std::vector<double>& positions) {
+                 LDScoreParams p;
+                 p.bedfile = bfile; p.n_snp = n_snp; p.n_org = n_org; p.ld_wind = ld_wind;
+                 p.maf = maf; p.std_thr = std_thr; p.rsq_thr = rsq_thr; p.positions = positions;
+                 return p;
+             }),
+             py::arg("bfile"), py::kw_only(), py::arg("n_snp"), py::arg("n_org"), py::arg("ld_wind"), py::arg("maf"),
+             py::arg("std_thr"), py::arg("rsq_thr"), py::arg("positions"))
+        .def_readwrite("bedfile", &LDScoreParams::bedfile)
+        .def_readwrite("n_snp", &LDScoreParams::n_snp)
+        .def_readwrite("n_org", &LDScoreParams::n_org)
+        .def_readwrite("ld_wind", &LDScoreParams::ld_wind)
+        .def_readwrite("positions", &LDScoreParams::positions)
+        .def_readwrite("maf", &LDScoreParams::maf)
+        .def_readwrite("std_thr", &LDScoreParams::std_thr)
+        .def_readwrite("rsq_thr", &LDScoreParams::rsq_thr);
+    py::class_<LDScoreResult>(m, "LDScoreResult")
+        .def(py::init<>())
+        .def_readwrite("l2", &LDScoreResult::l2)
+        .def_readwrite("l2d", &LDScoreResult::l2d)
+        .def_readwrite("maf", &LDScoreResult::maf)
+        .def_readwrite("residuals_std", &LDScoreResult::residuals_std)
+        .def_readwrite("l2_ws", &LDScoreResult::l2_ws)
+        .def_readwrite("l2d_ws", &LDScoreResult::l2d_ws)
+        .def_readwrite("l2d_wse", &LDScoreResult::l2d_wse);
+    m.def("calculate", &calculate, py::arg("params"));
+}

@@ -17,15 +17,19 @@ struct InvalidArgument : std::invalid_argument {
 void compute_windows(const double* pos, int32_t n_snp, double wind, std::vector<int32_t>& lo,
                      std::vector<int32_t>& hi);
 
+// A chunk = a run of owned i-blocks scored by one band launch.  SNP rows are unpacked into
+// the plane ring exactly once, in order: chunk c adds rows [new_row0, new_row1).
 struct Chunk {
     int32_t iblock0;      // first owned i-block (shard-local block index)
     int32_t n_iblocks;
-    int32_t col0;         // first shard-local SNP row unpacked into the ring (multiple of 64)
-    int32_t n_cols;       // rows unpacked
-    int32_t tile0;        // offset into the tile list
+    int32_t new_row0;     // shard-local rows this chunk adds to the ring (count, stats, unpack)
+    int32_t new_row1;
+    int64_t tile0;        // offset into the tile list
     int32_t n_tiles;
-    int32_t tb0;          // offset into tile_begin (n_iblocks + 1 entries)
+    int32_t tb0;          // offset into tile_begin (n_iblocks + 1 entries, relative to tile0)
 };
+
+enum Family { kFamCount = 0, kFamStats, kFamUnpack, kFamBand, kFamFinalize, kFamN };
 
 }  // namespace nldsc
 
@@ -44,7 +48,9 @@ struct nldsc_ld_session {
 
     std::vector<nldsc::Chunk> chunks;
     int64_t total_tiles = 0;
-    int64_t plane_rows = 0;                   // ring capacity in SNP rows
+    int64_t total_pairs = 0;                  // sum over owned rows of (window size - 1) before the MAF filter
+    int32_t max_chunk_tiles = 0;
+    int64_t plane_rows = 0;                   // ring capacity in SNP rows (multiple of 64)
 
     // device
     uint8_t* d_packed = nullptr;
@@ -65,7 +71,9 @@ struct nldsc_ld_session {
     int32_t* d_wsd = nullptr;
     int32_t* d_wsde = nullptr;
     nldsc::BandMaps* maps = nullptr;
-    cudaStream_t own_stream = nullptr;
+    cudaStream_t own_stream = nullptr;        // compute
+    cudaStream_t copy_stream = nullptr;       // H2D of packed rows, chunk by chunk
+    std::vector<cudaEvent_t> ev_uploaded;     // one per chunk
 
     // timing of the last run(): event pairs per kernel family
     struct Span { cudaEvent_t a, b; int family; };

@@ -29,11 +29,12 @@ __device__ __forceinline__ uint32_t tail_pair_mask(int n_org) {
 // One warp per SNP row.  Rows start at arbitrary byte offsets, so the warp walks the
 // aligned 32-bit words that cover [b0, b1) and masks the bytes outside the row.
 __global__ void __launch_bounds__(256)
-count_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t n_rows, int32_t n_org,
+count_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t row0, int32_t n_rows, int32_t n_org,
              int32_t* __restrict__ counts) {
     const int lane = threadIdx.x & 31;
-    const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= n_rows) return;
+    row += row0;
     const int64_t b0 = row * bps, b1 = b0 + bps;          // byte range of the row
     const int64_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;       // covering word range
     const uint32_t* __restrict__ words = reinterpret_cast<const uint32_t*>(packed);
@@ -68,11 +69,12 @@ count_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t n_rows, in
 
 // One thread per SNP: everything the filters and the epilogue need, from three counts.
 __global__ void __launch_bounds__(256)
-stats_kernel(const int32_t* __restrict__ counts, int32_t n_rows, int32_t n_org, double maf_thr,
+stats_kernel(const int32_t* __restrict__ counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
              double std_thr, SnpCoef* __restrict__ coef, uint8_t* __restrict__ flags,
              double* __restrict__ maf_out, double* __restrict__ rstd_out) {
-    const int row = blockIdx.x * blockDim.x + threadIdx.x;
+    int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_rows) return;
+    row += row0;
     const double nh = counts[row * 3 + 0], na = counts[row * 3 + 1], nm = counts[row * 3 + 2];
     const double n = n_org;
     const double n_obs = n - nm;
@@ -175,19 +177,19 @@ zero_rows_kernel(int8_t* __restrict__ planes, int64_t plane_stride, int32_t npad
     for (int p = 0; p < kPlanes; ++p) *reinterpret_cast<uint4*>(planes + p * plane_stride + off) = z;
 }
 
-void launch_count(const uint8_t* packed, int64_t bps, int32_t n_rows, int32_t n_org,
+void launch_count(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows, int32_t n_org,
                   int32_t* counts, cudaStream_t st) {
     if (n_rows <= 0) return;
     const int wpb = 8;
-    count_kernel<<<(n_rows + wpb - 1) / wpb, wpb * 32, 0, st>>>(packed, bps, n_rows, n_org, counts);
+    count_kernel<<<(n_rows + wpb - 1) / wpb, wpb * 32, 0, st>>>(packed, bps, row0, n_rows, n_org, counts);
     CUDA_CHECK(cudaGetLastError());
 }
 
-void launch_stats(const int32_t* counts, int32_t n_rows, int32_t n_org, double maf_thr,
+void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
                   double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
                   double* rstd_out, cudaStream_t st) {
     if (n_rows <= 0) return;
-    stats_kernel<<<(n_rows + 255) / 256, 256, 0, st>>>(counts, n_rows, n_org, maf_thr, std_thr,
+    stats_kernel<<<(n_rows + 255) / 256, 256, 0, st>>>(counts, row0, n_rows, n_org, maf_thr, std_thr,
                                                        coef, flags, maf_out, rstd_out);
     CUDA_CHECK(cudaGetLastError());
 }

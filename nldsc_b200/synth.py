@@ -144,3 +144,42 @@ def write_bfile(prefix: str, spec: SynthSpec, packed: np.ndarray | None = None,
     # the .bim stores cM with 8 decimals: hand back exactly what a parser will read
     cm_rt = np.array([float(f"{v:.8f}") for v in cm])
     return {"cm": cm_rt, "bp": bp, "n_snp": hi - lo, "n_org": spec.n_org}
+
+
+def generate_packed_cuda(spec: SynthSpec, device="cuda:0"):
+    """Same genotype model as generate_packed, drawn on the GPU with torch (different random
+    stream, so NOT byte-identical to the NumPy generator): the benchmark's workload at
+    BASELINE.json sizes takes seconds instead of minutes of host time.  torch is plumbing here
+    (RNG + elementwise ops); nothing of the LD-score path runs through it.
+    Returns a uint8 CUDA tensor [n_snp, ceil(n_org/4)] in PLINK (LSB-first) packing."""
+    import torch
+    dev = torch.device(device)
+    n, m = spec.n_org, spec.n_snp
+    n_chunks = (m + CHUNK - 1) // CHUNK
+    p = snp_frequencies(spec)
+    thr = np.full(n_chunks * CHUNK, -np.inf, dtype=np.float32)
+    nz = p > 0
+    thr[:m][nz] = _norm_ppf(p[nz]).astype(np.float32)
+    thr_t = torch.from_numpy(thr).to(dev).view(n_chunks, CHUNK)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(int(spec.seed) * 1000003 + 17)
+    bps = (n + 3) // 4
+    codes = torch.zeros((n_chunks, CHUNK, bps * 4), dtype=torch.uint8, device=dev)
+    a = float(np.sqrt(1.0 - spec.rho ** 2))
+    z = torch.randn((n_chunks, 2 * n), generator=gen, device=dev)
+    for t in range(CHUNK):
+        if t:
+            z.mul_(spec.rho).add_(torch.randn((n_chunks, 2 * n), generator=gen, device=dev), alpha=a)
+        al = z < thr_t[:, t:t + 1]
+        g = al[:, :n].to(torch.uint8) + al[:, n:].to(torch.uint8)         # 0 / 1 / 2 second alleles
+        codes[:, t, :n] = g + (g > 0).to(torch.uint8)                      # 0 -> 00, 1 -> 10 (het), 2 -> 11
+    codes = codes.view(n_chunks * CHUNK, bps * 4)[:m]
+    if spec.missing > 0:
+        for r0 in range(0, m, 8192):
+            blk = codes[r0:r0 + 8192]
+            miss = torch.rand(blk.shape, generator=gen, device=dev) < spec.missing
+            miss[:, 0] = False                                             # never an all-missing SNP (SURVEY F9)
+            miss[:, n:] = False
+            blk[miss] = 1
+    q = codes.view(m, bps, 4)
+    return (q[:, :, 0] | (q[:, :, 1] << 2) | (q[:, :, 2] << 4) | (q[:, :, 3] << 6)).contiguous()

@@ -1,0 +1,56 @@
+import glob
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN = sorted(glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz")))
+RESULT_KEYS = ("l2", "l2d", "maf", "residuals_std", "l2_ws", "l2d_ws", "l2d_wse")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a B200 (run with -m gpu on the GPU box)")
+
+
+def load_golden(path):
+    z = np.load(path)
+    g = {k: z[k] for k in z.files}
+    g["name"] = os.path.splitext(os.path.basename(path))[0]
+    for k in ("n_org",):
+        g[k] = int(g[k])
+    for k in ("ld_wind", "maf", "std_thr", "rsq_thr"):
+        g[k] = float(g[k])
+    return g
+
+
+@pytest.fixture(params=GOLDEN, ids=[os.path.splitext(os.path.basename(p))[0] for p in GOLDEN])
+def golden(request):
+    return load_golden(request.param)
+
+
+def assert_ld_close(got, want, *, exact_wsde=True, rtol=1e-9, label=""):
+    """The parity bar of BASELINE.json: filter decisions / retained lists / counts bit-exact,
+    L2 within 1e-9 relative, L2D within 1e-9 absolute-or-relative-to-max(|L2D|, 1)
+    (L2D is a sum of bias-corrected terms and legitimately crosses zero)."""
+    keep_w = ~np.isnan(want["l2"])
+    assert np.array_equal(np.isnan(got["l2"]), ~keep_w), label + " retained-SNP list"
+    assert np.array_equal(np.isnan(got["l2d"]), ~keep_w), label + " l2d NaN pattern"
+    assert np.array_equal(got["maf"], want["maf"], equal_nan=True), label + " maf bit-exact"
+    assert np.array_equal(got["l2_ws"], want["l2_ws"]), label + " WSA"
+    assert np.array_equal(got["l2d_ws"], want["l2d_ws"]), label + " WSD"
+    if exact_wsde:
+        assert np.array_equal(got["l2d_wse"], want["l2d_wse"]), label + " WSDE"
+    assert np.array_equal(np.isnan(got["residuals_std"]), np.isnan(want["residuals_std"])), label + " rstd NaN"
+    k = keep_w
+    if k.any():
+        rel = np.max(np.abs(got["l2"][k] - want["l2"][k]) / np.abs(want["l2"][k]))
+        assert rel <= rtol, f"{label} L2 rel err {rel}"
+        d = np.max(np.abs(got["l2d"][k] - want["l2d"][k]) / np.maximum(np.abs(want["l2d"][k]), 1.0))
+        assert d <= rtol, f"{label} L2D err {d}"
+        rs = np.max(np.abs(got["residuals_std"][k] - want["residuals_std"][k]))
+        assert rs <= rtol, f"{label} RSTD err {rs}"

@@ -1,0 +1,235 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle
+(oracle/ld_oracle.py) and the committed golden vectors of the compiled reference.
+
+Bar (BASELINE.json): filter decisions, retained-SNP lists, MAF and window counts bit-exact;
+L2 <= 1e-9 relative, L2D <= 1e-9 absolute-or-relative-to-max(|L2D|, 1), against the FP64
+build of the reference's own source (oracle-64)."""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+from conftest import RESULT_KEYS, assert_ld_close
+from nldsc_b200 import build, capi, synth
+from oracle import ld_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", autouse=True)
+def built():
+    build.build_module()
+    assert capi.device_count() >= 1
+
+
+def _ref64(g):
+    return {k: g["ref64_" + k] for k in RESULT_KEYS}
+
+
+def _run(g, **kw):
+    return capi.calculate_packed(g["packed"], g["packed"].shape[0], g["n_org"], g["positions"], g["ld_wind"],
+                                 g["maf"], g["std_thr"], g["rsq_thr"], **kw)
+
+
+def _case(n_org, n_snp, missing, seed, wind=1.0, density=340.0, maf=1e-4, std_thr=1e-5):
+    spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=missing, seed=seed, density=density)
+    packed = synth.generate_packed(spec)
+    cm, _ = synth.genetic_map(spec)
+    return {"packed": packed, "n_org": n_org, "positions": cm, "ld_wind": wind, "maf": maf, "std_thr": std_thr,
+            "rsq_thr": 1.0 / n_snp, "name": f"n{n_org}_m{n_snp}"}
+
+
+def _oracle(g):
+    return ld_oracle.ld_scores(g["packed"], g["n_org"], g["positions"], g["ld_wind"], g["maf"], g["std_thr"],
+                               g["rsq_thr"])
+
+
+# ---- unpack + count ------------------------------------------------------------------------
+
+@pytest.mark.parametrize("n_org", [1, 3, 4, 127, 128, 129, 1001, 1002, 1003, 4096])
+def test_unpack_and_count_match_decoder(n_org):
+    """BedStreamReader::read (stream.h:43-69) incl. the N%4 tail of SURVEY F4."""
+    rng = np.random.default_rng(n_org)
+    n_snp = 37
+    bps = (n_org + 3) // 4
+    packed = rng.integers(0, 256, (n_snp, bps), dtype=np.uint8)      # every code, every tail pattern
+    codes = ld_oracle.decode_bed_msb_first(packed, n_org)
+    planes, counts = capi.debug_unpack(packed, n_org)
+    want = np.stack([(codes == 2).sum(1), (codes == 3).sum(1), (codes == 1).sum(1)], 1)
+    assert np.array_equal(counts, want)
+    # planes hold the same multiset of samples per SNP (order inside a byte differs)
+    g, m, h, a = (planes[p].astype(np.int64) for p in range(4))
+    assert np.array_equal(h.sum(1), want[:, 0]) and np.array_equal(a.sum(1), want[:, 1])
+    assert np.array_equal(m.sum(1), want[:, 2]) and np.array_equal(g, h + 2 * a)
+    assert np.all((h + a + m) <= 1)
+    assert not planes[:, :, bps * 4:].any()                          # K padding is zero
+    # exact placement: slot (byte j, LSB pair k) -> organism 4j+k
+    lsb = np.stack([(packed >> (2 * k)) & 3 for k in range(4)], 2).reshape(n_snp, bps * 4)
+    valid = np.ones(bps * 4, bool)
+    if n_org % 4:
+        valid[(bps - 1) * 4:(bps - 1) * 4 + (4 - n_org % 4)] = False  # low pairs of the last byte are dropped
+    assert np.array_equal(h[:, :bps * 4], (lsb == 2) & valid)
+    assert np.array_equal(a[:, :bps * 4], (lsb == 3) & valid)
+    assert np.array_equal(m[:, :bps * 4], (lsb == 1) & valid)
+
+
+# ---- band GEMM: exact integer cross-counts -----------------------------------------------
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("n_org,n_snp", [(1003, 200), (130, 64), (5000, 130)])
+def test_cross_counts_exact(impl, n_org, n_snp, monkeypatch):
+    monkeypatch.setenv("NLDSC_BAND", impl)
+    rng = np.random.default_rng(n_org + n_snp)
+    packed = rng.integers(0, 256, (n_snp, (n_org + 3) // 4), dtype=np.uint8)
+    codes = ld_oracle.decode_bed_msb_first(packed, n_org)
+    nb = (n_snp + 63) // 64
+    pad = np.zeros((nb * 64, n_org), np.uint8)
+    pad[:n_snp] = codes
+    for ib, jb in {(0, 0), (0, nb - 1), (nb - 1, 0), (nb - 1, nb - 1)}:
+        got = capi.debug_cross_counts(packed, n_org, ib, jb)
+        want = ld_oracle.cross_counts(pad[ib * 64:ib * 64 + 64], pad[jb * 64:jb * 64 + 64])
+        assert np.array_equal(got, want), (impl, ib, jb)
+
+
+# ---- end to end ------------------------------------------------------------------------------
+
+@pytest.mark.parametrize("impl", ["simt", "tc"])
+def test_golden_reference_parity(golden, impl, monkeypatch):
+    monkeypatch.setenv("NLDSC_BAND", impl)
+    got = _run(golden)
+    assert_ld_close(got, _ref64(golden), label=f"{golden['name']}[{impl}]")
+
+
+def test_cfg1_full_parity():
+    """BASELINE.json configs[0]: N=1,000 x 10,000 SNPs, 1 cM, no missing -- every SNP vs the oracle."""
+    g = _case(1000, 10000, 0.0, seed=1)
+    assert_ld_close(_run(g), _oracle(g), label="cfg1")
+
+
+def test_missing_and_ragged_parity():
+    g = _case(2051, 3000, 0.02, seed=2)           # n % 4 == 3, 2% missing (configs[1] shape, scaled)
+    assert_ld_close(_run(g), _oracle(g), label="ragged")
+
+
+def test_tc_equals_simt_bitwise(monkeypatch):
+    g = _case(777, 1500, 0.03, seed=5)
+    monkeypatch.setenv("NLDSC_BAND", "tc")
+    a = _run(g)
+    monkeypatch.setenv("NLDSC_BAND", "simt")
+    b = _run(g)
+    for k in RESULT_KEYS:
+        assert np.array_equal(a[k], b[k], equal_nan=True), k
+
+
+def test_chunked_ring_equals_single_pass_bitwise(monkeypatch):
+    """Small chunks and a ring barely wider than one window (rows wrap many times)."""
+    g = _case(600, 4000, 0.02, seed=6, wind=0.5)
+    base = _run(g)
+    monkeypatch.setenv("NLDSC_CHUNK_ROWS", "128")
+    monkeypatch.setenv("NLDSC_PLANE_BYTES", str(640 * 4 * 640))      # 640 SNP rows of 4 x 640 bytes
+    small = _run(g)
+    for k in RESULT_KEYS:
+        assert np.array_equal(base[k], small[k], equal_nan=True), k
+
+
+def test_sharded_equals_single_bitwise():
+    """contiguous SNP ranges + halo, no exchange; gathered == single-GPU bitwise."""
+    g = _case(900, 3000, 0.02, seed=7)
+    n_snp = 3000
+    base = _run(g)
+    cuts = capi.plan_shards(g["positions"], g["ld_wind"], 3)
+    got = {k: np.empty_like(base[k]) for k in RESULT_KEYS}
+    for k in range(3):
+        with capi.Session(0, n_snp, g["n_org"], g["positions"], g["ld_wind"], g["maf"], g["std_thr"], g["rsq_thr"],
+                          row_begin=int(cuts[k]), row_end=int(cuts[k + 1])) as s:
+            s.upload(g["packed"])
+            s.run()
+            part = s.download()
+            st = s.stats()
+            assert st["load_begin"] <= cuts[k] and st["load_end"] >= cuts[k + 1]
+            if k == 1:
+                assert st["load_begin"] > 0 and st["load_end"] < n_snp      # really a halo, not the whole file
+        for key in RESULT_KEYS:
+            got[key][cuts[k]:cuts[k + 1]] = part[key]
+    for key in RESULT_KEYS:
+        assert np.array_equal(base[key], got[key], equal_nan=True), key
+    # unaligned cut (not a multiple of 64)
+    with capi.Session(0, n_snp, g["n_org"], g["positions"], g["ld_wind"], g["maf"], g["std_thr"], g["rsq_thr"],
+                      row_begin=1000, row_end=1777) as s:
+        s.upload(g["packed"])
+        s.run()
+        part = s.download()
+    for key in RESULT_KEYS:
+        assert np.array_equal(base[key][1000:1777], part[key], equal_nan=True), key
+
+
+def test_multi_gpu_env_matches_single(monkeypatch):
+    if capi.device_count() < 2:
+        pytest.skip("one GPU")
+    g = _case(900, 3000, 0.02, seed=8)
+    base = _run(g)
+    monkeypatch.setenv("NLDSC_GPUS", "2")
+    two = _run(g)
+    for key in RESULT_KEYS:
+        assert np.array_equal(base[key], two[key], equal_nan=True), key
+
+
+def test_degenerate_snps():
+    """Monomorphic SNPs are dropped (NaN / -1), collinear-dominance SNPs (no hom-second, residual
+    std exactly 0) are kept but not dominance-usable, equal positions share a window."""
+    g = _case(400, 700, 0.0, seed=9)
+    codes = ld_oracle.decode_bed_msb_first(g["packed"], 400).copy()
+    codes[5] = 0                                   # monomorphic
+    codes[6][codes[6] == 3] = 2                    # no hom-second -> dominance coding collinear
+    g["packed"] = synth.pack_codes(codes)
+    # pack_codes is LSB-first, the decoder MSB-first: only the multiset per SNP matters
+    g["positions"] = g["positions"].copy()
+    g["positions"][300:320] = g["positions"][300]
+    got, want = _run(g), _oracle(g)
+    assert_ld_close(got, want, label="degenerate")
+    assert np.isnan(got["l2"][5]) and got["l2_ws"][5] == -1 and got["maf"][5] == 0.0
+    assert got["residuals_std"][6] == 0.0 and got["l2_ws"][6] >= 0
+
+
+def test_bfile_path_and_module(tmp_path):
+    """nldsc_ld_calculate on a real .bed, and the pybind11 `_ldscore` drop-in on top of it."""
+    spec = synth.SynthSpec(n_org=501, n_snp=900, missing=0.02, seed=12)
+    packed = synth.generate_packed(spec)
+    info = synth.write_bfile(str(tmp_path / "t"), spec, packed)
+    want = ld_oracle.ld_scores(packed, 501, info["cm"], 1.0, 1e-4, 1e-5, 1 / 900)
+    got = capi.calculate(str(tmp_path / "t.bed"), 900, 501, info["cm"], 1.0, 1e-4, 1e-5, 1 / 900)
+    assert_ld_close(got, want, label="bfile")
+    sp = importlib.util.spec_from_file_location("_ldscore", build.ext_path())
+    m = importlib.util.module_from_spec(sp)
+    sp.loader.exec_module(m)
+    r = m.calculate(m.LDScoreParams(str(tmp_path / "t.bed"), n_snp=900, n_org=501, ld_wind=1.0, maf=1e-4,
+                                    std_thr=1e-5, rsq_thr=1 / 900, positions=list(info["cm"])))
+    for key in RESULT_KEYS:
+        assert np.array_equal(np.asarray(getattr(r, key)), got[key], equal_nan=True), key
+    assert isinstance(r.l2, list) and isinstance(r.l2_ws[0], int)
+
+
+def test_properties_at_bench_scale():
+    """configs[1] shape (N=10,000, 2% missing) on a 12,288-SNP slice: too big for the full
+    oracle in seconds, so size-independent properties + oracle on random rows."""
+    g = _case(10000, 12288, 0.02, seed=2)
+    out = _run(g)
+    keep = out["l2_ws"] >= 0
+    lo, hi = capi.plan_windows(g["positions"], g["ld_wind"])
+    # WSA = kept SNPs in the window minus self (ldscalc.h:52, stream.h:142-155)
+    ck = np.concatenate([[0], np.cumsum(keep)])
+    assert np.array_equal(out["l2_ws"][keep], (ck[hi + 1] - ck[lo])[keep] - 1)
+    assert np.all(out["l2d_ws"][keep] <= out["l2_ws"][keep]) and np.all(out["l2d_wse"][keep] <= out["l2d_ws"][keep])
+    # r2adj >= -1/(N-2) per pair
+    assert np.all(out["l2"][keep] >= 1.0 - out["l2_ws"][keep] / (10000 - 2) - 1e-9)
+    # oracle on three random rows with their full windows
+    rng = np.random.default_rng(0)
+    for i in rng.choice(np.nonzero(keep)[0], 3, replace=False):
+        a, b = lo[i], hi[i] + 1
+        sub = ld_oracle.ld_scores(g["packed"][a:b], 10000, g["positions"][a:b], g["ld_wind"], g["maf"],
+                                  g["std_thr"], g["rsq_thr"])
+        assert sub["l2_ws"][i - a] == out["l2_ws"][i]
+        assert abs(sub["l2"][i - a] - out["l2"][i]) <= 1e-9 * abs(sub["l2"][i - a])
+        assert abs(sub["l2d"][i - a] - out["l2d"][i]) <= 1e-9 * max(1.0, abs(sub["l2d"][i - a]))
+        assert sub["l2d_wse"][i - a] == out["l2d_wse"][i]

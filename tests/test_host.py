@@ -1,0 +1,111 @@
+"""CPU: the C-ABI library loads and exports what include/nldsc_ld.h declares, the host-side
+planning matches the reference's window semantics, and the error behaviour of the boundary
+(no compute happens here: there is no GPU and no CPU fallback)."""
+import os
+import re
+import struct
+
+import numpy as np
+import pytest
+
+from nldsc_b200 import build, capi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module", autouse=True)
+def built():
+    build.build_module()
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "nldsc_ld.h")).read()
+    declared = set(re.findall(r"\b(nldsc_ld_[a-z_]+)\s*\(", hdr))
+    declared -= {"nldsc_ld_params", "nldsc_ld_result", "nldsc_ld_stats", "nldsc_ld_session"}
+    assert len(declared) >= 12
+    L = capi.lib()
+    for name in sorted(declared):
+        assert hasattr(L, name), name
+    assert declared == set(capi.EXPORTS)
+
+
+def test_windows_match_reference_semantics():
+    rng = np.random.default_rng(0)
+    pos = np.sort(rng.uniform(0, 5, 3000))
+    pos[100:110] = pos[100]                       # ties
+    for wind in (0.0, 0.01, 0.3, 10.0):
+        lo, hi = capi.plan_windows(pos, wind)
+        for i in rng.integers(0, 3000, 200):
+            inw = np.nonzero(np.abs(pos - pos[i]) <= wind)[0]     # tools.h:43-44
+            assert lo[i] == inw[0] and hi[i] == inw[-1]
+
+
+def test_shard_cuts_cover_rows_once():
+    pos = np.cumsum(np.random.default_rng(1).exponential(1 / 340, 20000))
+    for parts in (1, 2, 3, 8):
+        cuts = capi.plan_shards(pos, 1.0, parts)
+        assert cuts[0] == 0 and cuts[-1] == 20000 and np.all(np.diff(cuts) >= 0)
+        assert np.all(cuts[1:-1] % 64 == 0)
+        lo, hi = capi.plan_windows(pos, 1.0)
+        area = np.add.reduceat((hi - lo + 1).astype(np.int64), cuts[:-1][np.diff(cuts) > 0])
+        assert area.max() / area.mean() < 1.15
+
+
+def test_invalid_positions_rejected():
+    with pytest.raises(ValueError):
+        capi.plan_windows(np.array([0.0, 2.0, 1.0]), 1.0)
+    with pytest.raises(ValueError):
+        capi.plan_windows(np.array([-1.0, 2.0]), 1.0)
+
+
+def test_bad_magic_is_value_error(tmp_path):
+    """reference stream.h:88-102 throws std::invalid_argument -> ValueError."""
+    p = tmp_path / "bad.bed"
+    p.write_bytes(bytes([0x6C, 0x1B, 0x00]) + bytes(10))
+    with pytest.raises(ValueError, match="magic"):
+        capi.calculate(str(p), 5, 8, np.arange(5.0), 1.0, 0.01, 1e-5, 0.1)
+
+
+def test_truncated_bed_is_value_error(tmp_path):
+    p = tmp_path / "short.bed"
+    p.write_bytes(bytes([0x6C, 0x1B, 0x01]) + bytes(9))
+    with pytest.raises(ValueError, match="size"):
+        capi.calculate(str(p), 5, 8, np.arange(5.0), 1.0, 0.01, 1e-5, 0.1)
+
+
+def test_missing_file_is_runtime_error():
+    with pytest.raises(RuntimeError):
+        capi.calculate("/nonexistent/x.bed", 5, 8, np.arange(5.0), 1.0, 0.01, 1e-5, 0.1)
+
+
+def test_ldscore_module_surface():
+    """Same names / kwargs / attributes as reference ldscore.cpp:17-54."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_ldscore", build.ext_path())
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    p = m.LDScoreParams("/x.bed", n_snp=2, n_org=4, ld_wind=1.0, maf=0.1, std_thr=1e-5, rsq_thr=0.1,
+                        positions=[0.0, 1.0])
+    assert (p.bedfile, p.n_snp, p.n_org, p.ld_wind, p.maf, p.std_thr, p.rsq_thr, p.positions) == \
+        ("/x.bed", 2, 4, 1.0, 0.1, 1e-5, 0.1, [0.0, 1.0])
+    with pytest.raises(TypeError):
+        m.LDScoreParams("/x.bed", 2, 4, 1.0, 0.1, 1e-5, 0.1, [0.0, 1.0])     # kw_only, ldscore.cpp:23
+    r = m.LDScoreResult()
+    for f in ("l2", "l2d", "maf", "residuals_std", "l2_ws", "l2d_ws", "l2d_wse"):
+        assert getattr(r, f) == []
+    q = m.LDScoreParams()
+    q.positions = [1.0]
+    assert q.positions == [1.0]
+    with pytest.raises(RuntimeError):
+        m.calculate(p)                                                       # no such file
+
+
+@pytest.mark.skipif(os.path.exists("/dev/nvidiactl"), reason="GPU box")
+def test_no_cpu_fallback(tmp_path):
+    """Without a GPU the product path fails loudly instead of computing on the host."""
+    p = tmp_path / "ok.bed"
+    p.write_bytes(bytes([0x6C, 0x1B, 0x01]) + bytes(2 * 5))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        capi.calculate(str(p), 5, 8, np.arange(5.0), 1.0, 0.01, 1e-5, 0.1)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        capi.calculate_packed(np.zeros((5, 2), np.uint8), 5, 8, np.arange(5.0), 1.0, 0.01, 1e-5, 0.1)
