@@ -1,0 +1,41 @@
+"""`python -m nldsc_b200 ld ...` -- the reference's `ld` command line (nldsc/__main__.py:35-97):
+same flags, same exactly-one-window rule, same output file."""
+from __future__ import annotations
+
+import argparse
+import sys
+
+from .ldscore import estimate_lds
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(prog="nldsc_b200")
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    ld = sub.add_parser("ld", help="estimate additive and dominance LD scores")
+    ld.add_argument("--bfile", required=True)
+    ld.add_argument("-o", "--out")
+    ld.add_argument("-kb", "--ld-wind-kb", dest="ld_wind_kb")
+    ld.add_argument("-cm", "--ld-wind-cm", dest="ld_wind_cm")
+    ld.add_argument("-maf", "--maf-thr", dest="maf_thr", required=True)   # effectively mandatory
+    ld.add_argument("-std", "--std-thr", dest="std_thr", default="1e-4")
+    ld.add_argument("-rsq", "--rsq-thr", dest="rsq_thr", default=None)
+    ld.add_argument("--extra", action="store_true")
+    ld.add_argument("--display", action="store_true")
+    a = ap.parse_args(argv)
+    if (a.ld_wind_kb is None) == (a.ld_wind_cm is None):
+        print("Must specify exactly one --ld-wind option", file=sys.stderr)
+        return 2
+    wind, metric = (a.ld_wind_kb, "kbp") if a.ld_wind_kb is not None else (a.ld_wind_cm, "cm")
+    try:
+        df = estimate_lds(a.bfile, wind, metric, a.maf_thr, a.std_thr, a.rsq_thr, out=a.out, extra=a.extra,
+                          summary=True)
+    except Exception as e:            # reference handle_exception: log + SystemExit (__main__.py:17-26)
+        print(f"error: {e}", file=sys.stderr)
+        return 1
+    if df is not None and a.display:
+        print(df.to_string())
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

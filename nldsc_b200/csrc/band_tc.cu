@@ -322,11 +322,8 @@ void band_maps_destroy(BandMaps* m) { delete m; }
 
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
     if (args.n_tiles <= 0) return;
-    static bool attr_set = false;
-    if (!attr_set) {
-        CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-        attr_set = true;
-    }
+    // per device (several GPUs may be driven from one process), so not cached in a static
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     const int grid = args.n_tiles < sm_count ? args.n_tiles : sm_count;
     band_tc_kernel<<<grid, kThreads, kSmemBytes, st>>>(maps->a, maps->b, args);
     CUDA_CHECK(cudaGetLastError());

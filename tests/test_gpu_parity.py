@@ -112,14 +112,14 @@ def test_missing_and_ragged_parity():
     assert_ld_close(_run(g), _oracle(g), label="ragged")
 
 
-def test_tc_equals_simt_bitwise(monkeypatch):
+def test_tc_agrees_with_simt_yardstick(monkeypatch):
+    """Same integer cross-counts, same epilogue; only the FP64 summation order inside a tile differs."""
     g = _case(777, 1500, 0.03, seed=5)
     monkeypatch.setenv("NLDSC_BAND", "tc")
     a = _run(g)
     monkeypatch.setenv("NLDSC_BAND", "simt")
     b = _run(g)
-    for k in RESULT_KEYS:
-        assert np.array_equal(a[k], b[k], equal_nan=True), k
+    assert_ld_close(a, b, rtol=1e-12, label="tc vs simt")
 
 
 def test_chunked_ring_equals_single_pass_bitwise(monkeypatch):
