@@ -81,7 +81,7 @@ typedef struct nldsc_ld_session nldsc_ld_session;
 typedef struct nldsc_ld_stats {
     int64_t pairs;            /* ordered in-window SNP pairs of the owned rows BEFORE the MAF filter
                                  (the scored pairs are the sum of the returned l2_ws >= 0) */
-    int64_t tiles;            /* 64x64 SNP-pair tiles issued to the band kernel */
+    int64_t tiles;            /* supertiles (2 i-blocks x 1 j-block of 64 SNPs) issued to the band kernel */
     int32_t chunks;           /* plane-ring refills */
     int32_t kernel_launches;  /* kernels launched by the last run() */
     int32_t load_begin;       /* first SNP row the shard needs (owned range minus halo, 64-aligned) */
@@ -128,6 +128,15 @@ int nldsc_ld_debug_unpack(const uint8_t* packed, int32_t n_snp, int32_t n_org, i
 int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_org,
                                 int32_t i_block, int32_t j_block, int32_t* acc_out,
                                 char* err, size_t errlen);
+/* nldsc_ld_plan_windows evaluated by the device kernel the calculate entry points use (plan.cu);
+ * must equal the host routine element for element. */
+int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* lo, int32_t* hi, char* err, size_t errlen);
+/* Measurement hook: runs the band kernel on `n_tiles` synthetic supertiles (2 x 64 x 64 SNP pairs each,
+ * K = n_org, band-like operand reuse) `reps` times and returns the mean CUDA-event time of one launch.
+ * mode 0 = the real kernel (TMA + MMA + epilogue), 1 = tcgen05 MMAs only (no operand loads: the int8
+ * tensor-pipe ceiling of this tile shape), 2 = TMA loads only (no MMAs: the operand-feed ceiling). */
+int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int32_t reps, float* ms_out,
+                              char* err, size_t errlen);
 /* Number of usable CUDA devices (0 and an error message when none). */
 int nldsc_ld_device_count(int32_t* count, char* err, size_t errlen);
 

@@ -22,7 +22,7 @@ EXPORTS = [
     "nldsc_ld_session_upload", "nldsc_ld_session_run", "nldsc_ld_session_download",
     "nldsc_ld_session_sync", "nldsc_ld_session_stats", "nldsc_ld_session_destroy",
     "nldsc_ld_debug_unpack", "nldsc_ld_debug_cross_counts", "nldsc_ld_device_count",
-    "nldsc_ld_plan_windows", "nldsc_ld_plan_shards",
+    "nldsc_ld_plan_windows", "nldsc_ld_plan_shards", "nldsc_ld_debug_band_probe", "nldsc_ld_debug_plan_windows_device",
 ]
 
 
@@ -125,6 +125,16 @@ def plan_windows(positions, ld_wind):
     lo, hi = np.empty(n, np.int32), np.empty(n, np.int32)
     err = C.create_string_buffer(512)
     _raise(lib().nldsc_ld_plan_windows(C.byref(p), _ip(lo), _ip(hi), err, C.c_size_t(512)), err)
+    return lo, hi
+
+
+def plan_windows_device(positions, ld_wind):
+    """plan_windows computed by the device kernel of the calculate path (parity hook)."""
+    n = len(positions)
+    p = make_params(n, 1, positions, ld_wind, 0.0, 0.0, 0.0)
+    lo, hi = np.empty(n, np.int32), np.empty(n, np.int32)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_plan_windows_device(C.byref(p), _ip(lo), _ip(hi), err, C.c_size_t(512)), err)
     return lo, hi
 
 
@@ -250,3 +260,15 @@ def debug_cross_counts(packed, n_org, i_block, j_block) -> np.ndarray:
     # row 32*(s/16) + 16*p + s%16, column 64*q + t
     r = acc.reshape(4, 2, 16, 3, 64)            # [s/16, p, s%16, q, t]
     return r.transpose(1, 3, 0, 2, 4).reshape(2, 3, 64, 64).astype(np.int64)
+
+
+def debug_band_probe(mode: int, n_org: int, n_tiles: int, reps: int = 5) -> dict:
+    """Band kernel on synthetic supertiles: mode 0 real, 1 MMA only, 2 TMA only.
+    -> {ms, tops} where tops counts the int8 ops the MMAs of one launch perform (2 * 256 * 192 * npad per supertile)."""
+    ms = C.c_float(0)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_band_probe(C.c_int32(mode), C.c_int32(n_org), C.c_int32(n_tiles), C.c_int32(reps),
+                                           C.byref(ms), err, C.c_size_t(512)), err)
+    npad = (n_org + 127) // 128 * 128
+    ops = 2.0 * 256 * 192 * npad * n_tiles
+    return {"ms": ms.value, "tops": ops / (ms.value * 1e-3) / 1e12, "gbs_operands": n_tiles * 2 * 28672 * (npad // 128) / (ms.value * 1e-3) / 1e9}

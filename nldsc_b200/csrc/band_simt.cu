@@ -14,13 +14,14 @@ constexpr int kChunk = 64;            // organisms per shared-memory pass
 constexpr int kPitch = kChunk / 4 + 1;   // words per row (+1: fewer bank conflicts)
 }
 
-// block = one tile; 256 threads; thread (s = tid/4, cg = tid%4) scores SNP s of the
-// i-block against j-SNPs cg*16 .. cg*16+15.
+// block = one (supertile, rank) = one 64x64 SNP-pair tile; 256 threads; thread (s = tid/4, cg = tid%4)
+// scores SNP s of the i-block against j-SNPs cg*16 .. cg*16+15.
 __global__ void __launch_bounds__(256)
 band_simt_kernel(const int8_t* __restrict__ planes, int64_t plane_stride, int32_t npad, const BandArgs args) {
     __shared__ uint32_t sh[5][kBlk][kPitch];   // g_i, m_i, m_j, h_j, a_j
-    const int t = blockIdx.x;
+    const int t = blockIdx.x >> 1, rank = blockIdx.x & 1;
     const Tile tl = args.tiles[t];
+    const int32_t a_row = tl.a_row[rank], i0 = tl.i0[rank];
     const int s = threadIdx.x >> 2, cg = threadIdx.x & 3;
 
     int32_t acc[6][16];
@@ -29,8 +30,8 @@ band_simt_kernel(const int8_t* __restrict__ planes, int64_t plane_stride, int32_
 #pragma unroll
         for (int c = 0; c < 16; ++c) acc[p][c] = 0;
 
-    const int8_t* src[5] = {planes + kPlaneG * plane_stride + (int64_t)tl.a_row * npad,
-                            planes + kPlaneM * plane_stride + (int64_t)tl.a_row * npad,
+    const int8_t* src[5] = {planes + kPlaneG * plane_stride + (int64_t)a_row * npad,
+                            planes + kPlaneM * plane_stride + (int64_t)a_row * npad,
                             planes + kPlaneM * plane_stride + (int64_t)tl.b_row * npad,
                             planes + kPlaneH * plane_stride + (int64_t)tl.b_row * npad,
                             planes + kPlaneA * plane_stride + (int64_t)tl.b_row * npad};
@@ -64,7 +65,7 @@ band_simt_kernel(const int8_t* __restrict__ planes, int64_t plane_stride, int32_
 
     if (args.dump != nullptr) {
         // same layout as the tensor-core kernel's accumulator dump
-        int32_t* d = args.dump + (int64_t)t * 128 * 192;
+        int32_t* d = args.dump + (int64_t)blockIdx.x * 128 * 192;
         const int rg = 32 * (s / 16) + (s % 16), rm = rg + 16;
 #pragma unroll
         for (int c = 0; c < 16; ++c) {
@@ -78,7 +79,7 @@ band_simt_kernel(const int8_t* __restrict__ planes, int64_t plane_stride, int32_
         }
     }
 
-    const RowCtx row = load_row_ctx(args, tl.i0 + s);
+    const RowCtx row = load_row_ctx(args, i0 + s);
     RowAcc ra;
 #pragma unroll
     for (int c = 0; c < 16; ++c)
@@ -93,7 +94,7 @@ band_simt_kernel(const int8_t* __restrict__ planes, int64_t plane_stride, int32_
         ra.wsde += __shfl_xor_sync(0xFFFFFFFFu, ra.wsde, o);
     }
     if (cg == 0) {
-        const int64_t o = (int64_t)t * kBlk + s;
+        const int64_t o = (int64_t)blockIdx.x * kBlk + s;
         args.part.add[o] = ra.add;
         args.part.dom[o] = ra.dom;
         args.part.wsa[o] = ra.wsa;
@@ -105,7 +106,7 @@ band_simt_kernel(const int8_t* __restrict__ planes, int64_t plane_stride, int32_
 void launch_band_simt(const int8_t* planes, int64_t plane_stride, int32_t npad, const BandArgs& args,
                       cudaStream_t st) {
     if (args.n_tiles <= 0) return;
-    band_simt_kernel<<<args.n_tiles, 256, 0, st>>>(planes, plane_stride, npad, args);
+    band_simt_kernel<<<2 * args.n_tiles, 256, 0, st>>>(planes, plane_stride, npad, args);
     CUDA_CHECK(cudaGetLastError());
 }
 
@@ -128,8 +129,9 @@ finalize_kernel(const FinalizeArgs a) {
     }
     double add = 1.0, dom = 0.0;                                     // ldscalc.h:27-28
     int wsa = 0, wsd = 0, wsde = 0;
-    for (int t = a.tile_begin[b]; t < a.tile_begin[b + 1]; ++t) {
-        const int64_t p = (int64_t)t * kBlk + r;
+    // i-block b of the chunk is rank b % 2 of supertile row b / 2
+    for (int t = a.tile_begin[b >> 1]; t < a.tile_begin[(b >> 1) + 1]; ++t) {
+        const int64_t p = ((int64_t)t * 2 + (b & 1)) * kBlk + r;
         add += a.part.add[p];
         dom += a.part.dom[p];
         wsa += a.part.wsa[p];

@@ -3,15 +3,22 @@
 // Replaces the pair loop of calculate() (reference ldscalc.h:34-47) and the two
 // arma::dot calls per ordered pair in Math::r2_adjusted (tools.h:87-92).
 //
-// One CTA per SM, persistent over a host-built list of 64x64 SNP-pair tiles that covers
-// only the band |pos_j - pos_i| <= window.  Per tile, a full-K (= organisms) int8 GEMM
-//     D[128 x 192] (int32, TMEM) = A[128 x K] * B[192 x K]^T
-//   A rows: per group of 16 i-SNPs, 16 rows of g (dosage 0/1/2) then 16 rows of m (missing)
-//   B rows: 64 rows of m_j, 64 of h_j (het), 64 of a_j (hom-second)
-// gives the six exact cross-counts of every pair.  Warp roles:
-//   warp 0   TMA producer  (cp.async.bulk.tensor, 128B-swizzled K-major tiles, 5-stage ring)
-//   warp 1   MMA issuer    (tcgen05.mma.kind::i8, M=128 N=192 K=32; 2 TMEM accumulators)
-//   warps 2-5 epilogue     (tcgen05.ld -> FP64 correlations -> r2adj -> row sums)
+// Persistent CTA PAIRS (cluster of 2 = the two SMs of a TPC, tcgen05 cta_group::2), one pair per
+// TPC, walking a host-built list of supertiles that covers only the band |pos_j - pos_i| <= window.
+// A supertile is two vertically adjacent 64-SNP i-blocks (one per CTA) x one 64-SNP j-block; per
+// supertile one full-K (= organisms) int8 GEMM
+//     D[256 x 192] (int32, TMEM: 128 lanes x 192 columns in each CTA) = A[256 x K] * B[192 x K]^T
+//   A rows (per CTA, 128): per group of 16 i-SNPs, 16 rows of g (dosage 0/1/2) then 16 rows of m
+//   B rows (192, half staged by each CTA): for j-SNPs 32r..32r+31 of the block, 32 rows of m_j,
+//                                          32 of h_j (het), 32 of a_j (hom-second)      (r = CTA rank)
+// gives the six exact cross-counts of every pair.  Sharing B between the two SMs cuts the operand
+// bytes each SM pulls from L2 and reads from shared memory from 40 KB to 28 KB per 128-organism
+// K-step, which is what bounded the one-CTA version (ncu: tensor pipe 46 %, L2 65 %).  Warp roles:
+//   warp 0   TMA producer  (cp.async.bulk.tensor.cta_group::2, 128B-swizzled K-major tiles, 8 stages;
+//                           both CTAs' bytes complete on the leader CTA's mbarrier)
+//   warp 1   MMA issuer    (leader CTA only: tcgen05.mma.cta_group::2.kind::i8, M=256 N=192 K=32;
+//                           commits multicast to both CTAs; 2 TMEM accumulators)
+//   warps 2-5 epilogue     (tcgen05.ld -> FP64 correlations -> r2adj -> row sums), each CTA its own rows
 // The accumulators are double-buffered in TMEM so the FP64 epilogue of tile t overlaps
 // the MMAs of tile t+1.
 #include "common.cuh"
@@ -23,15 +30,18 @@ namespace nldsc {
 
 namespace {
 
-constexpr int kStages = 5;
+constexpr int kStages = 8;
 constexpr int kKStep = 128;                 // organisms (bytes) per pipeline stage
-constexpr int kARows = 128, kBRows = 192;
+constexpr int kARows = 128;                 // per CTA: 64 i-SNPs x {g, m}
+constexpr int kBRows = 192;                 // per pair: 64 j-SNPs x {m, h, a}; each CTA stages half
+constexpr int kBHalf = kBRows / 2;          // 96 rows = 32 j-SNPs x {m, h, a}
 constexpr int kABytes = kARows * kKStep;    // 16 KB
-constexpr int kBBytes = kBRows * kKStep;    // 24 KB
-constexpr int kStageBytes = kABytes + kBBytes;
+constexpr int kBBytes = kBHalf * kKStep;    // 12 KB
+constexpr int kStageBytes = kABytes + kBBytes;   // 28 KB per CTA per stage
 constexpr int kTmemCols = 512;              // 2 accumulators of 192 columns at 0 and 256
 constexpr int kThreads = 192;
 constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+constexpr uint32_t kPeerMask = 0xFEFFFFFFu; // shared::cluster address of the same offset in the pair's even CTA
 
 // ---- PTX wrappers -------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -43,9 +53,6 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
@@ -62,28 +69,46 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         if (spins > (1u << 26)) __trap();
     }
 }
+// remote arrive on the leader (even) CTA's copy of `bar`
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerMask) : "memory");
+}
+// Executed by both CTAs of the pair; the bytes land in the issuing CTA's shared memory and
+// complete_tx on the LEADER CTA's barrier (peer bit cleared), which the MMA issuer waits on.
 __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar,
                                             int32_t c0, int32_t c1, int32_t c2) {
     asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes"
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
         " [%0], [%1, {%3, %4, %5}], [%2];"
-        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)),
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & kPeerMask),
           "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint64_t* bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
-                 : "memory");
+// arrive on the same barrier offset in BOTH CTAs once all prior MMAs of the pair have retired
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {
+    asm volatile(
+        "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+        ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3))
+        : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem]^T, int8 x int8 -> int32
+// D[tmem, both CTAs] (+)= A[smem, 128 rows per CTA] * B[smem, 96 rows per CTA]^T, int8 x int8 -> int32
 __device__ __forceinline__ void tc_mma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                           uint32_t accumulate) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
@@ -96,8 +121,8 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
     d |= 2ull << 61;                                           // SWIZZLE_128B
     return d;
 }
-// instruction descriptor, kind::i8: D = s32, A/B = u8, both K-major, M = 128, N = 192
-constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (0u << 10) | ((kBRows >> 3) << 17) | ((kARows >> 4) << 24);
+// instruction descriptor, kind::i8: D = s32, A/B = u8, both K-major, M = 256 (pair), N = 192
+constexpr uint32_t kIdesc = (2u << 4) | (0u << 7) | (0u << 10) | ((kBRows >> 3) << 17) | (((2 * kARows) >> 4) << 24);
 
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, int32_t (&v)[16]) {
     asm volatile(
@@ -111,67 +136,78 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 
 }  // namespace
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                const BandArgs args) {
     extern __shared__ uint8_t smem_raw[];
+    // identical offsets in both CTAs of the pair: the MMA addresses the peer's operands and the
+    // multicast commits address the peer's barriers by the leader's own offsets
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);
-    uint64_t* empty = full + kStages;
-    uint64_t* tfull = empty + kStages;
-    uint64_t* tempty = tfull + 2;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + kStages * kStageBytes);   // used in the leader CTA only
+    uint64_t* empty = full + kStages;          // one per CTA
+    uint64_t* tfull = empty + kStages;         // one per CTA
+    uint64_t* tempty = tfull + 2;              // used in the leader CTA only
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();               // 0 = leader (issues the MMAs)
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
         for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 8); }   // 4 epilogue warps x 2 CTAs
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                      "r"((uint32_t)kTmemCols)
                      : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
     }
     tc_fence_before();
-    __syncthreads();
+    cluster_sync_all();                        // peer barriers initialised before any remote arrive / complete_tx
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer (both CTAs: own A block, own half of B) =====
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < args.n_tiles; t += gridDim.x) {
+            for (int t = pair; t < args.n_tiles; t += n_pairs) {
                 const Tile tl = args.tiles[t];
+                const int32_t a_row = tl.a_row[rank];
+                const int32_t b_row = tl.b_row + 32 * static_cast<int32_t>(rank);
                 for (int k = 0; k < args.k_steps; ++k) {
                     mbar_wait(&empty[stage], phase ^ 1);
-                    mbar_expect_tx(&full[stage], kStageBytes);
+                    if (args.probe == 1) {           // tensor-pipe probe: operands are whatever the stage holds
+                        if (rank == 0) mbar_expect_tx(&full[stage], 0);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
+                    if (rank == 0) mbar_expect_tx(&full[stage], 2 * kStageBytes);    // both CTAs' bytes
                     uint8_t* sa = smem + stage * kStageBytes;
                     uint8_t* sb = sa + kABytes;
 #pragma unroll
                     for (int u = 0; u < 4; ++u)   // 16 SNPs x {g, m} = 32 rows per box
-                        tma_load_3d(sa + u * 4096, &map_a, &full[stage], k * kKStep, tl.a_row + 16 * u, kPlaneG);
-                    tma_load_3d(sb, &map_b, &full[stage], k * kKStep, tl.b_row, kPlaneM);   // 64 SNPs x {m, h, a}
+                        tma_load_3d(sa + u * 4096, &map_a, &full[stage], k * kKStep, a_row + 16 * u, kPlaneG);
+                    tma_load_3d(sb, &map_b, &full[stage], k * kKStep, b_row, kPlaneM);   // 32 SNPs x {m, h, a}
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
             }
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ===== MMA issuer =====
-        if (lane == 0) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (rank == 0 && lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
             int n = 0;
-            for (int t = blockIdx.x; t < args.n_tiles; t += gridDim.x, ++n) {
+            for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
                 const int buf = n & 1;
-                mbar_wait(&tempty[buf], ((n >> 1) & 1) ^ 1);       // epilogue drained this accumulator
+                mbar_wait(&tempty[buf], ((n >> 1) & 1) ^ 1);       // both CTAs' epilogues drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * 256;
                 for (int k = 0; k < args.k_steps; ++k) {
@@ -180,39 +216,44 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     const uint32_t sa = smem_u32(smem + stage * kStageBytes);
                     const uint64_t a_desc = make_smem_desc(sa);
                     const uint64_t b_desc = make_smem_desc(sa + kABytes);
+                    if (args.probe != 2) {
 #pragma unroll
-                    for (int kk = 0; kk < kKStep / 32; ++kk)       // +32 B along K inside the swizzle atom
-                        tc_mma_i8(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (k | kk) != 0);
-                    tc_commit(&empty[stage]);                       // smem slot free once these MMAs retire
+                        for (int kk = 0; kk < kKStep / 32; ++kk)   // +32 B along K inside the swizzle atom
+                            tc_mma_i8(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (k | kk) != 0);
+                    }
+                    tc_commit_pair(&empty[stage]);                  // both CTAs' smem slots free once these MMAs retire
                     if (++stage == kStages) { stage = 0; phase ^= 1; }
                 }
-                tc_commit(&tfull[buf]);                             // accumulator complete
+                tc_commit_pair(&tfull[buf]);                        // accumulator complete, in both CTAs
             }
         }
         __syncwarp();
     } else {
-        // ===== epilogue: 4 warps, warp q owns TMEM lanes 32q..32q+31 =====
+        // ===== epilogue: 4 warps per CTA, warp q owns TMEM lanes 32q..32q+31 of its CTA's i-block =====
         const int q = warp & 3;
         const bool is_g = lane < 16;                 // lanes 0-15 hold g rows, 16-31 the m rows of the same SNPs
         const int s = 16 * q + (lane & 15);          // SNP within the i-block
         int n = 0;
-        for (int t = blockIdx.x; t < args.n_tiles; t += gridDim.x, ++n) {
+        for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
             const int buf = n & 1;
             const Tile tl = args.tiles[t];
-            const RowCtx row = load_row_ctx(args, tl.i0 + s);
+            const int32_t i0 = tl.i0[rank];
+            const RowCtx row = load_row_ctx(args, i0 + s);
             RowAcc acc;
             mbar_wait(&tfull[buf], (n >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(32 * q) << 16);
 #pragma unroll 1
             for (int c = 0; c < 4; ++c) {            // 16 j-SNPs per pass
+                // columns: [m h a] of j-SNPs 0-31 (staged by CTA 0), then [m h a] of j-SNPs 32-63 (CTA 1)
+                const uint32_t col = 96 * (c >> 1) + 16 * (c & 1);
                 int32_t vm[16], vh[16], va[16];
-                tmem_ld16(taddr + 16 * c, vm);
-                tmem_ld16(taddr + 64 + 16 * c, vh);
-                tmem_ld16(taddr + 128 + 16 * c, va);
+                tmem_ld16(taddr + col, vm);
+                tmem_ld16(taddr + col + 32, vh);
+                tmem_ld16(taddr + col + 64, va);
                 tmem_ld_wait();
                 if (args.dump != nullptr) {
-                    int32_t* drow = args.dump + (static_cast<int64_t>(t) * kARows + 32 * q + lane) * kBRows;
+                    int32_t* drow = args.dump + ((static_cast<int64_t>(t) * 2 + rank) * kARows + 32 * q + lane) * kBRows;
 #pragma unroll
                     for (int e = 0; e < 16; ++e) {
                         drow[16 * c + e] = vm[e];
@@ -236,10 +277,10 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     pair_eval(args, row, tl.j0 + jl, Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
                 }
             }
-            // accumulator fully read: hand it back to the MMA warp
+            // accumulator fully read: hand it back to the leader's MMA warp
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tempty[buf]);
+            if (lane == 0) mbar_arrive_leader(&tempty[buf]);
             // even-j and odd-j halves of the row
             acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
             acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);
@@ -247,7 +288,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
             acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
             if (is_g) {
-                const int64_t o = static_cast<int64_t>(t) * kBlk + s;
+                const int64_t o = (static_cast<int64_t>(t) * 2 + rank) * kBlk + s;
                 args.part.add[o] = acc.add;
                 args.part.dom[o] = acc.dom;
                 args.part.wsa[o] = acc.wsa;
@@ -257,11 +298,12 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
     }
 
+    // nobody leaves while the peer may still read this CTA's operands or signal its barriers
     tc_fence_before();
-    __syncthreads();
+    cluster_sync_all();
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
                      : "memory");
     }
 }
@@ -269,7 +311,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 // ---- host side: TMA descriptors + launch ------------------------------------------------
 struct BandMaps {
     CUtensorMap a;   // box {128 B, 16 rows, 2 planes}
-    CUtensorMap b;   // box {128 B, 64 rows, 3 planes}
+    CUtensorMap b;   // box {128 B, 32 rows, 3 planes}
 };
 
 namespace {
@@ -311,7 +353,7 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
     BandMaps* m = new BandMaps;
     try {
         encode(&m->a, planes, plane_rows, npad, 16, 2);
-        encode(&m->b, planes, plane_rows, npad, 64, 3);
+        encode(&m->b, planes, plane_rows, npad, 32, 3);
     } catch (...) {
         delete m;
         throw;
@@ -324,8 +366,8 @@ void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cu
     if (args.n_tiles <= 0) return;
     // per device (several GPUs may be driven from one process), so not cached in a static
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    const int grid = args.n_tiles < sm_count ? args.n_tiles : sm_count;
-    band_tc_kernel<<<grid, kThreads, kSmemBytes, st>>>(maps->a, maps->b, args);
+    const int pairs = args.n_tiles < sm_count / 2 ? args.n_tiles : sm_count / 2;     // one CTA pair per TPC
+    band_tc_kernel<<<2 * pairs, kThreads, kSmemBytes, st>>>(maps->a, maps->b, args);
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -33,15 +33,17 @@ struct __align__(16) SnpCoef {
 constexpr uint8_t kFlagKeep = 1;   // passed the MAF filter (encoder.h:120-122)
 constexpr uint8_t kFlagDom = 2;    // residual std > std_thr (tools.h:31-33, ldscalc.h:40)
 
-// One 64x64 SNP-pair tile of the band.
+// One supertile of the band: two vertically adjacent 64-SNP i-blocks x one 64-SNP j-block, scored
+// by a CTA pair (cluster rank r owns i-block r; both share the j-block's operand).
+constexpr int32_t kDeadBlock = 0x3FFFFFC0;   // i0 of a missing second i-block: scores nothing
 struct Tile {
-    int32_t a_row;   // row of the i-block inside the plane ring
-    int32_t b_row;   // row of the j-block inside the plane ring
-    int32_t i0;      // first SNP (shard-local index) of the i-block
-    int32_t j0;      // first SNP (shard-local index) of the j-block
+    int32_t a_row[2];  // rows of the two i-blocks inside the plane ring
+    int32_t i0[2];     // first SNP (shard-local index) of each i-block, or kDeadBlock
+    int32_t b_row;     // row of the j-block inside the plane ring
+    int32_t j0;        // first SNP (shard-local index) of the j-block
 };
 
-// Per-row partial sums a tile contributes (SoA, index = tile * 64 + row).
+// Per-row partial sums a supertile contributes (SoA, index = (tile * 2 + rank) * 64 + row).
 struct Partials {
     double* add;     // sum of r2adj(A_i, A_j)
     double* dom;     // sum of r2adj(A_i, D_j) over dominance-usable j
@@ -64,7 +66,8 @@ struct BandArgs {
     double adj_c;               // (n - 1) / (n - 2)
     double rsq_thr;
     Partials part;
-    int32_t* dump;              // optional raw accumulators [tile][128][192] (parity hook)
+    int32_t* dump;              // optional raw accumulators [tile][rank][128][192] (parity hook)
+    int32_t probe;              // measurement hook: 0 = normal, 1 = MMAs without TMA loads, 2 = TMA loads without MMAs
 };
 
 // ---- error plumbing ----------------------------------------------------------------
@@ -91,6 +94,7 @@ void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n
 void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
                    int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
                    int32_t dst_row0, cudaStream_t st);
+void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st);
 void launch_zero_rows(int8_t* planes, int64_t plane_stride, int32_t npad, int32_t row0,
                       int32_t n_rows, cudaStream_t st);
 
@@ -103,7 +107,7 @@ void launch_band_simt(const int8_t* planes, int64_t plane_stride, int32_t npad,
                       const BandArgs& args, cudaStream_t st);
 
 struct FinalizeArgs {
-    const int32_t* tile_begin;  // [n_iblocks + 1] tile range of every owned i-block
+    const int32_t* tile_begin;  // [ceil(n_iblocks / 2) + 1] supertile range of every owned i-block pair
     int32_t iblock0;            // shard-local block index of the first owned block in this chunk
     int32_t n_iblocks;
     int32_t own_begin;          // shard-local first owned row

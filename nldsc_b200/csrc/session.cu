@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <cerrno>
+#include <chrono>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -30,15 +31,192 @@ void compute_windows(const double* pos, int32_t n_snp, double wind, std::vector<
                      std::vector<int32_t>& hi) {
     lo.resize(n_snp);
     hi.resize(n_snp);
-    int32_t l = 0, r = 0;
-    for (int32_t i = 0; i < n_snp; ++i) {
-        // SNPFilter::filter: std::abs(positions[snd] - positions[fst]) <= ld_wind  (tools.h:43-44)
-        while (l < i && !(std::abs(pos[l] - pos[i]) <= wind)) ++l;
-        if (r < i) r = i;
-        while (r + 1 < n_snp && std::abs(pos[r + 1] - pos[i]) <= wind) ++r;
-        lo[i] = l;
-        hi[i] = r;
+    if (n_snp <= 0) return;
+    // SNPFilter::filter: std::abs(positions[snd] - positions[fst]) <= ld_wind  (tools.h:43-44).  For sorted
+    // positions the predicate is monotone in either argument (IEEE subtraction is monotone and
+    // antisymmetric), so lo[] comes from one two-pointer sweep and hi[] is its inverse:
+    // hi[i] = #{j : lo[j] <= i} - 1.  The sweep is split over a few threads (it sits on the critical
+    // path of every call: nothing can be scored before the band plan exists).
+    auto inside = [&](int32_t l, int32_t i) { return std::abs(pos[l] - pos[i]) <= wind; };
+    auto sweep = [&](int32_t a, int32_t b) {
+        // first l <= a inside the window of a, by bisection on the monotone predicate
+        int32_t x = 0, y = a;
+        while (x < y) {
+            const int32_t m = x + (y - x) / 2;
+            if (inside(m, a)) y = m; else x = m + 1;
+        }
+        int32_t l = x;
+        for (int32_t i = a; i < b; ++i) {
+            while (l < i && !inside(l, i)) ++l;
+            lo[i] = l;
+        }
+    };
+    const int hw = static_cast<int>(std::thread::hardware_concurrency());
+    const int nt = n_snp < 32768 ? 1 : std::max(1, std::min(8, hw));
+    if (nt == 1) {
+        sweep(0, n_snp);
+    } else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nt; ++t) {
+            const int32_t a = static_cast<int32_t>(static_cast<int64_t>(n_snp) * t / nt);
+            const int32_t b = static_cast<int32_t>(static_cast<int64_t>(n_snp) * (t + 1) / nt);
+            th.emplace_back(sweep, a, b);
+        }
+        for (auto& t : th) t.join();
     }
+    std::vector<int32_t> cnt(static_cast<size_t>(n_snp) + 1, 0);
+    for (int32_t j = 0; j < n_snp; ++j) ++cnt[lo[j]];
+    int32_t run = 0;
+    for (int32_t i = 0; i < n_snp; ++i) {
+        run += cnt[i];
+        hi[i] = run - 1;
+    }
+}
+
+// ---- device workspace cache ------------------------------------------------------------------
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_arena_mu;
+Arena* g_arena[kMaxDevices] = {nullptr};
+bool g_arena_busy[kMaxDevices] = {false};
+}  // namespace
+
+void* Arena::alloc(size_t bytes) {
+    bytes = (bytes + 511) & ~size_t(511);
+    Block* best = nullptr;          // best fit: small buffers must not nibble at the block the plane ring needs
+    for (Block& b : blocks)
+        if (b.size - b.used >= bytes && (!best || b.size - b.used < best->size - best->used)) best = &b;
+    if (best) {
+        void* p = best->base + best->used;
+        best->used += bytes;
+        return p;
+    }
+    // small requests share 64 MB blocks; large ones (packed rows, plane ring) get their own
+    const size_t sz = std::max<size_t>(bytes, size_t(64) << 20);
+    void* p = nullptr;
+    CUDA_CHECK(cudaMalloc(&p, sz));
+    blocks.push_back(Block{static_cast<char*>(p), sz, bytes});
+    return p;
+}
+
+size_t Arena::capacity() const {
+    size_t c = 0;
+    for (const Block& b : blocks) c += b.size;
+    return c;
+}
+
+Arena* arena_acquire(int device) {
+    std::lock_guard<std::mutex> g(g_arena_mu);
+    if (device >= 0 && device < kMaxDevices && !g_arena_busy[device]) {
+        if (!g_arena[device]) {
+            g_arena[device] = new Arena;
+            g_arena[device]->device = device;
+            g_arena[device]->cached = true;
+        }
+        g_arena_busy[device] = true;
+        return g_arena[device];
+    }
+    Arena* a = new Arena;
+    a->device = device;
+    return a;
+}
+
+static void arena_free_blocks(Arena* a) {
+    for (Arena::Block& b : a->blocks) cudaFree(b.base);
+    a->blocks.clear();
+}
+
+void arena_release(Arena* a) {
+    if (!a) return;
+    if (!a->cached) {
+        arena_free_blocks(a);
+        delete a;
+        return;
+    }
+    // A workload of a different shape leaves blocks that no longer fit: keep at most the blocks in use
+    // by the last session plus nothing else (blocks the session never touched are dropped).
+    std::vector<Arena::Block> keep;
+    for (Arena::Block& b : a->blocks) {
+        if (b.used) { b.used = 0; keep.push_back(b); }
+        else cudaFree(b.base);
+    }
+    a->blocks.swap(keep);
+    std::lock_guard<std::mutex> g(g_arena_mu);
+    g_arena_busy[a->device] = false;
+}
+
+size_t arena_cached_bytes(int device) {
+    std::lock_guard<std::mutex> g(g_arena_mu);
+    if (device < 0 || device >= kMaxDevices || !g_arena[device] || g_arena_busy[device]) return 0;
+    return g_arena[device]->capacity();
+}
+
+void arena_trim(int device) {
+    std::lock_guard<std::mutex> g(g_arena_mu);
+    for (int d = 0; d < kMaxDevices; ++d) {
+        if ((device >= 0 && d != device) || !g_arena[d] || g_arena_busy[d]) continue;
+        cudaSetDevice(d);
+        arena_free_blocks(g_arena[d]);
+    }
+}
+
+// ---- pinned staging cache ---------------------------------------------------------------------
+namespace {
+HostStage* g_stage[kMaxDevices] = {nullptr};
+bool g_stage_busy[kMaxDevices] = {false};
+
+HostStage* host_stage_new(int device) {
+    HostStage* h = new HostStage;
+    h->device = device;
+    h->bytes = size_t(HostStage::kSlots) * (size_t(16) << 20);
+    if (cudaHostAlloc(&h->base, h->bytes, cudaHostAllocDefault) != cudaSuccess) {
+        delete h;
+        throw CudaError("cudaHostAlloc of the .bed staging ring failed");
+    }
+    for (auto& e : h->ev) {
+        CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    return h;
+}
+}  // namespace
+
+HostStage* host_stage_acquire(int device) {
+    {
+        std::lock_guard<std::mutex> g(g_arena_mu);
+        if (device >= 0 && device < kMaxDevices && !g_stage_busy[device]) {
+            g_stage_busy[device] = true;
+            if (g_stage[device]) return g_stage[device];
+        } else {
+            device = -1 - device;       // private stage
+        }
+    }
+    if (device >= 0) {
+        HostStage* h = nullptr;
+        try {
+            h = host_stage_new(device);
+        } catch (...) {
+            std::lock_guard<std::mutex> g(g_arena_mu);
+            g_stage_busy[device] = false;
+            throw;
+        }
+        h->cached = true;
+        std::lock_guard<std::mutex> g(g_arena_mu);
+        g_stage[device] = h;
+        return h;
+    }
+    return host_stage_new(-1 - device);
+}
+
+void host_stage_release(HostStage* h) {
+    if (!h) return;
+    if (h->cached) {
+        std::lock_guard<std::mutex> g(g_arena_mu);
+        g_stage_busy[h->device] = false;
+        return;
+    }
+    for (auto& e : h->ev) cudaEventDestroy(e);
+    cudaFreeHost(h->base);
+    delete h;
 }
 
 namespace {
@@ -78,16 +256,32 @@ int usable_devices() {
     return n;
 }
 
+// compute capability and SM count per device, queried once (cudaGetDeviceProperties costs milliseconds)
+struct DevInfo { int major = -1, minor = 0, sms = 0; };
+DevInfo& dev_info(int device) {
+    static DevInfo info[64];
+    static std::mutex mu;
+    std::lock_guard<std::mutex> g(mu);
+    DevInfo& d = info[device & 63];
+    if (d.major < 0) {
+        CUDA_CHECK(cudaDeviceGetAttribute(&d.major, cudaDevAttrComputeCapabilityMajor, device));
+        CUDA_CHECK(cudaDeviceGetAttribute(&d.minor, cudaDevAttrComputeCapabilityMinor, device));
+        CUDA_CHECK(cudaDeviceGetAttribute(&d.sms, cudaDevAttrMultiProcessorCount, device));
+    }
+    return d;
+}
+
 void require_sm100(int device) {
-    cudaDeviceProp p;
-    CUDA_CHECK(cudaGetDeviceProperties(&p, device));
-    if (p.major != 10) {
+    const DevInfo& d = dev_info(device);
+    if (d.major != 10) {
         char buf[160];
-        snprintf(buf, sizeof(buf), "device %d is sm_%d%d; this library is built for sm_100a only", device, p.major,
-                 p.minor);
+        snprintf(buf, sizeof(buf), "device %d is sm_%d%d; this library is built for sm_100a only", device, d.major,
+                 d.minor);
         throw CudaError(buf);
     }
 }
+
+int device_sm_count(int device) { return dev_info(device).sms; }
 
 void validate_params(const nldsc_ld_params* p) {
     if (!p) throw InvalidArgument("params is null");
@@ -103,10 +297,15 @@ void validate_params(const nldsc_ld_params* p) {
 }
 
 template <class T>
-T* dmalloc(size_t n) {
+T* dmalloc(size_t n) {          // parity / measurement hooks only; sessions allocate from their Arena
     void* p = nullptr;
     CUDA_CHECK(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
     return static_cast<T*>(p);
+}
+
+template <class T>
+T* amalloc(Arena* a, size_t n) {
+    return static_cast<T*>(a->alloc(std::max<size_t>(n, 1) * sizeof(T)));
 }
 
 int32_t floor64(int32_t x) { return x & ~63; }
@@ -130,6 +329,18 @@ struct SpanScope {
     ~SpanScope() { cudaEventRecord(s->spans[idx].b, st); }
 };
 
+// NLDSC_TRACE=1: host-side phase times on stderr
+struct Tracer {
+    bool on = getenv("NLDSC_TRACE") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void lap(const char* what) {
+        if (!on) return;
+        const auto n = std::chrono::steady_clock::now();
+        fprintf(stderr, "[nldsc_ld]   %-18s %.3f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+        t = n;
+    }
+};
+
 size_t env_size(const char* name, size_t dflt) {
     const char* v = getenv(name);
     if (!v || !*v) return dflt;
@@ -146,15 +357,16 @@ size_t env_size(const char* name, size_t dflt) {
 static void session_free(nldsc_ld_session* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    cudaFree(s->d_packed); cudaFree(s->d_counts); cudaFree(s->d_coef); cudaFree(s->d_flags);
-    cudaFree(s->d_maf); cudaFree(s->d_rstd); cudaFree(s->d_win_lo); cudaFree(s->d_win_hi);
-    cudaFree(s->d_planes); cudaFree(s->d_tiles); cudaFree(s->d_tile_begin);
-    cudaFree(s->part.add); cudaFree(s->part.dom); cudaFree(s->part.wsa); cudaFree(s->part.wsd);
-    cudaFree(s->part.wsde);
-    cudaFree(s->d_l2); cudaFree(s->d_l2d); cudaFree(s->d_wsa); cudaFree(s->d_wsd); cudaFree(s->d_wsde);
+    if (s->reader.joinable()) s->reader.join();
+    // every buffer lives in the arena; make sure nothing queued still touches it before it is reused
+    if (s->own_stream) cudaStreamSynchronize(s->own_stream);
+    if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);
+    arena_release(s->arena);
+    host_stage_release(s->stage);
+    if (s->ev_planned) cudaEventDestroy(s->ev_planned);
     if (s->maps) band_maps_destroy(s->maps);
     for (auto& sp : s->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
-    for (auto e : s->ev_uploaded) cudaEventDestroy(e);
+    for (auto e : s->ev_piece) cudaEventDestroy(e);
     if (s->ev_run0) cudaEventDestroy(s->ev_run0);
     if (s->ev_run1) cudaEventDestroy(s->ev_run1);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
@@ -162,10 +374,11 @@ static void session_free(nldsc_ld_session* s) {
     delete s;
 }
 
-static nldsc_ld_session* session_build(int device, const nldsc_ld_params* p, int32_t row_begin, int32_t row_end,
-                                       const std::vector<int32_t>& lo, const std::vector<int32_t>& hi) {
-    if (row_begin < 0 || row_end > p->n_snp || row_begin >= row_end)
-        throw InvalidArgument("shard row range is empty or outside [0, n_snp)");
+// Stage 1 of a session: device, geometry, the packed-row buffer and the copy machinery -- everything
+// the H2D upload needs, so the upload can start before the (host-side) band plan is built.
+static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int32_t load_begin, int32_t load_end) {
+    if (load_begin < 0 || load_end > p->n_snp || load_begin >= load_end || (load_begin % kBlk) != 0)
+        throw InvalidArgument("shard load range is empty, unaligned or outside [0, n_snp)");
     const int ndev = usable_devices();
     if (device < 0 || device >= ndev) throw CudaError("CUDA device index out of range");
     CUDA_CHECK(cudaSetDevice(device));
@@ -174,11 +387,10 @@ static nldsc_ld_session* session_build(int device, const nldsc_ld_params* p, int
     std::unique_ptr<nldsc_ld_session, void (*)(nldsc_ld_session*)> sp(new nldsc_ld_session, session_free);
     nldsc_ld_session* s = sp.get();
     s->device = device;
-    CUDA_CHECK(cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device));
+    s->arena = arena_acquire(device);
+    s->sm_count = device_sm_count(device);
     s->n_org = p->n_org;
     s->n_snp = p->n_snp;
-    s->row_begin = row_begin;
-    s->row_end = row_end;
     s->maf_thr = p->maf;
     s->std_thr = p->std_thr;
     s->rsq_thr = p->rsq_thr;
@@ -186,17 +398,124 @@ static nldsc_ld_session* session_build(int device, const nldsc_ld_params* p, int
     s->npad = static_cast<int32_t>(((static_cast<int64_t>(p->n_org) + kKAlign - 1) / kKAlign) * kKAlign);
     const char* band = getenv("NLDSC_BAND");
     s->use_simt = band && strcmp(band, "simt") == 0;
+    s->load_begin = load_begin;
+    s->load_end = load_end;
+    s->n_load = load_end - load_begin;
 
-    // ---- rows this shard needs: owned range widened by the window halo, 64-aligned on the left
-    s->load_begin = floor64(lo[row_begin]);
-    s->load_end = hi[row_end - 1] + 1;
-    s->n_load = s->load_end - s->load_begin;
+    s->d_packed = amalloc<uint8_t>(s->arena, static_cast<size_t>(s->n_load) * s->bps + 16);
+    CUDA_CHECK(cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking));
+    CUDA_CHECK(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    // the 16 bytes of slack the word-wise kernels may read past the last row
+    CUDA_CHECK(cudaMemsetAsync(s->d_packed + static_cast<size_t>(s->n_load) * s->bps, 0, 16, s->copy_stream));
+    // upload granularity: ~8 MB pieces, a whole number of 64-row blocks each
+    const int64_t rows8 = (int64_t(8) << 20) / s->bps;
+    s->piece_rows = static_cast<int32_t>(std::max<int64_t>(kBlk, rows8 / kBlk * kBlk));
+    s->ev_piece.resize((s->n_load + s->piece_rows - 1) / s->piece_rows);
+    for (auto& e : s->ev_piece) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CUDA_CHECK(cudaEventCreate(&s->ev_run0));
+    CUDA_CHECK(cudaEventCreate(&s->ev_run1));
+    return sp.release();
+}
+
+static void note_pieces_issued(nldsc_ld_session* s, int32_t n, const char* error = nullptr) {
+    {
+        std::lock_guard<std::mutex> g(s->up_mu);
+        s->pieces_issued = n;
+        if (error) s->up_error = error;
+    }
+    s->up_cv.notify_all();
+}
+
+// H2D of the packed rows from host memory, one copy + event per piece so run() can start on the
+// first chunk while the rest of the shard is still crossing PCIe.  host_rows points at row load_begin.
+static void session_upload_mem(nldsc_ld_session* s, const uint8_t* host_rows, cudaStream_t st) {
+    CUDA_CHECK(cudaSetDevice(s->device));
+    cudaStream_t cs = st ? st : s->copy_stream;
+    const int32_t n_pieces = static_cast<int32_t>(s->ev_piece.size());
+    for (int32_t k = 0; k < n_pieces; ++k) {
+        const int32_t r0 = k * s->piece_rows, r1 = std::min(s->n_load, r0 + s->piece_rows);
+        const size_t off = static_cast<size_t>(r0) * s->bps, len = static_cast<size_t>(r1 - r0) * s->bps;
+        CUDA_CHECK(cudaMemcpyAsync(s->d_packed + off, host_rows + off, len, cudaMemcpyHostToDevice, cs));
+        CUDA_CHECK(cudaEventRecord(s->ev_piece[k], cs));
+    }
+    note_pieces_issued(s, n_pieces);
+    s->upload_started = true;
+}
+
+// H2D straight from the .bed: a reader thread preads piece after piece into a small ring of pinned
+// slots and queues the copy of each; the caller's thread meanwhile plans and enqueues the kernels,
+// which wait (on the device) for the piece events.  Replaces the byte-at-a-time ifstream of
+// BedStreamReader (reference stream.h:43-69) -- SURVEY section 8(f)-1.
+static void session_upload_file(nldsc_ld_session* s, int fd) {
+    CUDA_CHECK(cudaSetDevice(s->device));
+    s->stage = host_stage_acquire(s->device);
+    s->upload_started = true;
+    s->reader = std::thread([s, fd] {
+        const int32_t n_pieces = static_cast<int32_t>(s->ev_piece.size());
+        int32_t done = 0;
+        try {
+            CUDA_CHECK(cudaSetDevice(s->device));
+            const size_t slot_bytes = s->stage->bytes / HostStage::kSlots;
+            int slot = 0;
+            for (int32_t k = 0; k < n_pieces; ++k) {
+                const int32_t r0 = k * s->piece_rows, r1 = std::min(s->n_load, r0 + s->piece_rows);
+                size_t off = static_cast<size_t>(r0) * s->bps;
+                const size_t end = static_cast<size_t>(r1) * s->bps;
+                while (off < end) {                      // a piece may span several slots (very long rows)
+                    const size_t len = std::min(slot_bytes, end - off);
+                    char* buf = static_cast<char*>(s->stage->base) + slot * slot_bytes;
+                    CUDA_CHECK(cudaEventSynchronize(s->stage->ev[slot]));       // slot's previous copy has landed
+                    size_t got = 0;
+                    while (got < len) {
+                        const ssize_t r = pread(fd, buf + got, len - got,
+                                                3 + static_cast<off_t>(s->load_begin) * s->bps + static_cast<off_t>(off + got));
+                        if (r <= 0) throw CudaError("short read on .bed file");
+                        got += static_cast<size_t>(r);
+                    }
+                    CUDA_CHECK(cudaMemcpyAsync(s->d_packed + off, buf, len, cudaMemcpyHostToDevice, s->copy_stream));
+                    CUDA_CHECK(cudaEventRecord(s->stage->ev[slot], s->copy_stream));
+                    slot = (slot + 1) % HostStage::kSlots;
+                    off += len;
+                }
+                CUDA_CHECK(cudaEventRecord(s->ev_piece[k], s->copy_stream));
+                note_pieces_issued(s, ++done);
+            }
+        } catch (const std::exception& e) {
+            note_pieces_issued(s, n_pieces, e.what());   // unblock run(); the error surfaces there / at download
+        }
+    });
+}
+
+static void join_reader(nldsc_ld_session* s) {
+    if (s->reader.joinable()) s->reader.join();
+}
+
+// Stage 2: windows -> owned i-blocks -> plane ring -> chunks and supertiles, and their device copies.
+// `ramp`: start with small chunks and double up to the regular size -- for the calculate* entry points,
+// where the upload runs concurrently and the first kernels should start after a few MB have landed.
+static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end, const std::vector<int32_t>& lo,
+                         const std::vector<int32_t>& hi, bool ramp = false) {
+    if (row_begin < 0 || row_end > s->n_snp || row_begin >= row_end)
+        throw InvalidArgument("shard row range is empty or outside [0, n_snp)");
+    // rows this shard needs: owned range widened by the window halo, 64-aligned on the left
+    if (s->load_begin > floor64(lo[row_begin]) || s->load_end < hi[row_end - 1] + 1)
+        throw InvalidArgument("shard load range does not cover the window halo of its rows");
+    CUDA_CHECK(cudaSetDevice(s->device));
+    Tracer tr;
+    s->row_begin = row_begin;
+    s->row_end = row_end;
     s->own_begin = row_begin - s->load_begin;
     s->own_end = row_end - s->load_begin;
     const int32_t n_load = s->n_load;
     const int32_t n_load_pad = (n_load + kBlk - 1) / kBlk * kBlk;
+    cudaStream_t st = s->own_stream;
 
-    std::vector<int32_t> wlo(n_load), whi(n_load);
+    // window bounds, shard-local; pad rows get an empty window.  Pinned-free staging: the vectors
+    // live in the session until the async copies have been consumed.
+    std::vector<int32_t>& wlo = s->h_win_lo;
+    std::vector<int32_t>& whi = s->h_win_hi;
+    wlo.assign(n_load_pad, 1);
+    whi.assign(n_load_pad, 0);
     for (int32_t i = 0; i < n_load; ++i) {
         wlo[i] = std::max(lo[i + s->load_begin] - s->load_begin, 0);
         whi[i] = std::min(hi[i + s->load_begin] - s->load_begin, n_load - 1);
@@ -214,56 +533,63 @@ static nldsc_ld_session* session_build(int device, const nldsc_ld_params* p, int
         jb_hi[b - ib0] = whi[r1] / kBlk;
         max_span = std::max(max_span, (jb_hi[b - ib0] - jb_lo[b - ib0] + 1) * kBlk);
     }
+    // a CTA pair scores two adjacent i-blocks against the union of their column ranges
+    for (int32_t b = 0; b + 1 < n_ib; ++b)
+        max_span = std::max(max_span, (jb_hi[b + 1] - jb_lo[b] + 1) * kBlk);
+    tr.lap("windows");
 
     // ---- fixed-size device buffers
-    s->d_packed = dmalloc<uint8_t>(static_cast<size_t>(n_load) * s->bps + 16);
-    s->d_counts = dmalloc<int32_t>(static_cast<size_t>(n_load_pad) * 3);
-    s->d_coef = dmalloc<SnpCoef>(n_load_pad);
-    s->d_flags = dmalloc<uint8_t>(n_load_pad);
-    s->d_maf = dmalloc<double>(n_load_pad);
-    s->d_rstd = dmalloc<double>(n_load_pad);
-    s->d_win_lo = dmalloc<int32_t>(n_load_pad);
-    s->d_win_hi = dmalloc<int32_t>(n_load_pad);
-    CUDA_CHECK(cudaMemset(s->d_flags, 0, n_load_pad));
-    CUDA_CHECK(cudaMemset(s->d_coef, 0, sizeof(SnpCoef) * n_load_pad));
-    CUDA_CHECK(cudaMemset(s->d_packed + static_cast<size_t>(n_load) * s->bps, 0, 16));
+    s->d_counts = amalloc<int32_t>(s->arena, static_cast<size_t>(n_load_pad) * 3);
+    s->d_coef = amalloc<SnpCoef>(s->arena, n_load_pad);
+    s->d_flags = amalloc<uint8_t>(s->arena, n_load_pad);
+    s->d_maf = amalloc<double>(s->arena, n_load_pad);
+    s->d_rstd = amalloc<double>(s->arena, n_load_pad);
+    s->d_win_lo = amalloc<int32_t>(s->arena, n_load_pad);
+    s->d_win_hi = amalloc<int32_t>(s->arena, n_load_pad);
+    CUDA_CHECK(cudaMemsetAsync(s->d_flags, 0, n_load_pad, st));
+    CUDA_CHECK(cudaMemsetAsync(s->d_coef, 0, sizeof(SnpCoef) * n_load_pad, st));
     const int32_t n_own = s->own_end - s->own_begin;
-    s->d_l2 = dmalloc<double>(n_own);
-    s->d_l2d = dmalloc<double>(n_own);
-    s->d_wsa = dmalloc<int32_t>(n_own);
-    s->d_wsd = dmalloc<int32_t>(n_own);
-    s->d_wsde = dmalloc<int32_t>(n_own);
-    {
-        std::vector<int32_t> pad_lo(n_load_pad, 1), pad_hi(n_load_pad, 0);
-        std::copy(wlo.begin(), wlo.end(), pad_lo.begin());
-        std::copy(whi.begin(), whi.end(), pad_hi.begin());
-        CUDA_CHECK(cudaMemcpy(s->d_win_lo, pad_lo.data(), sizeof(int32_t) * n_load_pad, cudaMemcpyHostToDevice));
-        CUDA_CHECK(cudaMemcpy(s->d_win_hi, pad_hi.data(), sizeof(int32_t) * n_load_pad, cudaMemcpyHostToDevice));
-    }
+    s->d_l2 = amalloc<double>(s->arena, n_own);
+    s->d_l2d = amalloc<double>(s->arena, n_own);
+    s->d_wsa = amalloc<int32_t>(s->arena, n_own);
+    s->d_wsd = amalloc<int32_t>(s->arena, n_own);
+    s->d_wsde = amalloc<int32_t>(s->arena, n_own);
+    CUDA_CHECK(cudaMemcpyAsync(s->d_win_lo, wlo.data(), sizeof(int32_t) * n_load_pad, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(s->d_win_hi, whi.data(), sizeof(int32_t) * n_load_pad, cudaMemcpyHostToDevice, st));
+    tr.lap("fixed buffers");
 
-    // ---- plane ring: as many SNP rows as the memory budget allows (4 int8 planes each)
-    size_t free_b = 0, total_b = 0;
-    CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+    // ---- plane ring: as many SNP rows as needed, within the memory budget (4 int8 planes each)
     const size_t row_bytes = static_cast<size_t>(kPlanes) * s->npad;
-    size_t budget = static_cast<size_t>(0.85 * static_cast<double>(free_b));
-    budget = std::min(budget, env_size("NLDSC_PLANE_BYTES", budget));
+    size_t reusable = 0;      // blocks cached from an earlier call are reusable, so they count as free
+    for (const Arena::Block& b : s->arena->blocks) reusable += b.size - b.used;
+    size_t budget = reusable;
+    if (static_cast<size_t>(n_load_pad) * row_bytes > reusable || getenv("NLDSC_PLANE_BYTES")) {
+        size_t free_b = 0, total_b = 0;
+        CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
+        budget = static_cast<size_t>(0.85 * static_cast<double>(free_b + reusable));
+        budget = std::min(budget, env_size("NLDSC_PLANE_BYTES", budget));
+    }
     int64_t cap = static_cast<int64_t>(budget / row_bytes) / kBlk * kBlk;
     cap = std::min<int64_t>(cap, n_load_pad);
     if (cap < max_span) {
         char buf[200];
         snprintf(buf, sizeof(buf),
-                 "window too wide for device memory: one SNP block needs %d resident SNP rows of %zu bytes, budget %zu bytes",
+                 "window too wide for device memory: one SNP block pair needs %d resident SNP rows of %zu bytes, budget %zu bytes",
                  max_span, row_bytes, budget);
         throw CudaError(buf);
     }
     s->plane_rows = cap;
-    s->d_planes = dmalloc<int8_t>(static_cast<size_t>(cap) * row_bytes);
+    s->d_planes = amalloc<int8_t>(s->arena, static_cast<size_t>(cap) * row_bytes);
+    tr.lap("plane ring");
 
     // ---- chunks: greedy runs of i-blocks whose column span fits the ring
     const int32_t chunk_rows = static_cast<int32_t>(
         std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", 32768), static_cast<size_t>(std::numeric_limits<int32_t>::max() / 2)));
-    std::vector<Tile> tiles;
-    std::vector<int32_t> tile_begin;
+    int32_t ramp_rows = (ramp && !getenv("NLDSC_CHUNK_ROWS")) ? 4096 : chunk_rows;
+    std::vector<Tile>& tiles = s->h_tiles;
+    std::vector<int32_t>& tile_begin = s->h_tile_begin;
+    tiles.clear();
+    tile_begin.clear();
     int32_t unpacked_to = jb_lo[0] * kBlk;   // rows below the first needed column never enter the ring
     for (int32_t b = 0; b < n_ib;) {
         Chunk c{};
@@ -275,22 +601,28 @@ static nldsc_ld_session* session_build(int device, const nldsc_ld_params* p, int
         while (e < n_ib) {
             const int32_t col1 = (jb_hi[e] + 1) * kBlk;
             if (col1 - col0 > cap) break;
-            if (e > b && (e - b) * kBlk >= chunk_rows) break;
+            if (e > b && (e - b) * kBlk >= std::min(ramp_rows, chunk_rows)) break;
             ++e;
         }
+        ramp_rows = std::min(chunk_rows, ramp_rows * 2);
         // e > b is guaranteed by cap >= max_span
         const int32_t col1 = (jb_hi[e - 1] + 1) * kBlk;
         c.n_iblocks = e - b;
         c.new_row0 = std::max(unpacked_to, col0);
         c.new_row1 = std::max(col1, c.new_row0);
         unpacked_to = c.new_row1;
-        for (int32_t k = b; k < e; ++k) {
+        // supertile rows: i-blocks (k, k+1) share their j-blocks; windows are monotone, so the union of
+        // the two j ranges is [jb_lo[k], jb_hi[k+1]] (pairs outside a block's own window score nothing)
+        for (int32_t k = b; k < e; k += 2) {
             tile_begin.push_back(static_cast<int32_t>(tiles.size() - c.tile0));
-            for (int32_t jb = jb_lo[k]; jb <= jb_hi[k]; ++jb) {
+            const bool two = k + 1 < e;
+            for (int32_t jb = jb_lo[k]; jb <= (two ? jb_hi[k + 1] : jb_hi[k]); ++jb) {
                 Tile t;
-                t.i0 = (ib0 + k) * kBlk;
+                t.i0[0] = (ib0 + k) * kBlk;
+                t.i0[1] = two ? (ib0 + k + 1) * kBlk : kDeadBlock;
+                t.a_row[0] = static_cast<int32_t>(t.i0[0] % cap);
+                t.a_row[1] = two ? static_cast<int32_t>(t.i0[1] % cap) : t.a_row[0];
                 t.j0 = jb * kBlk;
-                t.a_row = static_cast<int32_t>(t.i0 % cap);
                 t.b_row = static_cast<int32_t>(t.j0 % cap);
                 tiles.push_back(t);
             }
@@ -301,44 +633,25 @@ static nldsc_ld_session* session_build(int device, const nldsc_ld_params* p, int
         s->chunks.push_back(c);
         b = e;
     }
+    tr.lap("tile plan");
     s->total_tiles = static_cast<int64_t>(tiles.size());
-    s->d_tiles = dmalloc<Tile>(tiles.size());
-    s->d_tile_begin = dmalloc<int32_t>(tile_begin.size());
-    CUDA_CHECK(cudaMemcpy(s->d_tiles, tiles.data(), sizeof(Tile) * tiles.size(), cudaMemcpyHostToDevice));
-    CUDA_CHECK(cudaMemcpy(s->d_tile_begin, tile_begin.data(), sizeof(int32_t) * tile_begin.size(),
-                          cudaMemcpyHostToDevice));
-    const size_t np = static_cast<size_t>(s->max_chunk_tiles) * kBlk;
-    s->part.add = dmalloc<double>(np);
-    s->part.dom = dmalloc<double>(np);
-    s->part.wsa = dmalloc<int32_t>(np);
-    s->part.wsd = dmalloc<int32_t>(np);
-    s->part.wsde = dmalloc<int32_t>(np);
-
+    s->d_tiles = amalloc<Tile>(s->arena, tiles.size());
+    s->d_tile_begin = amalloc<int32_t>(s->arena, tile_begin.size());
+    CUDA_CHECK(cudaMemcpyAsync(s->d_tiles, tiles.data(), sizeof(Tile) * tiles.size(), cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(s->d_tile_begin, tile_begin.data(), sizeof(int32_t) * tile_begin.size(),
+                               cudaMemcpyHostToDevice, st));
+    const size_t np = static_cast<size_t>(s->max_chunk_tiles) * 2 * kBlk;
+    s->part.add = amalloc<double>(s->arena, np);
+    s->part.dom = amalloc<double>(s->arena, np);
+    s->part.wsa = amalloc<int32_t>(s->arena, np);
+    s->part.wsd = amalloc<int32_t>(s->arena, np);
+    s->part.wsde = amalloc<int32_t>(s->arena, np);
     if (!s->use_simt) s->maps = band_maps_create(s->d_planes, s->plane_rows, s->npad);
-    CUDA_CHECK(cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking));
-    CUDA_CHECK(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
-    s->ev_uploaded.resize(s->chunks.size());
-    for (auto& e : s->ev_uploaded) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    CUDA_CHECK(cudaEventCreate(&s->ev_run0));
-    CUDA_CHECK(cudaEventCreate(&s->ev_run1));
-    return sp.release();
-}
-
-// H2D of the packed rows, one copy per chunk so run() can start on chunk 0 while the rest
-// of the shard is still crossing PCIe.  host_rows points at row load_begin.
-static void session_upload(nldsc_ld_session* s, const uint8_t* host_rows, cudaStream_t st) {
-    CUDA_CHECK(cudaSetDevice(s->device));
-    cudaStream_t cs = st ? st : s->copy_stream;
-    for (size_t c = 0; c < s->chunks.size(); ++c) {
-        const Chunk& ch = s->chunks[c];
-        const int32_t r0 = std::min(ch.new_row0, s->n_load), r1 = std::min(ch.new_row1, s->n_load);
-        if (r1 > r0) {
-            const size_t off = static_cast<size_t>(r0) * s->bps, len = static_cast<size_t>(r1 - r0) * s->bps;
-            CUDA_CHECK(cudaMemcpyAsync(s->d_packed + off, host_rows + off, len, cudaMemcpyHostToDevice, cs));
-        }
-        CUDA_CHECK(cudaEventRecord(s->ev_uploaded[c], cs));
-    }
-    s->uploaded = true;
+    // the plan is consumed by kernels on the session's own stream or on a caller's stream
+    CUDA_CHECK(cudaEventCreateWithFlags(&s->ev_planned, cudaEventDisableTiming));
+    CUDA_CHECK(cudaEventRecord(s->ev_planned, st));
+    s->planned = true;
+    tr.lap("tile upload + maps");
 }
 
 static void unpack_rows(nldsc_ld_session* s, int32_t r0, int32_t r1, cudaStream_t st) {
@@ -359,17 +672,29 @@ static void unpack_rows(nldsc_ld_session* s, int32_t r0, int32_t r1, cudaStream_
 }
 
 static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
-    if (!s->uploaded) throw CudaError("session_run called before session_upload");
+    if (!s->upload_started) throw CudaError("session_run called before session_upload");
+    if (!s->planned) throw CudaError("session_run called before the band plan was built");
     CUDA_CHECK(cudaSetDevice(s->device));
     cudaStream_t st = st_in ? st_in : s->own_stream;
     s->spans_used = 0;
     s->launches = 0;
+    if (st != s->own_stream) CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_planned, 0));
     CUDA_CHECK(cudaEventRecord(s->ev_run0, st));
     const double n = static_cast<double>(s->n_org);
     for (size_t ci = 0; ci < s->chunks.size(); ++ci) {
         const Chunk& c = s->chunks[ci];
-        CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_uploaded[ci], 0));
         const int32_t r0 = std::min(c.new_row0, s->n_load), r1 = std::min(c.new_row1, s->n_load);
+        if (r1 > r0) {
+            // the chunk's kernels wait on the device for the last piece they read; the event must have
+            // been recorded by then, so wait on the host for the reader to have issued that piece
+            const int32_t piece = (r1 - 1) / s->piece_rows;
+            {
+                std::unique_lock<std::mutex> g(s->up_mu);
+                s->up_cv.wait(g, [&] { return s->pieces_issued > piece; });
+                if (!s->up_error.empty()) throw CudaError(s->up_error);
+            }
+            CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_piece[piece], 0));
+        }
         if (r1 > r0) {
             {
                 SpanScope sc(s, st, kFamCount);
@@ -434,6 +759,8 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
 
 static void session_download(nldsc_ld_session* s, nldsc_ld_result* out, cudaStream_t st_in) {
     if (!s->ran) throw CudaError("session_download called before session_run");
+    join_reader(s);
+    if (!s->up_error.empty()) throw CudaError(s->up_error);
     if (!out || !out->l2 || !out->l2d || !out->maf || !out->residuals_std || !out->l2_ws || !out->l2d_ws ||
         !out->l2d_wse)
         throw InvalidArgument("result arrays must all be non-null");
@@ -501,44 +828,96 @@ int first_device_from_env() {
     return (v && *v) ? atoi(v) : 0;
 }
 
-// `fetch(row0, row1)` returns a host pointer to packed rows [row0, row1) valid until the shard is done.
-template <class Fetch>
-void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, Fetch&& fetch) {
+// compute_windows on the device (plan.cu): positions up, two int32 arrays back.  Scratch is cached per device.
+void compute_windows_device(int device, const double* pos, int32_t n, double wind, std::vector<int32_t>& lo,
+                            std::vector<int32_t>& hi) {
+    static std::mutex mu;
+    static void* scratch[64] = {nullptr};
+    static size_t scratch_bytes[64] = {0};
+    std::lock_guard<std::mutex> g(mu);
+    CUDA_CHECK(cudaSetDevice(device));
+    const size_t need = static_cast<size_t>(n) * 16;
+    void*& buf = scratch[device & 63];
+    if (scratch_bytes[device & 63] < need) {
+        if (buf) cudaFree(buf);
+        buf = nullptr;
+        scratch_bytes[device & 63] = 0;
+        CUDA_CHECK(cudaMalloc(&buf, need + need / 4));
+        scratch_bytes[device & 63] = need + need / 4;
+    }
+    double* d_pos = static_cast<double*>(buf);
+    int32_t* d_lo = reinterpret_cast<int32_t*>(d_pos + n);
+    int32_t* d_hi = d_lo + n;
+    lo.resize(n);
+    hi.resize(n);
+    CUDA_CHECK(cudaMemcpy(d_pos, pos, sizeof(double) * n, cudaMemcpyHostToDevice));
+    launch_windows(d_pos, n, wind, d_lo, d_hi, nullptr);
+    CUDA_CHECK(cudaMemcpy(lo.data(), d_lo, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
+    CUDA_CHECK(cudaMemcpy(hi.data(), d_hi, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
+}
+
+// `start_upload(session)` begins the asynchronous H2D of the session's packed rows [load_begin, load_end)
+// (from host memory or from the .bed); it must not block on the transfer.
+template <class StartUpload>
+void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& start_upload) {
+    Tracer tr;
     validate_params(p);
     if (!out || !out->l2 || !out->l2d || !out->maf || !out->residuals_std || !out->l2_ws || !out->l2d_ws ||
         !out->l2d_wse)
         throw InvalidArgument("result arrays must all be non-null");
     const int ndev = usable_devices();
-    std::vector<int32_t> lo, hi;
-    compute_windows(p->positions, p->n_snp, p->ld_wind, lo, hi);
     const int dev0 = first_device_from_env();
     int parts = gpus_from_env(std::max(1, ndev - dev0));
     parts = std::max(1, std::min<int>(parts, (p->n_snp + kBlk - 1) / kBlk));
-    const std::vector<int32_t> cut = split_rows(lo, hi, parts);
+    tr.lap("validate+devices");
 
-    std::vector<ShardJob> jobs;
-    for (int k = 0; k < parts; ++k)
-        if (cut[k + 1] > cut[k]) jobs.push_back({dev0 + k, cut[k], cut[k + 1]});
+    const bool trace = tr.on;
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double, std::milli>(b - a).count();
+    };
+    std::vector<int32_t> lo, hi;
 
-    auto work = [&](ShardJob& j) {
+    auto work = [&](ShardJob& j) {      // one shard on one GPU
         nldsc_ld_session* s = nullptr;
+        const auto t0 = now();
+        auto t1 = t0, t2 = t0, t3 = t0, t4 = t0, t5 = t0;
         try {
-            s = session_build(j.device, p, j.row_begin, j.row_end, lo, hi);
-            const uint8_t* host = fetch(s->load_begin, s->load_end);
-            session_upload(s, host, nullptr);
+            s = session_open(j.device, p, floor64(lo[j.row_begin]), hi[j.row_end - 1] + 1);
+            t1 = now();
+            // plan first: its small H2D copies must not queue behind the bulk upload on the copy engine
+            session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true);
+            t2 = now();
+            start_upload(s);
+            t3 = now();
             session_run(s, nullptr);
+            t4 = now();
             nldsc_ld_result sub = *out;
             sub.l2 += j.row_begin; sub.l2d += j.row_begin; sub.maf += j.row_begin;
             sub.residuals_std += j.row_begin; sub.l2_ws += j.row_begin; sub.l2d_ws += j.row_begin;
             sub.l2d_wse += j.row_begin;
             session_download(s, &sub, nullptr);
+            t5 = now();
         } catch (const std::invalid_argument& e) {
             j.rc = NLDSC_ERR_INVALID; j.msg = e.what();
         } catch (const std::exception& e) {
             j.rc = NLDSC_ERR_RUNTIME; j.msg = e.what();
         }
         session_free(s);
+        if (trace)
+            fprintf(stderr, "[nldsc_ld] gpu %d rows [%d,%d): open %.2f ms, plan %.2f, upload-start %.2f, run-issue %.2f, "
+                            "download+sync %.2f, free %.2f\n",
+                    j.device, j.row_begin, j.row_end, ms(t0, t1), ms(t1, t2), ms(t2, t3), ms(t3, t4), ms(t4, t5),
+                    ms(t5, now()));
     };
+
+    require_sm100(dev0);
+    compute_windows_device(dev0, p->positions, p->n_snp, p->ld_wind, lo, hi);
+    tr.lap("windows (device)");
+    const std::vector<int32_t> cut = split_rows(lo, hi, parts);
+    std::vector<ShardJob> jobs;
+    for (int k = 0; k < parts; ++k)
+        if (cut[k + 1] > cut[k]) jobs.push_back({dev0 + k, cut[k], cut[k + 1]});
     if (jobs.size() == 1) {
         work(jobs[0]);
     } else {
@@ -594,7 +973,9 @@ int nldsc_ld_calculate_packed(const uint8_t* packed, const nldsc_ld_params* para
         if (!packed) throw InvalidArgument("packed is null");
         validate_params(params);
         const int64_t bps = (static_cast<int64_t>(params->n_org) + 3) / 4;
-        run_sharded(params, out, [&](int32_t r0, int32_t) { return packed + static_cast<size_t>(r0) * bps; });
+        run_sharded(params, out, [&](nldsc_ld_session* s) {
+            session_upload_mem(s, packed + static_cast<size_t>(s->load_begin) * bps, nullptr);
+        });
     });
 }
 
@@ -619,30 +1000,8 @@ int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char
                      static_cast<long long>(stt.st_size), static_cast<long long>(want));
             throw InvalidArgument(buf);
         }
-        // one pinned staging buffer per shard thread, filled by pread
-        std::vector<void*> pinned;
-        std::mutex mu;
-        struct Cleanup {
-            std::vector<void*>& v;
-            ~Cleanup() { for (void* q : v) cudaFreeHost(q); }
-        } cleanup{pinned};
-        run_sharded(params, out, [&](int32_t r0, int32_t r1) -> const uint8_t* {
-            const size_t len = static_cast<size_t>(r1 - r0) * bps;
-            void* buf = nullptr;
-            CUDA_CHECK(cudaHostAlloc(&buf, std::max<size_t>(len, 1), cudaHostAllocDefault));
-            {
-                std::lock_guard<std::mutex> g(mu);
-                pinned.push_back(buf);
-            }
-            size_t done = 0;
-            while (done < len) {
-                const ssize_t k = pread(fd, static_cast<char*>(buf) + done, std::min<size_t>(len - done, 1u << 30),
-                                        3 + static_cast<off_t>(r0) * bps + static_cast<off_t>(done));
-                if (k <= 0) throw CudaError("short read on .bed file");
-                done += static_cast<size_t>(k);
-            }
-            return static_cast<const uint8_t*>(buf);
-        });
+        // every shard streams its own byte range: reader thread -> pinned slot ring -> H2D (session_upload_file)
+        run_sharded(params, out, [&](nldsc_ld_session* s) { session_upload_file(s, fd); });
     });
 }
 
@@ -654,14 +1013,23 @@ int nldsc_ld_session_create(nldsc_ld_session** out, int device, const nldsc_ld_p
         validate_params(params);
         std::vector<int32_t> lo, hi;
         compute_windows(params->positions, params->n_snp, params->ld_wind, lo, hi);
-        *out = session_build(device, params, row_begin, row_end, lo, hi);
+        if (row_begin < 0 || row_end > params->n_snp || row_begin >= row_end)
+            throw InvalidArgument("shard row range is empty or outside [0, n_snp)");
+        nldsc_ld_session* s = session_open(device, params, floor64(lo[row_begin]), hi[row_end - 1] + 1);
+        try {
+            session_plan(s, row_begin, row_end, lo, hi);
+        } catch (...) {
+            session_free(s);
+            throw;
+        }
+        *out = s;
     });
 }
 
 int nldsc_ld_session_upload(nldsc_ld_session* s, const uint8_t* packed_rows, void* stream, char* err, size_t errlen) {
     return guarded(err, errlen, [&] {
         if (!s || !packed_rows) throw InvalidArgument("null session or buffer");
-        session_upload(s, packed_rows, static_cast<cudaStream_t>(stream));
+        session_upload_mem(s, packed_rows, static_cast<cudaStream_t>(stream));
     });
 }
 
@@ -767,13 +1135,13 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         uint8_t* d_packed = dmalloc<uint8_t>(static_cast<size_t>(n_snp) * bps + 16);
         const size_t plane_bytes = static_cast<size_t>(rows) * npad;
         int8_t* d_planes = dmalloc<int8_t>(plane_bytes * kPlanes);
-        int32_t* d_dump = dmalloc<int32_t>(128 * 192);
+        int32_t* d_dump = dmalloc<int32_t>(2 * 128 * 192);
         Tile* d_tile = dmalloc<Tile>(1);
         SnpCoef* d_coef = dmalloc<SnpCoef>(rows);
         uint8_t* d_flags = dmalloc<uint8_t>(rows);
         int32_t* d_w = dmalloc<int32_t>(static_cast<size_t>(rows) * 2);
-        double* d_pd = dmalloc<double>(2 * kBlk);
-        int32_t* d_pi = dmalloc<int32_t>(3 * kBlk);
+        double* d_pd = dmalloc<double>(4 * kBlk);
+        int32_t* d_pi = dmalloc<int32_t>(6 * kBlk);
         struct Free {
             std::vector<void*> v;
             ~Free() { for (void* q : v) cudaFree(q); }
@@ -785,7 +1153,7 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         CUDA_CHECK(cudaMemset(d_flags, 0, rows));
         CUDA_CHECK(cudaMemset(d_w, 0, sizeof(int32_t) * 2 * rows));
         launch_unpack(d_packed, bps, 0, n_snp, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, nullptr);
-        Tile t{i_block * kBlk, j_block * kBlk, i_block * kBlk, j_block * kBlk};
+        Tile t{{i_block * kBlk, i_block * kBlk}, {i_block * kBlk, kDeadBlock}, j_block * kBlk, j_block * kBlk};
         CUDA_CHECK(cudaMemcpy(d_tile, &t, sizeof(t), cudaMemcpyHostToDevice));
         BandArgs a{};
         a.tiles = d_tile;
@@ -801,10 +1169,10 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         a.adj_c = 1.0;
         a.rsq_thr = 0.0;
         a.part.add = d_pd;
-        a.part.dom = d_pd + kBlk;
+        a.part.dom = d_pd + 2 * kBlk;
         a.part.wsa = d_pi;
-        a.part.wsd = d_pi + kBlk;
-        a.part.wsde = d_pi + 2 * kBlk;
+        a.part.wsd = d_pi + 2 * kBlk;
+        a.part.wsde = d_pi + 4 * kBlk;
         a.dump = d_dump;
         const char* band = getenv("NLDSC_BAND");
         if (band && strcmp(band, "simt") == 0) {
@@ -816,6 +1184,93 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         }
         CUDA_CHECK(cudaDeviceSynchronize());
         CUDA_CHECK(cudaMemcpy(acc_out, d_dump, sizeof(int32_t) * 128 * 192, cudaMemcpyDeviceToHost));
+    });
+}
+
+int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* lo, int32_t* hi, char* err, size_t errlen) {
+    return guarded(err, errlen, [&] {
+        validate_params(params);
+        if (!lo || !hi) throw InvalidArgument("lo / hi is null");
+        usable_devices();
+        const int dev = first_device_from_env();
+        require_sm100(dev);
+        std::vector<int32_t> l, h;
+        compute_windows_device(dev, params->positions, params->n_snp, params->ld_wind, l, h);
+        std::copy(l.begin(), l.end(), lo);
+        std::copy(h.begin(), h.end(), hi);
+    });
+}
+
+int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int32_t reps, float* ms_out, char* err,
+                              size_t errlen) {
+    return guarded(err, errlen, [&] {
+        if (mode < 0 || mode > 2 || n_org <= 0 || n_tiles <= 0 || reps <= 0 || !ms_out) throw InvalidArgument("bad arguments");
+        usable_devices();
+        const int dev = first_device_from_env();
+        CUDA_CHECK(cudaSetDevice(dev));
+        require_sm100(dev);
+        int sm_count = 0;
+        CUDA_CHECK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+        const int64_t bps = (static_cast<int64_t>(n_org) + 3) / 4;
+        const int32_t npad = static_cast<int32_t>(((static_cast<int64_t>(n_org) + kKAlign - 1) / kKAlign) * kKAlign);
+        const int32_t rows = 4096, nb = rows / kBlk;
+        uint8_t* d_packed = dmalloc<uint8_t>(static_cast<size_t>(rows) * bps + 16);
+        const size_t plane_bytes = static_cast<size_t>(rows) * npad;
+        int8_t* d_planes = dmalloc<int8_t>(plane_bytes * kPlanes);
+        Tile* d_tiles = dmalloc<Tile>(n_tiles);
+        SnpCoef* d_coef = dmalloc<SnpCoef>(rows);
+        uint8_t* d_flags = dmalloc<uint8_t>(rows);
+        int32_t* d_w = dmalloc<int32_t>(static_cast<size_t>(rows) * 2);
+        double* d_pd = dmalloc<double>(static_cast<size_t>(n_tiles) * 4 * kBlk);
+        int32_t* d_pi = dmalloc<int32_t>(static_cast<size_t>(n_tiles) * 6 * kBlk);
+        struct Free {
+            std::vector<void*> v;
+            ~Free() { for (void* q : v) cudaFree(q); }
+        } fr{{d_packed, d_planes, d_tiles, d_coef, d_flags, d_w, d_pd, d_pi}};
+        CUDA_CHECK(cudaMemset(d_packed, 0xB9, static_cast<size_t>(rows) * bps + 16));   // codes 01 10 11 10 per byte
+        CUDA_CHECK(cudaMemset(d_coef, 0, sizeof(SnpCoef) * rows));
+        CUDA_CHECK(cudaMemset(d_flags, 0, rows));                                        // every pair rejected: cheapest epilogue
+        CUDA_CHECK(cudaMemset(d_w, 0, sizeof(int32_t) * 2 * rows));
+        launch_unpack(d_packed, bps, 0, rows, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, nullptr);
+        std::vector<Tile> tiles(n_tiles);
+        for (int32_t t = 0; t < n_tiles; ++t) {       // band-like walk: 22 j-blocks per i-block pair
+            const int32_t p = (t / 22) % (nb / 2), jb = (2 * p + t % 22) % nb;
+            tiles[t] = Tile{{2 * p * kBlk, (2 * p + 1) * kBlk}, {2 * p * kBlk, (2 * p + 1) * kBlk}, jb * kBlk, jb * kBlk};
+        }
+        CUDA_CHECK(cudaMemcpy(d_tiles, tiles.data(), sizeof(Tile) * n_tiles, cudaMemcpyHostToDevice));
+        BandArgs a{};
+        a.tiles = d_tiles;
+        a.n_tiles = n_tiles;
+        a.k_steps = npad / kKAlign;
+        a.coef = d_coef;
+        a.flags = d_flags;
+        a.win_lo = d_w;
+        a.win_hi = d_w + rows;
+        a.n_load = rows;
+        a.n = n_org;
+        a.inv_n = 1.0 / n_org;
+        a.adj_c = 1.0;
+        a.part.add = d_pd;
+        a.part.dom = d_pd + static_cast<size_t>(n_tiles) * 2 * kBlk;
+        a.part.wsa = d_pi;
+        a.part.wsd = d_pi + static_cast<size_t>(n_tiles) * 2 * kBlk;
+        a.part.wsde = d_pi + static_cast<size_t>(n_tiles) * 4 * kBlk;
+        a.probe = mode;
+        BandMaps* maps = band_maps_create(d_planes, rows, npad);
+        struct MapFree { BandMaps* m; ~MapFree() { band_maps_destroy(m); } } mf{maps};
+        cudaEvent_t e0, e1;
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        launch_band_tc(maps, a, sm_count, nullptr);                                      // warm-up
+        CUDA_CHECK(cudaEventRecord(e0, nullptr));
+        for (int r = 0; r < reps; ++r) launch_band_tc(maps, a, sm_count, nullptr);
+        CUDA_CHECK(cudaEventRecord(e1, nullptr));
+        CUDA_CHECK(cudaEventSynchronize(e1));
+        float ms = 0;
+        CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        *ms_out = ms / reps;
     });
 }
 

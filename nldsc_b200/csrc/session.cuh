@@ -3,6 +3,10 @@
 #include "common.cuh"
 #include "../../include/nldsc_ld.h"
 
+#include <condition_variable>
+#include <mutex>
+#include <string>
+#include <thread>
 #include <vector>
 
 namespace nldsc {
@@ -29,6 +33,35 @@ struct Chunk {
     int32_t tb0;          // offset into tile_begin (n_iblocks + 1 entries, relative to tile0)
 };
 
+// Device workspace of one session: a bump allocator over a few large cudaMalloc blocks that are
+// cached per device between calls, so a repeated nldsc_ld_calculate* pays no cudaMalloc / cudaFree
+// (each a device-wide synchronisation, and tens of ms for the multi-GB plane ring).
+struct Arena {
+    struct Block { char* base; size_t size, used; };
+    int device = -1;
+    bool cached = false;          // blocks go back to the per-device cache on release
+    std::vector<Block> blocks;
+    void* alloc(size_t bytes);    // 512-byte aligned; grows by cudaMalloc when no block has room
+    size_t capacity() const;
+};
+Arena* arena_acquire(int device);     // the device's cached arena, or a private one if that is in use
+void arena_release(Arena* a);         // resets the bump pointers; private arenas free their blocks
+size_t arena_cached_bytes(int device);
+void arena_trim(int device);          // frees the cached blocks (device < 0: every device)
+
+// Pinned staging ring for reading a .bed: kSlots slots the reader thread fills by pread and drains by
+// cudaMemcpyAsync; cached per device like the Arena (pinning memory costs tens of ms).
+struct HostStage {
+    static constexpr int kSlots = 4;
+    int device = -1;
+    bool cached = false;
+    void* base = nullptr;
+    size_t bytes = 0;             // kSlots equal slots
+    cudaEvent_t ev[kSlots] = {nullptr, nullptr, nullptr, nullptr};   // slot's last H2D has landed
+};
+HostStage* host_stage_acquire(int device);
+void host_stage_release(HostStage* h);
+
 enum Family { kFamCount = 0, kFamStats, kFamUnpack, kFamBand, kFamFinalize, kFamN };
 
 }  // namespace nldsc
@@ -44,7 +77,8 @@ struct nldsc_ld_session {
     int32_t npad = 0;
     double maf_thr = 0, std_thr = 0, rsq_thr = 0;
     bool use_simt = false;
-    bool uploaded = false;
+    bool upload_started = false;
+    bool planned = false;
 
     std::vector<nldsc::Chunk> chunks;
     int64_t total_tiles = 0;
@@ -52,7 +86,8 @@ struct nldsc_ld_session {
     int32_t max_chunk_tiles = 0;
     int64_t plane_rows = 0;                   // ring capacity in SNP rows (multiple of 64)
 
-    // device
+    // device (all carved from `arena`)
+    nldsc::Arena* arena = nullptr;
     uint8_t* d_packed = nullptr;
     int32_t* d_counts = nullptr;
     nldsc::SnpCoef* d_coef = nullptr;
@@ -72,8 +107,20 @@ struct nldsc_ld_session {
     int32_t* d_wsde = nullptr;
     nldsc::BandMaps* maps = nullptr;
     cudaStream_t own_stream = nullptr;        // compute
-    cudaStream_t copy_stream = nullptr;       // H2D of packed rows, chunk by chunk
-    std::vector<cudaEvent_t> ev_uploaded;     // one per chunk
+    cudaStream_t copy_stream = nullptr;       // H2D of packed rows, piece by piece
+    int32_t piece_rows = 0;                   // rows per upload piece (multiple of 64)
+    std::vector<cudaEvent_t> ev_piece;        // piece has landed in d_packed
+    cudaEvent_t ev_planned = nullptr;         // windows / tiles have landed
+    // upload progress as seen by the host: run() may only wait on piece events that were recorded
+    std::mutex up_mu;
+    std::condition_variable up_cv;
+    int32_t pieces_issued = 0;
+    std::string up_error;
+    std::thread reader;                       // .bed reader (nldsc_ld_calculate only)
+    nldsc::HostStage* stage = nullptr;
+    // host copies of the plan (sources of the asynchronous H2D copies)
+    std::vector<int32_t> h_win_lo, h_win_hi, h_tile_begin;
+    std::vector<nldsc::Tile> h_tiles;
 
     // timing of the last run(): event pairs per kernel family
     struct Span { cudaEvent_t a, b; int family; };

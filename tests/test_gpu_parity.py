@@ -74,6 +74,21 @@ def test_unpack_and_count_match_decoder(n_org):
     assert np.array_equal(m[:, :bps * 4], (lsb == 1) & valid)
 
 
+def test_device_windows_equal_host_windows():
+    """plan.cu windows_kernel vs the host sweep (tools.h:43-44 predicate), incl. ties, zero and huge windows."""
+    rng = np.random.default_rng(3)
+    pos = np.sort(rng.uniform(0, 40, 70001))
+    pos[500:540] = pos[500]
+    pos[-3:] = pos[-3]
+    for wind in (0.0, 1e-9, 0.37, 1.0, 1e6):
+        lo_h, hi_h = capi.plan_windows(pos, wind)
+        lo_d, hi_d = capi.plan_windows_device(pos, wind)
+        assert np.array_equal(lo_h, lo_d) and np.array_equal(hi_h, hi_d), wind
+    bp = np.sort(rng.integers(1, 10**8, 5000)).astype(np.float64)
+    for wind in (0.0, 1000.0, 5e6):
+        assert all(np.array_equal(a, b) for a, b in zip(capi.plan_windows(bp, wind), capi.plan_windows_device(bp, wind)))
+
+
 # ---- band GEMM: exact integer cross-counts -----------------------------------------------
 
 @pytest.mark.parametrize("impl", ["simt", "tc"])
