@@ -88,7 +88,8 @@ typedef struct nldsc_ld_stats {
     int32_t load_end;         /* one past the last SNP row needed */
     int32_t npad;             /* padded organisms per plane row (bytes) */
     int32_t band_impl;        /* 1 = tcgen05 kernel, 0 = SIMT yardstick (NLDSC_BAND=simt) */
-    float ms_count;           /* CUDA-event times of the last run(), per kernel family */
+    float ms_count;           /* CUDA-event times of the last run(), per kernel family; counting is fused
+                                 into the unpack kernel, so this one stays 0 */
     float ms_stats;
     float ms_unpack;
     float ms_band;
@@ -104,7 +105,7 @@ int nldsc_ld_session_create(nldsc_ld_session** out, int device, const nldsc_ld_p
  * on `stream` (a cudaStream_t, or NULL for the session's own stream). */
 int nldsc_ld_session_upload(nldsc_ld_session* s, const uint8_t* packed_rows, void* stream,
                             char* err, size_t errlen);
-/* Count -> per-SNP stats -> unpack -> banded int8 GEMM + FP64 epilogue -> finalize,
+/* Unpack (+ genotype counts) -> per-SNP stats -> banded int8 GEMM + FP64 epilogue -> finalize,
  * all asynchronous on `stream`.  Inputs must be resident (upload done). */
 int nldsc_ld_session_run(nldsc_ld_session* s, void* stream, char* err, size_t errlen);
 /* Device -> host copy of the owned rows' seven arrays (length row_end-row_begin),

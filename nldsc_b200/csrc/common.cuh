@@ -86,14 +86,12 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 
 // ---- kernel launchers (defined in the .cu files) -------------------------------------
 // counts / coef / flags / maf / rstd are indexed by shard-local row; rows [row0, row0 + n_rows) are processed
-void launch_count(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows, int32_t n_org,
-                  int32_t* counts, cudaStream_t st);
 void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
                   double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
                   double* rstd_out, cudaStream_t st);
 void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
                    int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
-                   int32_t dst_row0, cudaStream_t st);
+                   int32_t dst_row0, int32_t* counts, cudaStream_t st);   // counts != null: += genotype counts (zeroed by the caller)
 void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st);
 void launch_zero_rows(int8_t* planes, int64_t plane_stride, int32_t npad, int32_t row0,
                       int32_t n_rows, cudaStream_t st);

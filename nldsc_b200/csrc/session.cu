@@ -364,6 +364,8 @@ static void session_free(nldsc_ld_session* s) {
     arena_release(s->arena);
     host_stage_release(s->stage);
     if (s->ev_planned) cudaEventDestroy(s->ev_planned);
+    if (s->ev_up0) cudaEventDestroy(s->ev_up0);
+    if (s->ev_up1) cudaEventDestroy(s->ev_up1);
     if (s->maps) band_maps_destroy(s->maps);
     for (auto& sp : s->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : s->ev_piece) cudaEventDestroy(e);
@@ -414,6 +416,8 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     for (auto& e : s->ev_piece) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CUDA_CHECK(cudaEventCreate(&s->ev_run0));
     CUDA_CHECK(cudaEventCreate(&s->ev_run1));
+    CUDA_CHECK(cudaEventCreate(&s->ev_up0));
+    CUDA_CHECK(cudaEventCreate(&s->ev_up1));
     return sp.release();
 }
 
@@ -432,12 +436,14 @@ static void session_upload_mem(nldsc_ld_session* s, const uint8_t* host_rows, cu
     CUDA_CHECK(cudaSetDevice(s->device));
     cudaStream_t cs = st ? st : s->copy_stream;
     const int32_t n_pieces = static_cast<int32_t>(s->ev_piece.size());
+    CUDA_CHECK(cudaEventRecord(s->ev_up0, cs));
     for (int32_t k = 0; k < n_pieces; ++k) {
         const int32_t r0 = k * s->piece_rows, r1 = std::min(s->n_load, r0 + s->piece_rows);
         const size_t off = static_cast<size_t>(r0) * s->bps, len = static_cast<size_t>(r1 - r0) * s->bps;
         CUDA_CHECK(cudaMemcpyAsync(s->d_packed + off, host_rows + off, len, cudaMemcpyHostToDevice, cs));
         CUDA_CHECK(cudaEventRecord(s->ev_piece[k], cs));
     }
+    CUDA_CHECK(cudaEventRecord(s->ev_up1, cs));
     note_pieces_issued(s, n_pieces);
     s->upload_started = true;
 }
@@ -583,26 +589,51 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     tr.lap("plane ring");
 
     // ---- chunks: greedy runs of i-blocks whose column span fits the ring
+    // Chunk size: big chunks amortise the band kernel's launch and its partial last wave; with a concurrent
+    // upload (`ramp`) a chunk cannot start before its last row has landed, so chunks start small, double,
+    // and stop at half the regular size.
+    const bool fixed_rows = getenv("NLDSC_CHUNK_ROWS") != nullptr;
     const int32_t chunk_rows = static_cast<int32_t>(
-        std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", 32768), static_cast<size_t>(std::numeric_limits<int32_t>::max() / 2)));
-    int32_t ramp_rows = (ramp && !getenv("NLDSC_CHUNK_ROWS")) ? 4096 : chunk_rows;
+        std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? 16384 : 32768),
+                         static_cast<size_t>(std::numeric_limits<int32_t>::max() / 2)));
+    int32_t ramp_rows = (ramp && !fixed_rows) ? 4096 : chunk_rows;
+    const int32_t wave = std::max(1, s->sm_count / 2);       // supertiles scored concurrently (one per CTA pair)
     std::vector<Tile>& tiles = s->h_tiles;
     std::vector<int32_t>& tile_begin = s->h_tile_begin;
     tiles.clear();
     tile_begin.clear();
     int32_t unpacked_to = jb_lo[0] * kBlk;   // rows below the first needed column never enter the ring
+    // supertiles of the i-block pair starting at block k when the chunk ends at e
+    auto pair_tiles = [&](int32_t k, int32_t e) { return (k + 1 < e ? jb_hi[k + 1] : jb_hi[k]) - jb_lo[k] + 1; };
     for (int32_t b = 0; b < n_ib;) {
         Chunk c{};
         c.iblock0 = ib0 + b;
         c.tile0 = static_cast<int64_t>(tiles.size());
         c.tb0 = static_cast<int32_t>(tile_begin.size());
         const int32_t col0 = jb_lo[b] * kBlk;
+        const int32_t target = std::min(ramp_rows, chunk_rows);
         int32_t e = b;
         while (e < n_ib) {
             const int32_t col1 = (jb_hi[e] + 1) * kBlk;
             if (col1 - col0 > cap) break;
-            if (e > b && (e - b) * kBlk >= std::min(ramp_rows, chunk_rows)) break;
+            if (e > b && (e - b) * kBlk >= target) break;
             ++e;
+        }
+        // The kernel deals supertiles round-robin to `wave` CTA pairs and every supertile costs the same,
+        // so a launch takes ceil(n_tiles / wave) tile times: pull the chunk end back by up to 1/8 of the
+        // chunk (whole i-block pairs) to where the last wave is fullest.
+        if (!fixed_rows && e < n_ib && e - b >= 32 && (e - b) % 2 == 0) {
+            int64_t nt = 0;
+            for (int32_t k = b; k < e; k += 2) nt += pair_tiles(k, e);
+            int32_t best_e = e;
+            double best_fill = static_cast<double>(nt) / (static_cast<double>((nt + wave - 1) / wave) * wave);
+            int64_t nt_k = nt;
+            for (int32_t e2 = e - 2; e2 >= e - (e - b) / 8 && e2 - b >= 2; e2 -= 2) {
+                nt_k -= pair_tiles(e2, e);                  // drop the pair (e2, e2 + 1)
+                const double fill = static_cast<double>(nt_k) / (static_cast<double>((nt_k + wave - 1) / wave) * wave);
+                if (fill > best_fill + 1e-9) { best_fill = fill; best_e = e2; }
+            }
+            e = best_e;
         }
         ramp_rows = std::min(chunk_rows, ramp_rows * 2);
         // e > b is guaranteed by cap >= max_span
@@ -662,7 +693,7 @@ static void unpack_rows(nldsc_ld_session* s, int32_t r0, int32_t r1, cudaStream_
         int32_t n = static_cast<int32_t>(std::min<int64_t>(r1 - r0, s->plane_rows - slot));
         if (r0 < s->n_load) {
             n = std::min(n, s->n_load - r0);
-            launch_unpack(s->d_packed, s->bps, r0, n, s->n_org, s->npad, s->d_planes, plane_stride, slot, st);
+            launch_unpack(s->d_packed, s->bps, r0, n, s->n_org, s->npad, s->d_planes, plane_stride, slot, s->d_counts, st);
         } else {
             launch_zero_rows(s->d_planes, plane_stride, s->npad, slot, n, st);
         }
@@ -695,21 +726,19 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             }
             CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_piece[piece], 0));
         }
-        if (r1 > r0) {
-            {
-                SpanScope sc(s, st, kFamCount);
-                launch_count(s->d_packed, s->bps, r0, r1 - r0, s->n_org, s->d_counts, st);
-            }
-            {
-                SpanScope sc(s, st, kFamStats);
-                launch_stats(s->d_counts, r0, r1 - r0, s->n_org, s->maf_thr, s->std_thr, s->d_coef, s->d_flags,
-                             s->d_maf, s->d_rstd, st);
-            }
-            s->launches += 2;
-        }
         {
+            // unpack the chunk's new rows into the ring; the same pass counts their genotypes
             SpanScope sc(s, st, kFamUnpack);
+            if (r1 > r0)
+                CUDA_CHECK(cudaMemsetAsync(s->d_counts + static_cast<size_t>(r0) * 3, 0,
+                                           sizeof(int32_t) * 3 * static_cast<size_t>(r1 - r0), st));
             unpack_rows(s, c.new_row0, c.new_row1, st);
+        }
+        if (r1 > r0) {
+            SpanScope sc(s, st, kFamStats);
+            launch_stats(s->d_counts, r0, r1 - r0, s->n_org, s->maf_thr, s->std_thr, s->d_coef, s->d_flags,
+                         s->d_maf, s->d_rstd, st);
+            ++s->launches;
         }
         BandArgs a{};
         a.tiles = s->d_tiles + c.tile0;
@@ -898,6 +927,17 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
             sub.l2d_wse += j.row_begin;
             session_download(s, &sub, nullptr);
             t5 = now();
+            if (trace) {
+                nldsc_ld_stats st;
+                nldsc_ld_session_stats(s, &st);
+                float up = 0, gap = 0, lag = 0;
+                cudaEventElapsedTime(&up, s->ev_up0, s->ev_up1);       // memory uploads only (the .bed reader records none)
+                cudaEventElapsedTime(&gap, s->ev_up0, s->ev_run0);
+                cudaEventElapsedTime(&lag, s->ev_up1, s->ev_run1);
+                fprintf(stderr, "[nldsc_ld]   device: upload %.2f ms, run %.2f ms (band %.2f unpack %.2f count %.2f stats %.2f "
+                                "finalize %.2f), run starts %.2f after upload start, ends %.2f after upload end, %d chunks\n",
+                        up, st.ms_total, st.ms_band, st.ms_unpack, st.ms_count, st.ms_stats, st.ms_finalize, gap, lag, st.chunks);
+            }
         } catch (const std::invalid_argument& e) {
             j.rc = NLDSC_ERR_INVALID; j.msg = e.what();
         } catch (const std::exception& e) {
@@ -1107,8 +1147,8 @@ int nldsc_ld_debug_unpack(const uint8_t* packed, int32_t n_snp, int32_t n_org, i
         struct Free { void* a; void* b; void* c; ~Free() { cudaFree(a); cudaFree(b); cudaFree(c); } } fr{d_packed, d_counts, d_planes};
         CUDA_CHECK(cudaMemset(d_packed + static_cast<size_t>(n_snp) * bps, 0, 16));
         CUDA_CHECK(cudaMemcpy(d_packed, packed, static_cast<size_t>(n_snp) * bps, cudaMemcpyHostToDevice));
-        launch_count(d_packed, bps, 0, n_snp, n_org, d_counts, nullptr);
-        launch_unpack(d_packed, bps, 0, n_snp, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, nullptr);
+        CUDA_CHECK(cudaMemset(d_counts, 0, sizeof(int32_t) * 3 * static_cast<size_t>(n_snp)));
+        launch_unpack(d_packed, bps, 0, n_snp, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, d_counts, nullptr);
         CUDA_CHECK(cudaDeviceSynchronize());
         if (counts_out)
             CUDA_CHECK(cudaMemcpy(counts_out, d_counts, sizeof(int32_t) * 3 * n_snp, cudaMemcpyDeviceToHost));
@@ -1152,7 +1192,7 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         CUDA_CHECK(cudaMemset(d_coef, 0, sizeof(SnpCoef) * rows));
         CUDA_CHECK(cudaMemset(d_flags, 0, rows));
         CUDA_CHECK(cudaMemset(d_w, 0, sizeof(int32_t) * 2 * rows));
-        launch_unpack(d_packed, bps, 0, n_snp, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, nullptr);
+        launch_unpack(d_packed, bps, 0, n_snp, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, nullptr, nullptr);
         Tile t{{i_block * kBlk, i_block * kBlk}, {i_block * kBlk, kDeadBlock}, j_block * kBlk, j_block * kBlk};
         CUDA_CHECK(cudaMemcpy(d_tile, &t, sizeof(t), cudaMemcpyHostToDevice));
         BandArgs a{};
@@ -1231,7 +1271,7 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         CUDA_CHECK(cudaMemset(d_coef, 0, sizeof(SnpCoef) * rows));
         CUDA_CHECK(cudaMemset(d_flags, 0, rows));                                        // every pair rejected: cheapest epilogue
         CUDA_CHECK(cudaMemset(d_w, 0, sizeof(int32_t) * 2 * rows));
-        launch_unpack(d_packed, bps, 0, rows, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, nullptr);
+        launch_unpack(d_packed, bps, 0, rows, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, nullptr, nullptr);
         std::vector<Tile> tiles(n_tiles);
         for (int32_t t = 0; t < n_tiles; ++t) {       // band-like walk: 22 j-blocks per i-block pair
             const int32_t p = (t / 22) % (nb / 2), jb = (2 * p + t % 22) % nb;

@@ -111,6 +111,7 @@ struct nldsc_ld_session {
     int32_t piece_rows = 0;                   // rows per upload piece (multiple of 64)
     std::vector<cudaEvent_t> ev_piece;        // piece has landed in d_packed
     cudaEvent_t ev_planned = nullptr;         // windows / tiles have landed
+    cudaEvent_t ev_up0 = nullptr, ev_up1 = nullptr;   // first / last byte of the upload (timing)
     // upload progress as seen by the host: run() may only wait on piece events that were recorded
     std::mutex up_mu;
     std::condition_variable up_cv;

@@ -1,7 +1,7 @@
 // PLINK .bed 2-bit decode, per-SNP genotype counts and per-SNP statistics.
 //
 // Replaces (reference, nldsc/ldscore/_ldscore/):
-//   BedStreamReader::read            stream.h:43-69    -> count_kernel / unpack_kernel
+//   BedStreamReader::read            stream.h:43-69    -> unpack_kernel (planes + genotype counts)
 //   SNPInMemory::decode + ctor       encoder.h:54-60,91-133
 //   Math::regression_residuals       tools.h:54-68     -> stats_kernel (closed forms over
 //   Math::var_ / standardise         tools.h:70-85        the three genotype counts)
@@ -24,47 +24,6 @@ __device__ __forceinline__ uint32_t tail_pair_mask(int n_org) {
     // bits of the LAST byte of a row that hold real samples (high n_org%4 pairs)
     const int r = n_org & 3;
     return r == 0 ? 0xFFu : ((0xFFu << (8 - 2 * r)) & 0xFFu);
-}
-
-// One warp per SNP row.  Rows start at arbitrary byte offsets, so the warp walks the
-// aligned 32-bit words that cover [b0, b1) and masks the bytes outside the row.
-__global__ void __launch_bounds__(256)
-count_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t row0, int32_t n_rows, int32_t n_org,
-             int32_t* __restrict__ counts) {
-    const int lane = threadIdx.x & 31;
-    int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (row >= n_rows) return;
-    row += row0;
-    const int64_t b0 = row * bps, b1 = b0 + bps;          // byte range of the row
-    const int64_t w0 = b0 >> 2, w1 = (b1 + 3) >> 2;       // covering word range
-    const uint32_t* __restrict__ words = reinterpret_cast<const uint32_t*>(packed);
-    const uint32_t tmask = tail_pair_mask(n_org);
-    int nh = 0, na = 0, nm = 0;
-    for (int64_t w = w0 + lane; w < w1; w += 32) {
-        uint32_t x = __ldg(words + w);
-        const int64_t wb = w << 2;
-        if (wb < b0) x &= 0xFFFFFFFFu << (8 * (int)(b0 - wb));
-        if (wb + 4 > b1) x &= 0xFFFFFFFFu >> (8 * (int)(wb + 4 - b1));
-        if (wb <= b1 - 1 && b1 - 1 < wb + 4) {             // word holds the row's last byte
-            const int sh = 8 * (int)(b1 - 1 - wb);
-            x &= ~(0xFFu << sh) | (tmask << sh);
-        }
-        const uint32_t lo = x & 0x55555555u, hi = (x >> 1) & 0x55555555u;
-        na += __popc(hi & lo);
-        nh += __popc(hi & ~lo);
-        nm += __popc(lo & ~hi);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        nh += __shfl_xor_sync(0xFFFFFFFFu, nh, o);
-        na += __shfl_xor_sync(0xFFFFFFFFu, na, o);
-        nm += __shfl_xor_sync(0xFFFFFFFFu, nm, o);
-    }
-    if (lane == 0) {
-        counts[row * 3 + 0] = nh;
-        counts[row * 3 + 1] = na;
-        counts[row * 3 + 2] = nm;
-    }
 }
 
 // One thread per SNP: everything the filters and the epilogue need, from three counts.
@@ -131,12 +90,14 @@ __device__ __forceinline__ void expand_byte(uint32_t b, uint32_t& g, uint32_t& m
 }
 
 // grid.x = rows, grid.y * blockDim.x covers npad/16 sixteen-organism groups.
-// Each thread turns 4 packed bytes into 16 bytes of each of the 4 planes (coalesced 16-B stores).
+// Each thread turns 4 packed bytes into 16 bytes of each of the 4 planes (coalesced 16-B stores) and,
+// when `counts` is given, popcounts the same word: the genotype counts of the row come out of the
+// pass that reads the bytes anyway (integer atomics: exact and order-independent).
 __global__ void __launch_bounds__(256)
 unpack_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t row0, int32_t n_org,
-              int32_t npad, int8_t* __restrict__ planes, int64_t plane_stride, int32_t dst_row0) {
+              int32_t npad, int8_t* __restrict__ planes, int64_t plane_stride, int32_t dst_row0,
+              int32_t* __restrict__ counts) {
     const int t = blockIdx.y * blockDim.x + threadIdx.x;      // 16-organism group
-    if (t * 16 >= npad) return;
     const int64_t row = (int64_t)row0 + blockIdx.x;
     const int64_t rb = (int64_t)t * 4;                         // row-relative first byte
     uint32_t x = 0;
@@ -155,16 +116,34 @@ unpack_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t row0, int
             x &= ~(0xFFu << s2) | (tail_pair_mask(n_org) << s2);
         }
     }
-    uint4 g, m, h, a;
-    expand_byte(x & 0xFFu, g.x, m.x, h.x, a.x);
-    expand_byte((x >> 8) & 0xFFu, g.y, m.y, h.y, a.y);
-    expand_byte((x >> 16) & 0xFFu, g.z, m.z, h.z, a.z);
-    expand_byte(x >> 24, g.w, m.w, h.w, a.w);
-    const int64_t off = ((int64_t)dst_row0 + blockIdx.x) * npad + (int64_t)t * 16;
-    *reinterpret_cast<uint4*>(planes + kPlaneG * plane_stride + off) = g;
-    *reinterpret_cast<uint4*>(planes + kPlaneM * plane_stride + off) = m;
-    *reinterpret_cast<uint4*>(planes + kPlaneH * plane_stride + off) = h;
-    *reinterpret_cast<uint4*>(planes + kPlaneA * plane_stride + off) = a;
+    if (t * 16 < npad) {
+        uint4 g, m, h, a;
+        expand_byte(x & 0xFFu, g.x, m.x, h.x, a.x);
+        expand_byte((x >> 8) & 0xFFu, g.y, m.y, h.y, a.y);
+        expand_byte((x >> 16) & 0xFFu, g.z, m.z, h.z, a.z);
+        expand_byte(x >> 24, g.w, m.w, h.w, a.w);
+        const int64_t off = ((int64_t)dst_row0 + blockIdx.x) * npad + (int64_t)t * 16;
+        *reinterpret_cast<uint4*>(planes + kPlaneG * plane_stride + off) = g;
+        *reinterpret_cast<uint4*>(planes + kPlaneM * plane_stride + off) = m;
+        *reinterpret_cast<uint4*>(planes + kPlaneH * plane_stride + off) = h;
+        *reinterpret_cast<uint4*>(planes + kPlaneA * plane_stride + off) = a;
+    }
+    if (counts != nullptr) {                                    // block-uniform
+        const uint32_t lo = x & 0x55555555u, hi = (x >> 1) & 0x55555555u;
+        // three counts <= 16 each in one register: bits 0-9 het, 10-19 hom-second, 20-29 missing
+        uint32_t c = __popc(hi & ~lo) | (__popc(hi & lo) << 10) | (__popc(lo & ~hi) << 20);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);    // <= 512 per field
+        __shared__ uint32_t part[8];
+        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = c;
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            uint32_t tot = 0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) tot += (part[w] >> (10 * threadIdx.x)) & 0x3FFu;
+            if (tot) atomicAdd(counts + row * 3 + threadIdx.x, (int32_t)tot);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -175,14 +154,6 @@ zero_rows_kernel(int8_t* __restrict__ planes, int64_t plane_stride, int32_t npad
     const uint4 z = make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int p = 0; p < kPlanes; ++p) *reinterpret_cast<uint4*>(planes + p * plane_stride + off) = z;
-}
-
-void launch_count(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows, int32_t n_org,
-                  int32_t* counts, cudaStream_t st) {
-    if (n_rows <= 0) return;
-    const int wpb = 8;
-    count_kernel<<<(n_rows + wpb - 1) / wpb, wpb * 32, 0, st>>>(packed, bps, row0, n_rows, n_org, counts);
-    CUDA_CHECK(cudaGetLastError());
 }
 
 void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
@@ -196,11 +167,11 @@ void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n
 
 void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
                    int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
-                   int32_t dst_row0, cudaStream_t st) {
+                   int32_t dst_row0, int32_t* counts, cudaStream_t st) {
     if (n_rows <= 0) return;
     const int groups = npad / 16;
     dim3 grid(n_rows, (groups + 255) / 256);
-    unpack_kernel<<<grid, 256, 0, st>>>(packed, bps, row0, n_org, npad, planes, plane_stride, dst_row0);
+    unpack_kernel<<<grid, 256, 0, st>>>(packed, bps, row0, n_org, npad, planes, plane_stride, dst_row0, counts);
     CUDA_CHECK(cudaGetLastError());
 }
 
