@@ -361,6 +361,7 @@ static void session_free(nldsc_ld_session* s) {
     // every buffer lives in the arena; make sure nothing queued still touches it before it is reused
     if (s->own_stream) cudaStreamSynchronize(s->own_stream);
     if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);
+    if (s->unpack_stream) cudaStreamSynchronize(s->unpack_stream);
     arena_release(s->arena);
     host_stage_release(s->stage);
     if (s->ev_planned) cudaEventDestroy(s->ev_planned);
@@ -369,6 +370,10 @@ static void session_free(nldsc_ld_session* s) {
     if (s->maps) band_maps_destroy(s->maps);
     for (auto& sp : s->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : s->ev_piece) cudaEventDestroy(e);
+    for (auto e : s->ev_unpacked) cudaEventDestroy(e);
+    for (auto e : s->ev_band) cudaEventDestroy(e);
+    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+    if (s->unpack_stream) cudaStreamDestroy(s->unpack_stream);
     if (s->ev_run0) cudaEventDestroy(s->ev_run0);
     if (s->ev_run1) cudaEventDestroy(s->ev_run1);
     if (s->own_stream) cudaStreamDestroy(s->own_stream);
@@ -405,8 +410,13 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     s->n_load = load_end - load_begin;
 
     s->d_packed = amalloc<uint8_t>(s->arena, static_cast<size_t>(s->n_load) * s->bps + 16);
-    CUDA_CHECK(cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking));
+    // the band kernel's CTAs go first; unpack blocks fill the thread slots that are left on every SM
+    int prio_lo = 0, prio_hi = 0;
+    CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    CUDA_CHECK(cudaStreamCreateWithPriority(&s->own_stream, cudaStreamNonBlocking, prio_hi));
     CUDA_CHECK(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
+    CUDA_CHECK(cudaStreamCreateWithPriority(&s->unpack_stream, cudaStreamNonBlocking, prio_lo));
+    CUDA_CHECK(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
     // the 16 bytes of slack the word-wise kernels may read past the last row
     CUDA_CHECK(cudaMemsetAsync(s->d_packed + static_cast<size_t>(s->n_load) * s->bps, 0, 16, s->copy_stream));
     // upload granularity: ~8 MB pieces, a whole number of 64-row blocks each
@@ -596,7 +606,10 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     const int32_t chunk_rows = static_cast<int32_t>(
         std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? 16384 : 32768),
                          static_cast<size_t>(std::numeric_limits<int32_t>::max() / 2)));
-    int32_t ramp_rows = (ramp && !fixed_rows) ? 4096 : chunk_rows;
+    // without a concurrent upload a short first chunk still pays: its unpack is the only one that runs alone
+    const char* rp = getenv("NLDSC_RAMP");
+    const bool ramp0 = rp ? rp[0] != '0' : true;
+    int32_t ramp_rows = (ramp0 && !fixed_rows) ? (ramp ? 4096 : 8192) : chunk_rows;
     const int32_t wave = std::max(1, s->sm_count / 2);       // supertiles scored concurrently (one per CTA pair)
     std::vector<Tile>& tiles = s->h_tiles;
     std::vector<int32_t>& tile_begin = s->h_tile_begin;
@@ -712,6 +725,23 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     if (st != s->own_stream) CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_planned, 0));
     CUDA_CHECK(cudaEventRecord(s->ev_run0, st));
     const double n = static_cast<double>(s->n_org);
+    // Two streams: unpack + stats of the next chunk (HBM-bound, no shared memory) run beside the band
+    // kernel of the current one (tensor / L2-bound, one persistent CTA per SM) -- NLDSC_OVERLAP=0 puts
+    // everything back on the compute stream.
+    const char* ov = getenv("NLDSC_OVERLAP");
+    const bool overlap = !(ov && ov[0] == '0');
+    cudaStream_t us = overlap ? s->unpack_stream : st;
+    if (overlap) {
+        CUDA_CHECK(cudaEventRecord(s->ev_fork, st));
+        CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_fork, 0));
+        while (s->ev_unpacked.size() < s->chunks.size()) {
+            cudaEvent_t e;
+            CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            s->ev_unpacked.push_back(e);
+            CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            s->ev_band.push_back(e);
+        }
+    }
     for (size_t ci = 0; ci < s->chunks.size(); ++ci) {
         const Chunk& c = s->chunks[ci];
         const int32_t r0 = std::min(c.new_row0, s->n_load), r1 = std::min(c.new_row1, s->n_load);
@@ -724,21 +754,37 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
                 s->up_cv.wait(g, [&] { return s->pieces_issued > piece; });
                 if (!s->up_error.empty()) throw CudaError(s->up_error);
             }
-            CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_piece[piece], 0));
+            CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_piece[piece], 0));
+        }
+        if (overlap && c.new_row1 > c.new_row0) {
+            // ring hazard: rows [new_row0, new_row1) land in the slots of rows `plane_rows` earlier; the
+            // latest earlier chunk that still reads any of those must have finished its band kernel
+            const int64_t first_safe = static_cast<int64_t>(c.new_row1) - s->plane_rows;   // rows below are overwritten
+            int64_t wait_for = -1;
+            for (size_t k = 0; k < ci; ++k) {
+                const Chunk& e = s->chunks[k];
+                const int64_t col0 = static_cast<int64_t>(s->h_tiles[e.tile0].j0);          // first column the chunk reads
+                if (col0 < first_safe) wait_for = static_cast<int64_t>(k);
+            }
+            if (wait_for >= 0) CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_band[wait_for], 0));
         }
         {
             // unpack the chunk's new rows into the ring; the same pass counts their genotypes
-            SpanScope sc(s, st, kFamUnpack);
+            SpanScope sc(s, us, kFamUnpack);
             if (r1 > r0)
                 CUDA_CHECK(cudaMemsetAsync(s->d_counts + static_cast<size_t>(r0) * 3, 0,
-                                           sizeof(int32_t) * 3 * static_cast<size_t>(r1 - r0), st));
-            unpack_rows(s, c.new_row0, c.new_row1, st);
+                                           sizeof(int32_t) * 3 * static_cast<size_t>(r1 - r0), us));
+            unpack_rows(s, c.new_row0, c.new_row1, us);
         }
         if (r1 > r0) {
-            SpanScope sc(s, st, kFamStats);
+            SpanScope sc(s, us, kFamStats);
             launch_stats(s->d_counts, r0, r1 - r0, s->n_org, s->maf_thr, s->std_thr, s->d_coef, s->d_flags,
-                         s->d_maf, s->d_rstd, st);
+                         s->d_maf, s->d_rstd, us);
             ++s->launches;
+        }
+        if (overlap) {
+            CUDA_CHECK(cudaEventRecord(s->ev_unpacked[ci], us));
+            CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_unpacked[ci], 0));
         }
         BandArgs a{};
         a.tiles = s->d_tiles + c.tile0;
@@ -763,6 +809,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
                 launch_band_tc(s->maps, a, s->sm_count, st);
             ++s->launches;
         }
+        if (overlap) CUDA_CHECK(cudaEventRecord(s->ev_band[ci], st));
         FinalizeArgs f{};
         f.tile_begin = s->d_tile_begin + c.tb0;
         f.iblock0 = c.iblock0;

@@ -108,6 +108,10 @@ struct nldsc_ld_session {
     nldsc::BandMaps* maps = nullptr;
     cudaStream_t own_stream = nullptr;        // compute
     cudaStream_t copy_stream = nullptr;       // H2D of packed rows, piece by piece
+    cudaStream_t unpack_stream = nullptr;     // unpack + stats of chunk c+1 run beside the band kernel of chunk c
+    std::vector<cudaEvent_t> ev_unpacked;     // per chunk: planes, coefficients and flags are ready
+    std::vector<cudaEvent_t> ev_band;         // per chunk: the band kernel no longer reads its ring rows
+    cudaEvent_t ev_fork = nullptr;            // run() start on the compute stream, seen by the unpack stream
     int32_t piece_rows = 0;                   // rows per upload piece (multiple of 64)
     std::vector<cudaEvent_t> ev_piece;        // piece has landed in d_packed
     cudaEvent_t ev_planned = nullptr;         // windows / tiles have landed

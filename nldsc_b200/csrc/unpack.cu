@@ -79,6 +79,11 @@ stats_kernel(const int32_t* __restrict__ counts, int32_t row0, int32_t n_rows, i
     rstd_out[row] = rsd_out;
 }
 
+#ifndef NLDSC_STREAM_STORES
+#define NLDSC_STREAM_STORES 1
+#endif
+constexpr bool kStreamStores = NLDSC_STREAM_STORES != 0;
+
 // byte with four 2-bit genotype codes -> one 32-bit word per plane, byte k = sample k
 __device__ __forceinline__ void expand_byte(uint32_t b, uint32_t& g, uint32_t& m, uint32_t& h, uint32_t& a) {
     const uint32_t p = (b | (b << 6) | (b << 12) | (b << 18)) & 0x03030303u;
@@ -87,6 +92,14 @@ __device__ __forceinline__ void expand_byte(uint32_t b, uint32_t& g, uint32_t& m
     h = hi ^ a;           // 10 het
     m = lo ^ a;           // 01 missing
     g = hi + a;           // additive dosage 0/1/2
+}
+
+// Plane rows are written once and next read by the band kernel's TMA loads, usually after far more than an
+// L2's worth of other rows: store them evict-first so they do not displace the operand tiles the band
+// kernel of the previous chunk (running beside this kernel) is re-reading from L2.
+__device__ __forceinline__ void st_plane(int8_t* p, const uint4& v) {
+    if (kStreamStores) __stcs(reinterpret_cast<uint4*>(p), v);
+    else *reinterpret_cast<uint4*>(p) = v;
 }
 
 // grid.x = rows, grid.y * blockDim.x covers npad/16 sixteen-organism groups.
@@ -123,10 +136,10 @@ unpack_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t row0, int
         expand_byte((x >> 16) & 0xFFu, g.z, m.z, h.z, a.z);
         expand_byte(x >> 24, g.w, m.w, h.w, a.w);
         const int64_t off = ((int64_t)dst_row0 + blockIdx.x) * npad + (int64_t)t * 16;
-        *reinterpret_cast<uint4*>(planes + kPlaneG * plane_stride + off) = g;
-        *reinterpret_cast<uint4*>(planes + kPlaneM * plane_stride + off) = m;
-        *reinterpret_cast<uint4*>(planes + kPlaneH * plane_stride + off) = h;
-        *reinterpret_cast<uint4*>(planes + kPlaneA * plane_stride + off) = a;
+        st_plane(planes + kPlaneG * plane_stride + off, g);
+        st_plane(planes + kPlaneM * plane_stride + off, m);
+        st_plane(planes + kPlaneH * plane_stride + off, h);
+        st_plane(planes + kPlaneA * plane_stride + off, a);
     }
     if (counts != nullptr) {                                    // block-uniform
         const uint32_t lo = x & 0x55555555u, hi = (x >> 1) & 0x55555555u;
