@@ -8,6 +8,8 @@
 // calculate call -- nothing can be scored before the band plan exists.
 #include "common.cuh"
 
+#include <algorithm>
+
 namespace nldsc {
 
 __global__ void __launch_bounds__(256)
@@ -34,6 +36,24 @@ windows_kernel(const double* __restrict__ pos, int32_t n, double wind, int32_t* 
 void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st) {
     if (n <= 0) return;
     windows_kernel<<<(n + 255) / 256, 256, 0, st>>>(pos, n, wind, lo, hi);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+// Small-array transport that stays off the copy engines: while a shard's packed rows are queued on the
+// H2D engine (hundreds of MB, FIFO), a cudaMemcpy of the band plan would wait behind all of them.  The SMs
+// read / write pinned host memory directly instead (UVA), sharing PCIe with the bulk upload.
+__global__ void __launch_bounds__(256)
+copy16_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, size_t n16) {
+    for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n16;
+         i += static_cast<size_t>(gridDim.x) * blockDim.x)
+        dst[i] = src[i];
+}
+
+void launch_copy16(const void* src, void* dst, size_t bytes, cudaStream_t st) {
+    const size_t n16 = (bytes + 15) / 16;       // both buffers are padded to 16 bytes by their allocators
+    if (n16 == 0) return;
+    const int blocks = static_cast<int>(std::min<size_t>((n16 + 255) / 256, 1184));
+    copy16_kernel<<<blocks, 256, 0, st>>>(static_cast<const uint4*>(src), static_cast<uint4*>(dst), n16);
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -220,6 +220,50 @@ void host_stage_release(HostStage* h) {
 }
 
 namespace {
+PlanStage* g_pstage[kMaxDevices] = {nullptr};
+bool g_pstage_busy[kMaxDevices] = {false};
+}  // namespace
+
+void PlanStage::reserve(size_t need) {
+    if (need <= bytes) return;
+    if (base) cudaFreeHost(base);
+    base = nullptr;
+    bytes = 0;
+    const size_t want = need + need / 4 + 4096;
+    void* q = nullptr;
+    if (cudaHostAlloc(&q, want, cudaHostAllocPortable) != cudaSuccess) throw CudaError("cudaHostAlloc of the plan staging buffer failed");
+    base = static_cast<char*>(q);
+    bytes = want;
+}
+
+PlanStage* plan_stage_acquire(int device) {
+    std::lock_guard<std::mutex> g(g_arena_mu);
+    if (device >= 0 && device < kMaxDevices && !g_pstage_busy[device]) {
+        g_pstage_busy[device] = true;
+        if (!g_pstage[device]) {
+            g_pstage[device] = new PlanStage;
+            g_pstage[device]->device = device;
+            g_pstage[device]->cached = true;
+        }
+        return g_pstage[device];
+    }
+    PlanStage* h = new PlanStage;       // the device's cached buffer is in use: a private one
+    h->device = device;
+    return h;
+}
+
+void plan_stage_release(PlanStage* h) {
+    if (!h) return;
+    if (h->cached) {
+        std::lock_guard<std::mutex> g(g_arena_mu);
+        g_pstage_busy[h->device] = false;
+        return;
+    }
+    if (h->base) cudaFreeHost(h->base);
+    delete h;
+}
+
+namespace {
 
 void set_err(char* err, size_t errlen, const char* msg) {
     if (err && errlen) {
@@ -364,6 +408,7 @@ static void session_free(nldsc_ld_session* s) {
     if (s->unpack_stream) cudaStreamSynchronize(s->unpack_stream);
     arena_release(s->arena);
     host_stage_release(s->stage);
+    plan_stage_release(s->pstage);
     if (s->ev_planned) cudaEventDestroy(s->ev_planned);
     if (s->ev_up0) cudaEventDestroy(s->ev_up0);
     if (s->ev_up1) cudaEventDestroy(s->ev_up1);
@@ -395,6 +440,7 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     nldsc_ld_session* s = sp.get();
     s->device = device;
     s->arena = arena_acquire(device);
+    s->pstage = plan_stage_acquire(device);
     s->sm_count = device_sm_count(device);
     s->n_org = p->n_org;
     s->n_snp = p->n_snp;
@@ -570,8 +616,6 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     s->d_wsa = amalloc<int32_t>(s->arena, n_own);
     s->d_wsd = amalloc<int32_t>(s->arena, n_own);
     s->d_wsde = amalloc<int32_t>(s->arena, n_own);
-    CUDA_CHECK(cudaMemcpyAsync(s->d_win_lo, wlo.data(), sizeof(int32_t) * n_load_pad, cudaMemcpyHostToDevice, st));
-    CUDA_CHECK(cudaMemcpyAsync(s->d_win_hi, whi.data(), sizeof(int32_t) * n_load_pad, cudaMemcpyHostToDevice, st));
     tr.lap("fixed buffers");
 
     // ---- plane ring: as many SNP rows as needed, within the memory budget (4 int8 planes each)
@@ -609,7 +653,19 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // without a concurrent upload a short first chunk still pays: its unpack is the only one that runs alone
     const char* rp = getenv("NLDSC_RAMP");
     const bool ramp0 = rp ? rp[0] != '0' : true;
-    int32_t ramp_rows = (ramp0 && !fixed_rows) ? (ramp ? 4096 : 8192) : chunk_rows;
+    // first chunk with a concurrent upload: what has landed by the time the plan is built and shipped
+    // (~0.7 ms of PCIe, ~40 MB), so its kernels neither wait for data nor start needlessly small
+    const int64_t landed = static_cast<int64_t>(env_size("NLDSC_FIRST_BYTES", size_t(40) << 20)) / std::max<int64_t>(1, s->bps);
+    const int32_t first_rows = static_cast<int32_t>(std::min<int64_t>(chunk_rows, std::max<int64_t>(4096, landed / 4096 * 4096)));
+    int32_t ramp_rows = (ramp0 && !fixed_rows) ? (ramp ? first_rows : 8192) : chunk_rows;
+    const char* tp = getenv("NLDSC_TAPER");
+    // taper the chunk size towards the end of the shard only when the upload is clearly the longer pole
+    // (narrow windows / few organisms): then the last chunk starts when the last byte lands and its length
+    // is the tail.  Rough rates: 2.6e15 executed int8 op/s in the band kernel, 54 GB/s over PCIe gen5.
+    const double n_own_rows = std::max(1, s->own_end - s->own_begin);
+    const double compute_ns_row = (static_cast<double>(s->total_pairs) / n_own_rows + 3.0 * kBlk) * s->npad * 12.0 / 2.6e6;
+    const double upload_ns_row = static_cast<double>(s->bps) / 54.0;
+    const bool taper = ramp && !fixed_rows && (tp ? tp[0] != '0' : compute_ns_row < 0.7 * upload_ns_row);
     const int32_t wave = std::max(1, s->sm_count / 2);       // supertiles scored concurrently (one per CTA pair)
     std::vector<Tile>& tiles = s->h_tiles;
     std::vector<int32_t>& tile_begin = s->h_tile_begin;
@@ -624,7 +680,10 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         c.tile0 = static_cast<int64_t>(tiles.size());
         c.tb0 = static_cast<int32_t>(tile_begin.size());
         const int32_t col0 = jb_lo[b] * kBlk;
-        const int32_t target = std::min(ramp_rows, chunk_rows);
+        int32_t target = std::min(ramp_rows, chunk_rows);
+        // with a concurrent upload the last chunk cannot start before the last byte has landed: taper the
+        // chunk size towards the end of the shard so that tail is short
+        if (taper) target = std::min(target, std::max(4096, (n_ib - b) * kBlk / 2 / 4096 * 4096));
         int32_t e = b;
         while (e < n_ib) {
             const int32_t col1 = (jb_hi[e] + 1) * kBlk;
@@ -681,9 +740,23 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     s->total_tiles = static_cast<int64_t>(tiles.size());
     s->d_tiles = amalloc<Tile>(s->arena, tiles.size());
     s->d_tile_begin = amalloc<int32_t>(s->arena, tile_begin.size());
-    CUDA_CHECK(cudaMemcpyAsync(s->d_tiles, tiles.data(), sizeof(Tile) * tiles.size(), cudaMemcpyHostToDevice, st));
-    CUDA_CHECK(cudaMemcpyAsync(s->d_tile_begin, tile_begin.data(), sizeof(int32_t) * tile_begin.size(),
-                               cudaMemcpyHostToDevice, st));
+    {
+        // plan arrays -> pinned staging -> device by an SM copy: the H2D copy engine is busy with (or about to
+        // be queued full of) the shard's packed rows, and these few MB must not wait behind them
+        auto pad16 = [](size_t b) { return (b + 15) & ~size_t(15); };
+        const size_t b_win = pad16(sizeof(int32_t) * n_load_pad), b_tiles = pad16(sizeof(Tile) * tiles.size()),
+                     b_tb = pad16(sizeof(int32_t) * tile_begin.size());
+        s->pstage->reserve(2 * b_win + b_tiles + b_tb);
+        char* h = s->pstage->base;
+        memcpy(h, wlo.data(), sizeof(int32_t) * n_load_pad);
+        memcpy(h + b_win, whi.data(), sizeof(int32_t) * n_load_pad);
+        memcpy(h + 2 * b_win, tiles.data(), sizeof(Tile) * tiles.size());
+        memcpy(h + 2 * b_win + b_tiles, tile_begin.data(), sizeof(int32_t) * tile_begin.size());
+        launch_copy16(h, s->d_win_lo, b_win, st);
+        launch_copy16(h + b_win, s->d_win_hi, b_win, st);
+        launch_copy16(h + 2 * b_win, s->d_tiles, b_tiles, st);
+        launch_copy16(h + 2 * b_win + b_tiles, s->d_tile_begin, b_tb, st);
+    }
     const size_t np = static_cast<size_t>(s->max_chunk_tiles) * 2 * kBlk;
     s->part.add = amalloc<double>(s->arena, np);
     s->part.dom = amalloc<double>(s->arena, np);
@@ -904,15 +977,18 @@ int first_device_from_env() {
     return (v && *v) ? atoi(v) : 0;
 }
 
-// compute_windows on the device (plan.cu): positions up, two int32 arrays back.  Scratch is cached per device.
-void compute_windows_device(int device, const double* pos, int32_t n, double wind, std::vector<int32_t>& lo,
-                            std::vector<int32_t>& hi) {
+// compute_windows on the device (plan.cu).  Positions go up and the two int32 arrays come back through
+// pinned staging and SM copies on `st`, never the copy engines: a shard's bulk upload may already be queued
+// there.  Device scratch is cached per device.
+void compute_windows_device(int device, PlanStage* ps, cudaStream_t st, const double* pos, int32_t n, double wind,
+                            std::vector<int32_t>& lo, std::vector<int32_t>& hi) {
     static std::mutex mu;
     static void* scratch[64] = {nullptr};
     static size_t scratch_bytes[64] = {0};
     std::lock_guard<std::mutex> g(mu);
     CUDA_CHECK(cudaSetDevice(device));
-    const size_t need = static_cast<size_t>(n) * 16;
+    const size_t n2 = (static_cast<size_t>(n) + 1) & ~size_t(1), n4 = (static_cast<size_t>(n) + 3) & ~size_t(3);
+    const size_t b_pos = n2 * sizeof(double), b_idx = n4 * sizeof(int32_t), need = b_pos + 2 * b_idx;
     void*& buf = scratch[device & 63];
     if (scratch_bytes[device & 63] < need) {
         if (buf) cudaFree(buf);
@@ -921,15 +997,18 @@ void compute_windows_device(int device, const double* pos, int32_t n, double win
         CUDA_CHECK(cudaMalloc(&buf, need + need / 4));
         scratch_bytes[device & 63] = need + need / 4;
     }
-    double* d_pos = static_cast<double*>(buf);
-    int32_t* d_lo = reinterpret_cast<int32_t*>(d_pos + n);
-    int32_t* d_hi = d_lo + n;
+    char* d = static_cast<char*>(buf);
+    ps->reserve(need);
+    memcpy(ps->base, pos, sizeof(double) * n);
+    launch_copy16(ps->base, d, b_pos, st);
+    launch_windows(reinterpret_cast<const double*>(d), n, wind, reinterpret_cast<int32_t*>(d + b_pos),
+                   reinterpret_cast<int32_t*>(d + b_pos + b_idx), st);
+    launch_copy16(d + b_pos, ps->base + b_pos, 2 * b_idx, st);
+    CUDA_CHECK(cudaStreamSynchronize(st));
     lo.resize(n);
     hi.resize(n);
-    CUDA_CHECK(cudaMemcpy(d_pos, pos, sizeof(double) * n, cudaMemcpyHostToDevice));
-    launch_windows(d_pos, n, wind, d_lo, d_hi, nullptr);
-    CUDA_CHECK(cudaMemcpy(lo.data(), d_lo, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
-    CUDA_CHECK(cudaMemcpy(hi.data(), d_hi, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
+    memcpy(lo.data(), ps->base + b_pos, sizeof(int32_t) * n);
+    memcpy(hi.data(), ps->base + b_pos + b_idx, sizeof(int32_t) * n);
 }
 
 // `start_upload(session)` begins the asynchronous H2D of the session's packed rows [load_begin, load_end)
@@ -953,18 +1032,22 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
         return std::chrono::duration<double, std::milli>(b - a).count();
     };
     std::vector<int32_t> lo, hi;
+    const bool whole = parts == 1;
 
     auto work = [&](ShardJob& j) {      // one shard on one GPU
         nldsc_ld_session* s = nullptr;
         const auto t0 = now();
         auto t1 = t0, t2 = t0, t3 = t0, t4 = t0, t5 = t0;
         try {
-            s = session_open(j.device, p, floor64(lo[j.row_begin]), hi[j.row_end - 1] + 1);
+            // one shard = the whole file: its load range needs no windows, so the packed rows start crossing
+            // PCIe before anything is planned (windows and plan travel by SM copies, not the copy engine)
+            if (whole) s = session_open(j.device, p, 0, p->n_snp);
+            else s = session_open(j.device, p, floor64(lo[j.row_begin]), hi[j.row_end - 1] + 1);
             t1 = now();
-            // plan first: its small H2D copies must not queue behind the bulk upload on the copy engine
-            session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true);
-            t2 = now();
             start_upload(s);
+            t2 = now();
+            if (whole) compute_windows_device(j.device, s->pstage, s->own_stream, p->positions, p->n_snp, p->ld_wind, lo, hi);
+            session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true);
             t3 = now();
             session_run(s, nullptr);
             t4 = now();
@@ -992,19 +1075,30 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
         }
         session_free(s);
         if (trace)
-            fprintf(stderr, "[nldsc_ld] gpu %d rows [%d,%d): open %.2f ms, plan %.2f, upload-start %.2f, run-issue %.2f, "
+            fprintf(stderr, "[nldsc_ld] gpu %d rows [%d,%d): open %.2f ms, upload-start %.2f, windows+plan %.2f, run-issue %.2f, "
                             "download+sync %.2f, free %.2f\n",
                     j.device, j.row_begin, j.row_end, ms(t0, t1), ms(t1, t2), ms(t2, t3), ms(t3, t4), ms(t4, t5),
                     ms(t5, now()));
     };
 
     require_sm100(dev0);
-    compute_windows_device(dev0, p->positions, p->n_snp, p->ld_wind, lo, hi);
-    tr.lap("windows (device)");
-    const std::vector<int32_t> cut = split_rows(lo, hi, parts);
     std::vector<ShardJob> jobs;
-    for (int k = 0; k < parts; ++k)
-        if (cut[k + 1] > cut[k]) jobs.push_back({dev0 + k, cut[k], cut[k + 1]});
+    if (whole) {
+        jobs.push_back({dev0, 0, p->n_snp});
+    } else {
+        PlanStage* ps = plan_stage_acquire(dev0);
+        try {
+            compute_windows_device(dev0, ps, nullptr, p->positions, p->n_snp, p->ld_wind, lo, hi);
+        } catch (...) {
+            plan_stage_release(ps);
+            throw;
+        }
+        plan_stage_release(ps);
+        tr.lap("windows (device)");
+        const std::vector<int32_t> cut = split_rows(lo, hi, parts);
+        for (int k = 0; k < parts; ++k)
+            if (cut[k + 1] > cut[k]) jobs.push_back({dev0 + k, cut[k], cut[k + 1]});
+    }
     if (jobs.size() == 1) {
         work(jobs[0]);
     } else {
@@ -1282,7 +1376,14 @@ int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* l
         const int dev = first_device_from_env();
         require_sm100(dev);
         std::vector<int32_t> l, h;
-        compute_windows_device(dev, params->positions, params->n_snp, params->ld_wind, l, h);
+        PlanStage* ps = plan_stage_acquire(dev);
+        try {
+            compute_windows_device(dev, ps, nullptr, params->positions, params->n_snp, params->ld_wind, l, h);
+        } catch (...) {
+            plan_stage_release(ps);
+            throw;
+        }
+        plan_stage_release(ps);
         std::copy(l.begin(), l.end(), lo);
         std::copy(h.begin(), h.end(), hi);
     });

@@ -62,6 +62,18 @@ struct HostStage {
 HostStage* host_stage_acquire(int device);
 void host_stage_release(HostStage* h);
 
+// Pinned staging for the small planning arrays (positions up, windows back, band plan up), moved by
+// launch_copy16 instead of the copy engines; cached per device and grown on demand.
+struct PlanStage {
+    int device = -1;
+    bool cached = false;
+    char* base = nullptr;
+    size_t bytes = 0;
+    void reserve(size_t need);    // contents are lost when the buffer grows
+};
+PlanStage* plan_stage_acquire(int device);
+void plan_stage_release(PlanStage* h);
+
 enum Family { kFamCount = 0, kFamStats, kFamUnpack, kFamBand, kFamFinalize, kFamN };
 
 }  // namespace nldsc
@@ -123,6 +135,7 @@ struct nldsc_ld_session {
     std::string up_error;
     std::thread reader;                       // .bed reader (nldsc_ld_calculate only)
     nldsc::HostStage* stage = nullptr;
+    nldsc::PlanStage* pstage = nullptr;
     // host copies of the plan (sources of the asynchronous H2D copies)
     std::vector<int32_t> h_win_lo, h_win_hi, h_tile_begin;
     std::vector<nldsc::Tile> h_tiles;
