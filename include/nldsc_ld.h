@@ -60,6 +60,13 @@ typedef struct nldsc_ld_result {
  * halo, one host thread per GPU, no collective; results gathered host-side. */
 int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char* err, size_t errlen);
 
+/* nldsc_ld_calculate with the GPUs named by the caller instead of the environment: shards go to devices
+ * first_device .. first_device + n_devices - 1.  Lets ONE process score several chromosome bfiles at the
+ * same time, one host thread and one GPU (or GPU group) each -- the multi-chromosome driver of SURVEY.md
+ * section 8(f)-3; the reference handles one chromosome per invocation (ldscore/common.py:114-117). */
+int nldsc_ld_calculate_on(const nldsc_ld_params* params, nldsc_ld_result* out, int32_t first_device,
+                          int32_t n_devices, char* err, size_t errlen);
+
 /* Same computation from a host buffer holding the genotype bytes of the .bed
  * WITHOUT its 3-byte magic: n_snp rows of ceil(n_org/4) bytes (what
  * BedStreamReader::read consumes, stream.h:43-69). */

@@ -23,6 +23,7 @@ EXPORTS = [
     "nldsc_ld_session_sync", "nldsc_ld_session_stats", "nldsc_ld_session_destroy",
     "nldsc_ld_debug_unpack", "nldsc_ld_debug_cross_counts", "nldsc_ld_device_count",
     "nldsc_ld_plan_windows", "nldsc_ld_plan_shards", "nldsc_ld_debug_band_probe", "nldsc_ld_debug_plan_windows_device",
+    "nldsc_ld_calculate_on",
 ]
 
 
@@ -153,6 +154,16 @@ def calculate(bedfile, n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr) 
     out, r = alloc_result(n_snp)
     err = C.create_string_buffer(512)
     _raise(lib().nldsc_ld_calculate(C.byref(p), C.byref(r), err, C.c_size_t(512)), err)
+    return out
+
+
+def calculate_on(bedfile, n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr, first_device, n_devices=1) -> dict:
+    """nldsc_ld_calculate on GPUs first_device .. first_device + n_devices - 1 (thread-safe placement)."""
+    p = make_params(n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr, bedfile)
+    out, r = alloc_result(n_snp)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_calculate_on(C.byref(p), C.byref(r), C.c_int32(first_device), C.c_int32(n_devices), err,
+                                       C.c_size_t(512)), err)
     return out
 
 

@@ -6,6 +6,7 @@
 // forwards to the C ABI in include/nldsc_ld.h; nothing here computes.  Error mapping follows
 // the reference: std::invalid_argument -> ValueError (bad PLINK magic, stream.h:97-101),
 // std::runtime_error -> RuntimeError.  Unlike the reference the GIL is released for the call.
+#include <pybind11/numpy.h>
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
 
@@ -37,7 +38,7 @@ struct LDScoreResult {
     std::vector<int> l2_ws, l2d_ws, l2d_wse;
 };
 
-LDScoreResult calculate(LDScoreParams& p) {
+LDScoreResult calculate_impl(LDScoreParams& p, int first_device, int n_devices) {
     if (static_cast<long long>(p.positions.size()) != p.n_snp)
         throw std::invalid_argument("positions must hold n_snp coordinates");
     LDScoreResult r;
@@ -60,11 +61,22 @@ LDScoreResult calculate(LDScoreParams& p) {
     int rc;
     {
         py::gil_scoped_release nogil;
-        rc = nldsc_ld_calculate(&cp, &cr, err, sizeof(err));
+        rc = n_devices > 0 ? nldsc_ld_calculate_on(&cp, &cr, first_device, n_devices, err, sizeof(err))
+                           : nldsc_ld_calculate(&cp, &cr, err, sizeof(err));
     }
     if (rc == NLDSC_ERR_INVALID) throw std::invalid_argument(err);
     if (rc != NLDSC_OK) throw std::runtime_error(err);
     return r;
+}
+
+LDScoreResult calculate(LDScoreParams& p) { return calculate_impl(p, -1, 0); }
+
+// NumPy view of one result vector; the array keeps the LDScoreResult alive, nothing is copied.
+// The list attributes of the reference surface copy the whole vector into a new list on every read
+// (ldscore.cpp:43-51) -- seconds at 1.2M SNPs; these do not.
+template <class T>
+py::array_t<T> view(py::object owner, std::vector<T>& v) {
+    return py::array_t<T>({static_cast<py::ssize_t>(v.size())}, {static_cast<py::ssize_t>(sizeof(T))}, v.data(), owner);
 }
 
 }  // namespace
@@ -100,4 +112,16 @@ PYBIND11_MODULE(_ldscore, m) {
         .def_readwrite("l2d_ws", &LDScoreResult::l2d_ws)
         .def_readwrite("l2d_wse", &LDScoreResult::l2d_wse);
     m.def("calculate", &calculate, py::arg("params"));
+    // ---- additions beside the reference surface (names above are unchanged) ----
+    m.def("calculate_on", &calculate_impl, py::arg("params"), py::arg("first_device"), py::arg("n_devices") = 1,
+          "calculate() on GPUs first_device .. first_device + n_devices - 1 instead of NLDSC_DEVICE / NLDSC_GPUS; "
+          "thread-safe, so one process can score several chromosomes at once");
+    m.def("as_arrays", [](py::object r) {
+        LDScoreResult& v = r.cast<LDScoreResult&>();
+        py::dict d;
+        d["l2"] = view(r, v.l2); d["l2d"] = view(r, v.l2d); d["maf"] = view(r, v.maf);
+        d["residuals_std"] = view(r, v.residuals_std);
+        d["l2_ws"] = view(r, v.l2_ws); d["l2d_ws"] = view(r, v.l2d_ws); d["l2d_wse"] = view(r, v.l2d_wse);
+        return d;
+    }, py::arg("result"), "zero-copy NumPy views of the seven result vectors");
 }

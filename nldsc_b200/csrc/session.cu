@@ -961,7 +961,12 @@ struct ShardJob {
     std::string msg;
 };
 
+// placement chosen by the caller of nldsc_ld_calculate_on for the calls made on this thread
+thread_local int tl_first_device = -1;
+thread_local int tl_n_devices = 0;
+
 int gpus_from_env(int available) {
+    if (tl_n_devices > 0) return std::min(tl_n_devices, available);
     const char* v = getenv("NLDSC_GPUS");
     int want = 1;
     if (v && *v) {
@@ -973,6 +978,7 @@ int gpus_from_env(int available) {
 }
 
 int first_device_from_env() {
+    if (tl_first_device >= 0) return tl_first_device;
     const char* v = getenv("NLDSC_DEVICE");
     return (v && *v) ? atoi(v) : 0;
 }
@@ -1184,6 +1190,26 @@ int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char
         // every shard streams its own byte range: reader thread -> pinned slot ring -> H2D (session_upload_file)
         run_sharded(params, out, [&](nldsc_ld_session* s) { session_upload_file(s, fd); });
     });
+}
+
+int nldsc_ld_calculate_on(const nldsc_ld_params* params, nldsc_ld_result* out, int32_t first_device, int32_t n_devices,
+                          char* err, size_t errlen) {
+    if (first_device < 0 || n_devices < 1) {
+        set_err(err, errlen, "first_device must be >= 0 and n_devices >= 1");
+        return NLDSC_ERR_INVALID;
+    }
+    struct Placement {
+        Placement(int d, int n) { tl_first_device = d; tl_n_devices = n; }
+        ~Placement() { tl_first_device = -1; tl_n_devices = 0; }
+    } placement(first_device, n_devices);
+    int32_t have = 0;
+    const int rc = nldsc_ld_device_count(&have, err, errlen);
+    if (rc != NLDSC_OK) return rc;
+    if (first_device >= have) {
+        set_err(err, errlen, "first_device is not a usable CUDA device");
+        return NLDSC_ERR_RUNTIME;
+    }
+    return nldsc_ld_calculate(params, out, err, errlen);
 }
 
 int nldsc_ld_session_create(nldsc_ld_session** out, int device, const nldsc_ld_params* params, int32_t row_begin,

@@ -10,10 +10,19 @@ the reference tree: `python -m nldsc_b200 ld --bfile ... --ld-wind-cm ... -maf .
   make_output (column layout)    ldscore/routine.py:32-48
   window / threshold validation  ldscore/common.py:10-36,146-182
   .bim / .fam parsing            ldscore/common.py:86-89,114-117,130-133
+
+Beside the mirror (things the reference does not have):
+  result_arrays                  zero-copy NumPy views instead of per-read list copies (ldscore.cpp:43-51)
+  m_counts / write_m_files       the `.M` / `.M_5_50` side files h2's LDScoreReader looks for
+                                 (h2/common.py:115-144), with its own fallback formula for MD
+  estimate_lds_genome            all chromosome bfiles of a genome in one process, spread over the GPUs
 """
 from __future__ import annotations
 
 import os
+import queue
+import re
+import threading
 
 import numpy as np
 import pandas as pd
@@ -68,22 +77,69 @@ def _module():
     return _ldscore
 
 
+_FIELDS = ("l2", "l2d", "maf", "residuals_std", "l2_ws", "l2d_ws", "l2d_wse")
+
+
+def result_arrays(ld) -> dict:
+    """The seven result vectors as NumPy arrays.  With this repo's `_ldscore` they are views into the
+    result object (`as_arrays`); with the reference's module each list attribute is converted once."""
+    lds = _module()
+    if hasattr(lds, "as_arrays") and isinstance(ld, lds.LDScoreResult):
+        return lds.as_arrays(ld)
+    return {k: np.asarray(getattr(ld, k), dtype=np.float64 if k in _FIELDS[:4] else np.int64) for k in _FIELDS}
+
+
 def make_output(bim: pd.DataFrame, ld, *, extra: bool = False) -> pd.DataFrame:
     """CHR SNP BP L2 L2D [MAF WSA WSD WSDE RSTD] -- the layout h2's LDScoreReader reads by name."""
+    a = ld if isinstance(ld, dict) else result_arrays(ld)
     out = pd.DataFrame({"CHR": bim["CHR"], "SNP": bim["SNP"], "BP": bim["BP"],
-                        "L2": np.asarray(ld.l2, dtype=np.float64), "L2D": np.asarray(ld.l2d, dtype=np.float64)})
+                        "L2": np.asarray(a["l2"], dtype=np.float64), "L2D": np.asarray(a["l2d"], dtype=np.float64)})
     if extra:
-        out["MAF"] = np.asarray(ld.maf, dtype=np.float64)
-        out["WSA"] = np.asarray(ld.l2_ws, dtype=np.int64)
-        out["WSD"] = np.asarray(ld.l2d_ws, dtype=np.int64)
-        out["WSDE"] = np.asarray(ld.l2d_wse, dtype=np.int64)
-        out["RSTD"] = np.asarray(ld.residuals_std, dtype=np.float64)
+        out["MAF"] = np.asarray(a["maf"], dtype=np.float64)
+        out["WSA"] = np.asarray(a["l2_ws"], dtype=np.int64)
+        out["WSD"] = np.asarray(a["l2d_ws"], dtype=np.int64)
+        out["WSDE"] = np.asarray(a["l2d_wse"], dtype=np.int64)
+        out["RSTD"] = np.asarray(a["residuals_std"], dtype=np.float64)
+    return out
+
+
+def m_counts(arrays: dict, snp_ids=None, maf_min: float | None = None) -> tuple[int, int]:
+    """(M, MD) as h2 computes them when no side file exists (h2/common.py:126-130): M = rows of the .L2
+    file that survive `dropna().drop_duplicates('SNP')`, MD = int(M * mean(WSDE / WSA)) over those rows.
+    `maf_min` = 0.05 gives the `.M_5_50` flavour (common SNPs only).  Rows with WSA = 0 (a retained SNP
+    with an empty window) are left out of the mean, where the reference would divide by zero."""
+    l2 = np.asarray(arrays["l2"], dtype=np.float64)
+    keep = ~np.isnan(l2) & ~np.isnan(np.asarray(arrays["l2d"], dtype=np.float64))
+    if snp_ids is not None:
+        first = ~pd.Series(np.asarray(snp_ids)).duplicated().to_numpy()
+        keep &= first
+    if maf_min is not None:
+        keep &= np.asarray(arrays["maf"], dtype=np.float64) > maf_min
+    m = int(keep.sum())
+    wsa = np.asarray(arrays["l2_ws"], dtype=np.float64)[keep]
+    wsde = np.asarray(arrays["l2d_wse"], dtype=np.float64)[keep]
+    ok = wsa > 0
+    md = int(m * float(np.mean(wsde[ok] / wsa[ok]))) if ok.any() else 0
+    return m, md
+
+
+def write_m_files(l2_path: str, arrays: dict, snp_ids=None) -> dict:
+    """`<stem>.M` and `<stem>.M_5_50` next to an .L2 file, in the tab-separated `M MD` layout that
+    LDScoreReader._read_m parses (h2/common.py:141-144)."""
+    stem = os.path.splitext(l2_path)[0]
+    out = {}
+    for suffix, maf_min in ((".M", None), (".M_5_50", 0.05)):
+        m, md = m_counts(arrays, snp_ids, maf_min)
+        with open(stem + suffix, "w") as f:
+            f.write(f"M\tMD\n{m}\t{md}\n")
+        out[suffix] = (m, md)
     return out
 
 
 def estimate_lds(bfile: str, ld_wind: float, wind_metric: str, maf_thr: float = 1e-5, std_thr: float = 1e-5,
                  rsq_thr: float | None = None, *, out: str | None = None, extra: bool = False,
-                 summary: bool = False, verbose: int = 0):
+                 summary: bool = False, verbose: int = 0, device: int | None = None, gpus: int = 1,
+                 m_files: bool = False):
     lds = _module()
     bed, bim_path, fam_path = _bfile_paths(bfile)
     bim = pd.read_csv(bim_path, sep="\t", names=BIM_COLUMNS)
@@ -97,14 +153,86 @@ def estimate_lds(bfile: str, ld_wind: float, wind_metric: str, maf_thr: float = 
     positions = bim["CM" if metric == "cm" else "BP"].to_numpy(dtype=np.float64)
     params = lds.LDScoreParams(bfile=bed, n_snp=len(bim), n_org=n_org, ld_wind=wind, maf=maf, std_thr=std,
                                rsq_thr=rsq, positions=positions)
-    ld = lds.calculate(params)
+    ld = lds.calculate(params) if device is None else lds.calculate_on(params, device, gpus)
+    arrays = result_arrays(ld)
     if summary:
-        d = pd.DataFrame({"L2": ld.l2, "L2D": ld.l2d, "MAF": ld.maf})
+        d = pd.DataFrame({"L2": arrays["l2"], "L2D": arrays["l2d"], "MAF": arrays["maf"]})
         print("L2/L2D/MAF Correlation matrix\n" + str(d.corr()))
         print(f"- Number of additive non-null LD: {d['L2'].count()}\n"
               f"- Number of non-additive non-null LD: {d['L2D'].count()}")
-    out_df = make_output(bim, ld, extra=extra)
+    out_df = make_output(bim, arrays, extra=extra)
     if out:
         out_df.to_csv(out, sep="\t", index=False, float_format="%.5f")
+        if m_files:
+            write_m_files(out, arrays, bim["SNP"])
         return None
     return out_df
+
+
+def _genome_bfiles(bfile: str) -> list[tuple[str, str]]:
+    """`prefix@suffix` (ldsc convention: @ = chromosome number) -> [(chromosome label, bfile)] for the
+    chromosomes whose .bed exists; a plain bfile gives one entry labelled by its file name."""
+    if "@" not in bfile:
+        return [(os.path.basename(bfile), bfile)]
+    found = []
+    for c in [str(i) for i in range(1, 23)] + ["X"]:
+        cand = bfile.replace("@", c)
+        if os.path.exists(cand + ".bed"):
+            found.append((c, cand))
+    if not found:
+        raise FileNotFoundError(f'No chromosome bfile matches "{bfile}"')
+    return found
+
+
+def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: float = 1e-5, std_thr: float = 1e-5,
+                        rsq_thr: float | None = None, *, out_dir: str, extra: bool = True, gpus: int | None = None,
+                        first_device: int = 0) -> pd.DataFrame:
+    """Score every chromosome bfile of a genome in ONE process.
+
+    The reference scores one chromosome per invocation (ldscore/common.py:114-117) and never writes the
+    `.M` files `h2` looks for.  Here the chromosomes are dealt, largest .bed first, to one host thread per
+    GPU (`_ldscore.calculate_on`, no collective: chromosomes are independent); each writes
+    `<out_dir>/<chr>.L2` (+ `.M`, `.M_5_50`), the folder layout LDScoreReader._read_folder globs
+    (h2/common.py:98-112).  Returns one row per chromosome: CHR, file, SNPs, M, MD, seconds, device."""
+    lds = _module()
+    jobs = _genome_bfiles(bfile)
+    os.makedirs(out_dir, exist_ok=True)
+    if gpus is None:
+        gpus = int(os.environ.get("NLDSC_GPUS", "1")) if os.environ.get("NLDSC_GPUS", "1") != "all" else 64
+    n_dev = max(1, min(int(gpus), len(jobs)))
+    jobs.sort(key=lambda j: -os.path.getsize(j[1] + ".bed"))          # longest first
+    todo: queue.Queue = queue.Queue()
+    for j in jobs:
+        todo.put(j)
+    rows, errors, lock = [], [], threading.Lock()
+
+    def worker(device: int) -> None:
+        import time
+        while True:
+            try:
+                label, path = todo.get_nowait()
+            except queue.Empty:
+                return
+            try:
+                t0 = time.perf_counter()
+                l2_path = os.path.join(out_dir, f"{label}.L2")
+                estimate_lds(path, ld_wind, wind_metric, maf_thr, std_thr, rsq_thr, out=l2_path, extra=extra,
+                             device=device, gpus=1, m_files=True)
+                m, md = (int(x) for x in open(os.path.splitext(l2_path)[0] + ".M").read().split()[2:4])
+                with lock:
+                    rows.append({"CHR": label, "file": l2_path, "SNPs": sum(1 for _ in open(path + ".bim")),
+                                 "M": m, "MD": md, "seconds": time.perf_counter() - t0, "device": device})
+            except Exception as e:          # one bad chromosome must not hide behind the others
+                with lock:
+                    errors.append((label, e))
+
+    threads = [threading.Thread(target=worker, args=(first_device + d,)) for d in range(n_dev)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    if errors:
+        label, e = errors[0]
+        raise RuntimeError(f"chromosome {label}: {e}") from e
+    order = {label: i for i, (label, _) in enumerate(_genome_bfiles(bfile))}
+    return pd.DataFrame(sorted(rows, key=lambda r: order[r["CHR"]]))

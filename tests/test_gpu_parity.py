@@ -4,7 +4,7 @@
 Bar (BASELINE.json): filter decisions, retained-SNP lists, MAF and window counts bit-exact;
 L2 <= 1e-9 relative, L2D <= 1e-9 absolute-or-relative-to-max(|L2D|, 1), against the FP64
 build of the reference's own source (oracle-64)."""
-import importlib.util
+import importlib
 import os
 
 import numpy as np
@@ -215,9 +215,7 @@ def test_bfile_path_and_module(tmp_path):
     want = ld_oracle.ld_scores(packed, 501, info["cm"], 1.0, 1e-4, 1e-5, 1 / 900)
     got = capi.calculate(str(tmp_path / "t.bed"), 900, 501, info["cm"], 1.0, 1e-4, 1e-5, 1 / 900)
     assert_ld_close(got, want, label="bfile")
-    sp = importlib.util.spec_from_file_location("_ldscore", build.ext_path())
-    m = importlib.util.module_from_spec(sp)
-    sp.loader.exec_module(m)
+    m = importlib.import_module("nldsc_b200._ldscore")
     r = m.calculate(m.LDScoreParams(str(tmp_path / "t.bed"), n_snp=900, n_org=501, ld_wind=1.0, maf=1e-4,
                                     std_thr=1e-5, rsq_thr=1 / 900, positions=list(info["cm"])))
     for key in RESULT_KEYS:
@@ -248,3 +246,38 @@ def test_properties_at_bench_scale():
         assert abs(sub["l2"][i - a] - out["l2"][i]) <= 1e-9 * abs(sub["l2"][i - a])
         assert abs(sub["l2d"][i - a] - out["l2d"][i]) <= 1e-9 * max(1.0, abs(sub["l2d"][i - a]))
         assert sub["l2d_wse"][i - a] == out["l2d_wse"][i]
+
+
+def test_genome_driver_writes_l2_and_m_files(tmp_path):
+    """three chromosome bfiles scored in one process by two worker threads
+    (`_ldscore.calculate_on`), each `.L2` equal to the single-chromosome path and each `.M` equal to
+    h2's own fallback formula on that file (reference h2/common.py:126-130)."""
+    import dataclasses
+    import pandas as pd
+    from nldsc_b200 import ldscore
+    specs = {}
+    for c, (n_snp, seed) in {"1": (700, 31), "2": (500, 32), "21": (300, 33)}.items():
+        spec = dataclasses.replace(synth.SynthSpec(n_org=403, n_snp=n_snp, missing=0.02, seed=seed), chrom=int(c))
+        packed = synth.generate_packed(spec, workers=1)
+        info = synth.write_bfile(str(tmp_path / f"g.{c}"), spec, packed)
+        specs[c] = (packed, info)
+    summary = ldscore.estimate_lds_genome(str(tmp_path / "g.@"), 1.0, "cm", 1e-4, 1e-5, out_dir=str(tmp_path / "out"),
+                                          gpus=2 if capi.device_count() >= 2 else 1)
+    assert list(summary["CHR"]) == ["1", "2", "21"]
+    for c, (packed, info) in specs.items():
+        n_snp = info["n_snp"]
+        want = ld_oracle.ld_scores(packed, 403, info["cm"], 1.0, 1e-4, 1e-5, 1.0 / n_snp)
+        df = pd.read_csv(tmp_path / "out" / f"{c}.L2", sep="\t")
+        assert list(df.columns) == ["CHR", "SNP", "BP", "L2", "L2D", "MAF", "WSA", "WSD", "WSDE", "RSTD"]
+        keep = want["keep"]
+        assert np.array_equal(df["L2"].notna().to_numpy(), keep)
+        assert np.array_equal(df["WSA"].to_numpy(), want["l2_ws"])
+        assert np.allclose(df["L2"].to_numpy()[keep], want["l2"][keep], rtol=0, atol=6e-6)     # %.5f in the file
+        # h2's fallback on the file it will read
+        score = df.dropna().drop_duplicates(subset="SNP")
+        m = len(score["L2"])
+        md = int(m * (score["WSDE"] / score["WSA"]).mean())
+        got = pd.read_csv(tmp_path / "out" / f"{c}.M", sep="\t")
+        assert (int(got["M"].iloc[0]), int(got["MD"].iloc[0])) == (m, md)
+        row = summary[summary["CHR"] == c].iloc[0]
+        assert (row["M"], row["MD"], row["SNPs"]) == (m, md, n_snp)

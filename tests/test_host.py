@@ -1,6 +1,7 @@
 """CPU: the C-ABI library loads and exports what include/nldsc_ld.h declares, the host-side
 planning matches the reference's window semantics, and the error behaviour of the boundary
 (no compute happens here: there is no GPU and no CPU fallback)."""
+import importlib
 import os
 import re
 import struct
@@ -80,10 +81,7 @@ def test_missing_file_is_runtime_error():
 
 def test_ldscore_module_surface():
     """Same names / kwargs / attributes as reference ldscore.cpp:17-54."""
-    import importlib.util
-    spec = importlib.util.spec_from_file_location("_ldscore", build.ext_path())
-    m = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(m)
+    m = importlib.import_module("nldsc_b200._ldscore")
     p = m.LDScoreParams("/x.bed", n_snp=2, n_org=4, ld_wind=1.0, maf=0.1, std_thr=1e-5, rsq_thr=0.1,
                         positions=[0.0, 1.0])
     assert (p.bedfile, p.n_snp, p.n_org, p.ld_wind, p.maf, p.std_thr, p.rsq_thr, p.positions) == \
@@ -98,6 +96,44 @@ def test_ldscore_module_surface():
     assert q.positions == [1.0]
     with pytest.raises(RuntimeError):
         m.calculate(p)                                                       # no such file
+
+
+def test_result_arrays_are_views_and_m_files_follow_h2(tmp_path):
+    """NumPy views of the result vectors; `.M` files in LDScoreReader's layout with its
+    own fallback formula (reference h2/common.py:126-130,141-144)."""
+    import pandas as pd
+    from nldsc_b200 import ldscore
+    m = importlib.import_module("nldsc_b200._ldscore")
+    r = m.LDScoreResult()
+    r.l2 = [1.5, float("nan"), 2.5, 3.0]
+    r.l2d = [0.1, float("nan"), 0.2, 0.3]
+    r.maf = [0.2, 0.0, 0.01, 0.4]
+    r.residuals_std = [0.5, float("nan"), 0.5, 0.5]
+    r.l2_ws, r.l2d_ws, r.l2d_wse = [4, -1, 2, 0], [4, -1, 2, 0], [2, -1, 2, 0]
+    a = m.as_arrays(r)
+    assert a["l2"].dtype == np.float64 and a["l2_ws"].dtype == np.int32
+    assert not a["l2"].flags.owndata and a["l2"].base is not None
+    np.testing.assert_array_equal(a["l2_ws"], [4, -1, 2, 0])
+    # h2's fallback on the same rows: dropna, M = len, MD = int(M * mean(WSDE / WSA)); the WSA = 0 row is left out of the mean
+    assert ldscore.m_counts(a) == (3, int(3 * np.mean([2 / 4, 2 / 2])))
+    assert ldscore.m_counts(a, maf_min=0.05) == (2, int(2 * (2 / 4)))
+    assert ldscore.m_counts(a, snp_ids=["a", "b", "a", "c"]) == (2, int(2 * (2 / 4)))
+    out = ldscore.write_m_files(str(tmp_path / "22.L2"), a)
+    got = pd.read_csv(tmp_path / "22.M", sep="\t")          # LDScoreReader._read_m
+    assert (int(got["M"].iloc[0]), int(got["MD"].iloc[0])) == out[".M"] == (3, 2)
+    assert (tmp_path / "22.M_5_50").read_text() == "M\tMD\n2\t1\n"
+
+
+def test_genome_bfile_pattern(tmp_path):
+    from nldsc_b200 import ldscore
+    for c in (2, 11, 21):
+        (tmp_path / f"g.{c}.bed").write_bytes(b"x" * c)
+    got = ldscore._genome_bfiles(str(tmp_path / "g.@"))
+    assert [c for c, _ in got] == ["2", "11", "21"]
+    with pytest.raises(FileNotFoundError):
+        ldscore._genome_bfiles(str(tmp_path / "h.@"))
+    with pytest.raises(ValueError):
+        capi.calculate_on("/x.bed", 2, 4, np.arange(2.0), 1.0, 0.1, 1e-5, 0.1, first_device=-1)
 
 
 @pytest.mark.skipif(os.path.exists("/dev/nvidiactl"), reason="GPU box")
