@@ -83,10 +83,10 @@ def snp_stats(codes: np.ndarray, maf_thr: float):
 
 
 def ld_scores(packed: np.ndarray, n_org: int, positions: np.ndarray, ld_wind: float,
-              maf_thr: float, std_thr: float, rsq_thr: float) -> dict:
+              maf_thr: float, std_thr: float, rsq_thr: float, rows=None) -> dict:
     """calculate(), ldscalc.h:8-65, for sorted non-negative positions (the window
     of SNP i is {j != i : kept_j and |pos_j - pos_i| <= ld_wind}, stream.h:142-155
-    with tools.h:41-49)."""
+    with tools.h:41-49).  `rows`: score only these SNPs (spot checks at large sizes)."""
     positions = np.asarray(positions, dtype=np.float64)
     m = packed.shape[0]
     assert np.all(positions >= 0) and np.all(np.diff(positions) >= 0)
@@ -104,7 +104,8 @@ def ld_scores(packed: np.ndarray, n_org: int, positions: np.ndarray, ld_wind: fl
     hi = np.searchsorted(positions, positions + ld_wind, side="right")   # exclusive
     with np.errstate(all="ignore"):
         dom_ok = rstd > std_thr                          # tools.h:31-33 (NaN -> False)
-    for i in np.nonzero(keep)[0]:
+    todo = np.nonzero(keep)[0] if rows is None else [i for i in rows if keep[i]]
+    for i in todo:
         js = np.arange(lo[i], hi[i])
         # the searchsorted bounds use pos -/+ wind; re-check with the reference's own
         # expression |pos_j - pos_i| <= wind (tools.h:43-44) at the two edges
