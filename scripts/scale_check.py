@@ -46,6 +46,19 @@ for name in (sys.argv[1:] or list(CASES)):
            "int8_ops_per_s_algorithmic": pairs * 12.0 * c["n_org"] / min(times),
            "bed_bytes": int(host.numel()), "wsa_property": ok_wsa, "order_property": ok_order, "floor_property": ok_floor,
            "env": c.get("env", {})}
+    # kernel-only: shard resident in HBM, per-family CUDA-event times of one run (as bench.py's `value` leg)
+    sess = capi.Session(0, c["n_snp"], c["n_org"], cm, c["wind"], 1e-4, 1e-5, 1.0 / c["n_snp"])
+    sess.upload(host); sess.sync()
+    for _ in range(3):
+        sess.run()
+    sess.sync()
+    st = sess.stats()
+    sess.close()
+    ops = pairs * 12.0 * c["n_org"]
+    rec["resident"] = {"ms_step": st["ms_total"], "ms_band": st["ms_band"], "ms_unpack": st["ms_unpack"], "chunks": st["chunks"],
+                       "tiles": st["tiles"], "band_algorithmic_top_s": ops / (st["ms_band"] * 1e-3) / 1e12,
+                       "band_executed_top_s": st["tiles"] * 2 * 128 * 192 * 2.0 * st["npad"] / (st["ms_band"] * 1e-3) / 1e12,
+                       "step_algorithmic_top_s": ops / (st["ms_total"] * 1e-3) / 1e12}
     hn = host.numpy()
     rng = np.random.default_rng(1)
     errs = []
