@@ -182,7 +182,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 const int32_t b_row = tl.b_row + 32 * static_cast<int32_t>(rank);
                 for (int k = 0; k < args.k_steps; ++k) {
                     mbar_wait(&empty[stage], phase ^ 1);
-                    if (args.probe == 1) {           // tensor-pipe probe: operands are whatever the stage holds
+                    if (args.probe == 1 || args.probe == 3) {   // no loads: operands are whatever the stage holds
                         if (rank == 0) mbar_expect_tx(&full[stage], 0);
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                         continue;
@@ -216,7 +216,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                     const uint32_t sa = smem_u32(smem + stage * kStageBytes);
                     const uint64_t a_desc = make_smem_desc(sa);
                     const uint64_t b_desc = make_smem_desc(sa + kABytes);
-                    if (args.probe != 2) {
+                    if (args.probe < 2) {
 #pragma unroll
                         for (int kk = 0; kk < kKStep / 32; ++kk)   // +32 B along K inside the swizzle atom
                             tc_mma_i8(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (k | kk) != 0);

@@ -67,7 +67,7 @@ struct BandArgs {
     double rsq_thr;
     Partials part;
     int32_t* dump;              // optional raw accumulators [tile][rank][128][192] (parity hook)
-    int32_t probe;              // measurement hook: 0 = normal, 1 = MMAs without TMA loads, 2 = TMA loads without MMAs
+    int32_t probe;              // measurement hook: 0 = normal, 1 = MMAs without TMA loads, 2 = TMA loads without MMAs, 3 = epilogue only
 };
 
 // ---- error plumbing ----------------------------------------------------------------

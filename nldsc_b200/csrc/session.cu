@@ -1418,7 +1418,7 @@ int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* l
 int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int32_t reps, float* ms_out, char* err,
                               size_t errlen) {
     return guarded(err, errlen, [&] {
-        if (mode < 0 || mode > 2 || n_org <= 0 || n_tiles <= 0 || reps <= 0 || !ms_out) throw InvalidArgument("bad arguments");
+        if (mode < 0 || mode > 4 || n_org <= 0 || n_tiles <= 0 || reps <= 0 || !ms_out) throw InvalidArgument("bad arguments");
         usable_devices();
         const int dev = first_device_from_env();
         CUDA_CHECK(cudaSetDevice(dev));
@@ -1443,8 +1443,14 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         } fr{{d_packed, d_planes, d_tiles, d_coef, d_flags, d_w, d_pd, d_pi}};
         CUDA_CHECK(cudaMemset(d_packed, 0xB9, static_cast<size_t>(rows) * bps + 16));   // codes 01 10 11 10 per byte
         CUDA_CHECK(cudaMemset(d_coef, 0, sizeof(SnpCoef) * rows));
-        CUDA_CHECK(cudaMemset(d_flags, 0, rows));                                        // every pair rejected: cheapest epilogue
+        // modes 0-2: every pair rejected (cheapest epilogue); 3 = epilogue only and 4 = whole kernel, every pair scored
+        const bool full_epi = mode >= 3;
+        CUDA_CHECK(cudaMemset(d_flags, full_epi ? (kFlagKeep | kFlagDom) : 0, rows));
         CUDA_CHECK(cudaMemset(d_w, 0, sizeof(int32_t) * 2 * rows));
+        if (full_epi) {
+            std::vector<int32_t> whi(rows, rows - 1);
+            CUDA_CHECK(cudaMemcpy(d_w + rows, whi.data(), sizeof(int32_t) * rows, cudaMemcpyHostToDevice));
+        }
         launch_unpack(d_packed, bps, 0, rows, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, nullptr, nullptr);
         std::vector<Tile> tiles(n_tiles);
         for (int32_t t = 0; t < n_tiles; ++t) {       // band-like walk: 22 j-blocks per i-block pair
@@ -1469,7 +1475,7 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         a.part.wsa = d_pi;
         a.part.wsd = d_pi + static_cast<size_t>(n_tiles) * 2 * kBlk;
         a.part.wsde = d_pi + static_cast<size_t>(n_tiles) * 4 * kBlk;
-        a.probe = mode;
+        a.probe = mode == 4 ? 0 : mode;
         BandMaps* maps = band_maps_create(d_planes, rows, npad);
         struct MapFree { BandMaps* m; ~MapFree() { band_maps_destroy(m); } } mf{maps};
         cudaEvent_t e0, e1;
