@@ -273,7 +273,11 @@ def main():
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_note,
                 "ms_band": st["ms_band"], "ms_unpack": st["ms_unpack"], "ms_count": st["ms_count"],
                 "ms_stats": st["ms_stats"], "ms_finalize": st["ms_finalize"], "ms_step_device": dev_ms,
-                "tiles": st["tiles"], "chunks": st["chunks"]}
+                "tiles": st["tiles"], "chunks": st["chunks"],
+                # one band launch per chunk: `achieved` = ops per launch / mean launch time = ops per step / ms_band
+                "launches_per_step": st["chunks"], "ops_per_launch": ops / max(1, st["chunks"]),
+                "ms_per_launch": st["ms_band"] / max(1, st["chunks"]),
+                "executed_frac": (st["tiles"] * 2.0 * 256 * 192 * st["npad"] / band_s / 1e12 / peak) if band_s > 0 else 0.0}
     sess.close()
 
     # ---- e2e: host buffer -> C ABI -> host results ----------------------------------------------
