@@ -278,6 +278,19 @@ def main():
                 "launches_per_step": st["chunks"], "ops_per_launch": ops / max(1, st["chunks"]),
                 "ms_per_launch": st["ms_band"] / max(1, st["chunks"]),
                 "executed_frac": (st["tiles"] * 2.0 * 256 * 192 * st["npad"] / band_s / 1e12 / peak) if band_s > 0 else 0.0}
+    # secondary kernel, HBM-bound: time unpack ALONE (one step with the two streams serialised; beside the band
+    # kernel its span is stretched by the contention).  Algorithmic bytes per SNP: ceil(N/4) read + 4 planes * npad written.
+    os.environ["NLDSC_OVERLAP"] = "0"
+    sess.run()
+    sess.sync()
+    os.environ.pop("NLDSC_OVERLAP")
+    st1 = sess.stats()
+    ub = float(st1["load_end"] - st1["load_begin"]) * (bps + 4.0 * st1["npad"])
+    hbm_peak = peaks["hbm_gbs"] if peaks else 6500.0
+    if st1["ms_unpack"] > 0:
+        roofline["unpack"] = {"bound": "hbm", "kernel": "unpack_kernel", "achieved": ub / (st1["ms_unpack"] * 1e-3) / 1e9,
+                              "peak": hbm_peak, "unit": "GB/s", "frac": ub / (st1["ms_unpack"] * 1e-3) / 1e9 / hbm_peak,
+                              "ms_alone": st1["ms_unpack"], "ms_beside_band": st["ms_unpack"]}
     sess.close()
 
     # ---- e2e: host buffer -> C ABI -> host results ----------------------------------------------
@@ -303,7 +316,9 @@ def main():
             rows = 3072
             pk = host[:rows].numpy()
             cpairs, cdt = time_reference(pk, cm, N_ORG, rows)
+            c1pairs, c1dt = time_reference(pk, cm, N_ORG, 512, threads=1)
             cpu = {"value": cpairs / cdt, "unit": UNIT, "cores": host_cores(), "kind": "reference",
+                   "single_thread_value": c1pairs / c1dt,
                    "sample": f"first {rows} SNPs of the workload bfile, {cpairs} pairs, {cdt:.1f} s; stock float32 "
                              "reference source (oracle/_ref/libref_ld32.so), OpenMP over all host cores"}
             # parity spot check of the timed GPU run against that same reference output is in tests/

@@ -354,6 +354,8 @@ T* amalloc(Arena* a, size_t n) {
 
 int32_t floor64(int32_t x) { return x & ~63; }
 
+cudaEvent_t ev_get(int device, bool timing);     // per-device pools, defined below
+
 struct SpanScope {
     nldsc_ld_session* s;
     cudaStream_t st;
@@ -361,8 +363,8 @@ struct SpanScope {
     SpanScope(nldsc_ld_session* s_, cudaStream_t st_, int family) : s(s_), st(st_) {
         if (s->spans_used == s->spans.size()) {
             nldsc_ld_session::Span sp;
-            CUDA_CHECK(cudaEventCreate(&sp.a));
-            CUDA_CHECK(cudaEventCreate(&sp.b));
+            sp.a = ev_get(s->device, true);
+            sp.b = ev_get(s->device, true);
             sp.family = family;
             s->spans.push_back(sp);
         }
@@ -396,6 +398,52 @@ size_t env_size(const char* name, size_t dflt) {
 
 }  // namespace
 
+// ---- per-device pools of streams and events --------------------------------------------------------
+// A calculate call creates ~100 events and three streams; creating and destroying them costs ~0.5 ms per
+// call, which is 7 % of an 7 ms chromosome.  Sessions borrow them here and hand them back idle.
+namespace {
+struct DevPool {
+    std::vector<cudaEvent_t> ev[2];          // [0] cudaEventDisableTiming, [1] timing
+    std::vector<cudaStream_t> st[3];         // [0] high priority, [1] default, [2] low priority
+};
+DevPool g_pool[kMaxDevices];
+
+cudaEvent_t ev_get(int device, bool timing) {
+    {
+        std::lock_guard<std::mutex> g(g_arena_mu);
+        auto& v = g_pool[device & (kMaxDevices - 1)].ev[timing ? 1 : 0];
+        if (!v.empty()) { cudaEvent_t e = v.back(); v.pop_back(); return e; }
+    }
+    cudaEvent_t e = nullptr;
+    if (timing) CUDA_CHECK(cudaEventCreate(&e));
+    else CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    return e;
+}
+void ev_put(int device, bool timing, cudaEvent_t e) {
+    if (!e) return;
+    std::lock_guard<std::mutex> g(g_arena_mu);
+    g_pool[device & (kMaxDevices - 1)].ev[timing ? 1 : 0].push_back(e);
+}
+cudaStream_t stream_get(int device, int kind) {
+    {
+        std::lock_guard<std::mutex> g(g_arena_mu);
+        auto& v = g_pool[device & (kMaxDevices - 1)].st[kind];
+        if (!v.empty()) { cudaStream_t t = v.back(); v.pop_back(); return t; }
+    }
+    int prio_lo = 0, prio_hi = 0;
+    CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    cudaStream_t t = nullptr;
+    if (kind == 1) CUDA_CHECK(cudaStreamCreateWithFlags(&t, cudaStreamNonBlocking));
+    else CUDA_CHECK(cudaStreamCreateWithPriority(&t, cudaStreamNonBlocking, kind == 0 ? prio_hi : prio_lo));
+    return t;
+}
+void stream_put(int device, int kind, cudaStream_t t) {     // the stream must be idle
+    if (!t) return;
+    std::lock_guard<std::mutex> g(g_arena_mu);
+    g_pool[device & (kMaxDevices - 1)].st[kind].push_back(t);
+}
+}  // namespace
+
 // ---- session ------------------------------------------------------------------------------
 
 static void session_free(nldsc_ld_session* s) {
@@ -409,20 +457,20 @@ static void session_free(nldsc_ld_session* s) {
     arena_release(s->arena);
     host_stage_release(s->stage);
     plan_stage_release(s->pstage);
-    if (s->ev_planned) cudaEventDestroy(s->ev_planned);
-    if (s->ev_up0) cudaEventDestroy(s->ev_up0);
-    if (s->ev_up1) cudaEventDestroy(s->ev_up1);
+    ev_put(s->device, false, s->ev_planned);
+    ev_put(s->device, true, s->ev_up0);
+    ev_put(s->device, true, s->ev_up1);
     if (s->maps) band_maps_destroy(s->maps);
-    for (auto& sp : s->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
-    for (auto e : s->ev_piece) cudaEventDestroy(e);
-    for (auto e : s->ev_unpacked) cudaEventDestroy(e);
-    for (auto e : s->ev_band) cudaEventDestroy(e);
-    if (s->ev_fork) cudaEventDestroy(s->ev_fork);
-    if (s->unpack_stream) cudaStreamDestroy(s->unpack_stream);
-    if (s->ev_run0) cudaEventDestroy(s->ev_run0);
-    if (s->ev_run1) cudaEventDestroy(s->ev_run1);
-    if (s->own_stream) cudaStreamDestroy(s->own_stream);
-    if (s->copy_stream) cudaStreamDestroy(s->copy_stream);
+    for (auto& sp : s->spans) { ev_put(s->device, true, sp.a); ev_put(s->device, true, sp.b); }
+    for (auto e : s->ev_piece) ev_put(s->device, false, e);
+    for (auto e : s->ev_unpacked) ev_put(s->device, false, e);
+    for (auto e : s->ev_band) ev_put(s->device, false, e);
+    ev_put(s->device, false, s->ev_fork);
+    stream_put(s->device, 2, s->unpack_stream);
+    ev_put(s->device, true, s->ev_run0);
+    ev_put(s->device, true, s->ev_run1);
+    stream_put(s->device, 0, s->own_stream);
+    stream_put(s->device, 1, s->copy_stream);
     delete s;
 }
 
@@ -457,23 +505,21 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
 
     s->d_packed = amalloc<uint8_t>(s->arena, static_cast<size_t>(s->n_load) * s->bps + 16);
     // the band kernel's CTAs go first; unpack blocks fill the thread slots that are left on every SM
-    int prio_lo = 0, prio_hi = 0;
-    CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-    CUDA_CHECK(cudaStreamCreateWithPriority(&s->own_stream, cudaStreamNonBlocking, prio_hi));
-    CUDA_CHECK(cudaStreamCreateWithFlags(&s->copy_stream, cudaStreamNonBlocking));
-    CUDA_CHECK(cudaStreamCreateWithPriority(&s->unpack_stream, cudaStreamNonBlocking, prio_lo));
-    CUDA_CHECK(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
+    s->own_stream = stream_get(device, 0);
+    s->copy_stream = stream_get(device, 1);
+    s->unpack_stream = stream_get(device, 2);
+    s->ev_fork = ev_get(device, false);
     // the 16 bytes of slack the word-wise kernels may read past the last row
     CUDA_CHECK(cudaMemsetAsync(s->d_packed + static_cast<size_t>(s->n_load) * s->bps, 0, 16, s->copy_stream));
     // upload granularity: ~8 MB pieces, a whole number of 64-row blocks each
     const int64_t rows8 = (int64_t(8) << 20) / s->bps;
     s->piece_rows = static_cast<int32_t>(std::max<int64_t>(kBlk, rows8 / kBlk * kBlk));
     s->ev_piece.resize((s->n_load + s->piece_rows - 1) / s->piece_rows);
-    for (auto& e : s->ev_piece) CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-    CUDA_CHECK(cudaEventCreate(&s->ev_run0));
-    CUDA_CHECK(cudaEventCreate(&s->ev_run1));
-    CUDA_CHECK(cudaEventCreate(&s->ev_up0));
-    CUDA_CHECK(cudaEventCreate(&s->ev_up1));
+    for (auto& e : s->ev_piece) e = ev_get(device, false);
+    s->ev_run0 = ev_get(device, true);
+    s->ev_run1 = ev_get(device, true);
+    s->ev_up0 = ev_get(device, true);
+    s->ev_up1 = ev_get(device, true);
     return sp.release();
 }
 
@@ -765,7 +811,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     s->part.wsde = amalloc<int32_t>(s->arena, np);
     if (!s->use_simt) s->maps = band_maps_create(s->d_planes, s->plane_rows, s->npad);
     // the plan is consumed by kernels on the session's own stream or on a caller's stream
-    CUDA_CHECK(cudaEventCreateWithFlags(&s->ev_planned, cudaEventDisableTiming));
+    s->ev_planned = ev_get(s->device, false);
     CUDA_CHECK(cudaEventRecord(s->ev_planned, st));
     s->planned = true;
     tr.lap("tile upload + maps");
@@ -808,11 +854,8 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         CUDA_CHECK(cudaEventRecord(s->ev_fork, st));
         CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_fork, 0));
         while (s->ev_unpacked.size() < s->chunks.size()) {
-            cudaEvent_t e;
-            CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-            s->ev_unpacked.push_back(e);
-            CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-            s->ev_band.push_back(e);
+            s->ev_unpacked.push_back(ev_get(s->device, false));
+            s->ev_band.push_back(ev_get(s->device, false));
         }
     }
     for (size_t ci = 0; ci < s->chunks.size(); ++ci) {

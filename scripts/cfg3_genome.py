@@ -1,0 +1,46 @@
+"""BASELINE.json configs[2]: N=50,000 x 5 chromosome bfiles of 100,000 SNPs, 2% missing, 1 cM window, scored by the
+genome driver (one process, one host thread per GPU, .bed files read from disk) on the GPUs of this box.
+Writes gpurun_out/cfg3_genome.json.   usage: cfg3_genome.py [gpus] [n_snp_per_chromosome]"""
+import dataclasses, json, os, shutil, sys, tempfile, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import pandas as pd
+import torch
+from nldsc_b200 import ldscore, synth
+
+gpus = int(sys.argv[1]) if len(sys.argv) > 1 else torch.cuda.device_count()
+n_snp = int(sys.argv[2]) if len(sys.argv) > 2 else 100_000
+N = 50_000
+d = tempfile.mkdtemp(prefix="cfg3_")
+t0 = time.perf_counter()
+for c in range(1, 6):
+    spec = dataclasses.replace(synth.SynthSpec(n_org=N, n_snp=n_snp, missing=0.02, seed=30 + c), chrom=c)
+    packed = synth.generate_packed_cuda(spec).cpu().numpy()
+    cm, bp = synth.genetic_map(spec)
+    with open(f"{d}/g.{c}.bed", "wb") as f:
+        f.write(synth.BED_MAGIC); f.write(packed.tobytes())
+    pd.DataFrame({"c": c, "s": [f"rs{c}_{k}" for k in range(n_snp)], "cm": np.round(cm, 8), "bp": bp, "a": "A", "b": "C"}
+                 ).to_csv(f"{d}/g.{c}.bim", sep="\t", header=False, index=False)
+    with open(f"{d}/g.{c}.fam", "w") as f:
+        f.writelines(f"F{i}\tI{i}\t0\t0\t0\t-9\n" for i in range(N))
+    del packed
+torch.cuda.empty_cache()
+gen_s = time.perf_counter() - t0
+runs = []
+for rep in range(2):
+    shutil.rmtree(f"{d}/out", ignore_errors=True)
+    t0 = time.perf_counter()
+    summ = ldscore.estimate_lds_genome(f"{d}/g.@", 1.0, "cm", 1e-4, 1e-5, out_dir=f"{d}/out", gpus=gpus)
+    runs.append(time.perf_counter() - t0)
+pairs = 0
+for c in range(1, 6):
+    df = pd.read_csv(f"{d}/out/{c}.L2", sep="\t")
+    pairs += int(df["WSA"][df["WSA"] >= 0].sum())
+rec = {"config": "configs[2]: N=50,000 x 5 chromosomes x %d SNPs, 2%% missing, 1 cM" % n_snp, "gpus": gpus, "bed_bytes": 5 * n_snp * (N // 4),
+       "pairs": pairs, "wall_s": runs, "pairs_per_s_wall": pairs / min(runs), "generate_s": gen_s,
+       "per_chromosome": summ.drop(columns=["file"]).to_dict(orient="records"),
+       "note": "wall time of estimate_lds_genome: .bim/.fam parsing, .bed read from the page cache, GPU scoring, %.5f .L2 + .M files written"}
+print(json.dumps(rec))
+os.makedirs("gpurun_out", exist_ok=True)
+json.dump(rec, open("gpurun_out/cfg3_genome.json", "w"), indent=1)
+shutil.rmtree(d, ignore_errors=True)
