@@ -449,7 +449,7 @@ void stream_put(int device, int kind, cudaStream_t t) {     // the stream must b
 static void session_free(nldsc_ld_session* s) {
     if (!s) return;
     cudaSetDevice(s->device);
-    if (s->reader.joinable()) s->reader.join();
+    for (auto& t : s->readers) if (t.joinable()) t.join();
     // every buffer lives in the arena; make sure nothing queued still touches it before it is reused
     if (s->own_stream) cudaStreamSynchronize(s->own_stream);
     if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);
@@ -558,44 +558,61 @@ static void session_upload_file(nldsc_ld_session* s, int fd) {
     CUDA_CHECK(cudaSetDevice(s->device));
     s->stage = host_stage_acquire(s->device);
     s->upload_started = true;
-    s->reader = std::thread([s, fd] {
-        const int32_t n_pieces = static_cast<int32_t>(s->ev_piece.size());
-        int32_t done = 0;
-        try {
-            CUDA_CHECK(cudaSetDevice(s->device));
-            const size_t slot_bytes = s->stage->bytes / HostStage::kSlots;
-            int slot = 0;
-            for (int32_t k = 0; k < n_pieces; ++k) {
-                const int32_t r0 = k * s->piece_rows, r1 = std::min(s->n_load, r0 + s->piece_rows);
-                size_t off = static_cast<size_t>(r0) * s->bps;
-                const size_t end = static_cast<size_t>(r1) * s->bps;
-                while (off < end) {                      // a piece may span several slots (very long rows)
-                    const size_t len = std::min(slot_bytes, end - off);
-                    char* buf = static_cast<char*>(s->stage->base) + slot * slot_bytes;
-                    CUDA_CHECK(cudaEventSynchronize(s->stage->ev[slot]));       // slot's previous copy has landed
-                    size_t got = 0;
-                    while (got < len) {
-                        const ssize_t r = pread(fd, buf + got, len - got,
-                                                3 + static_cast<off_t>(s->load_begin) * s->bps + static_cast<off_t>(off + got));
-                        if (r <= 0) throw CudaError("short read on .bed file");
-                        got += static_cast<size_t>(r);
+    const int32_t n_pieces = static_cast<int32_t>(s->ev_piece.size());
+    s->piece_done.assign(n_pieces, 0);
+    const int n_readers = std::max(1, std::min<int>(HostStage::kReaders, n_pieces));
+    for (int t = 0; t < n_readers; ++t) {
+        s->readers.emplace_back([s, fd, t, n_readers, n_pieces] {
+            auto publish = [&](int32_t k, const char* error) {        // piece k is queued (or the upload has failed)
+                {
+                    std::lock_guard<std::mutex> g(s->up_mu);
+                    if (error) {
+                        if (s->up_error.empty()) s->up_error = error;
+                        s->pieces_issued = n_pieces;                    // unblock run(); the error surfaces there / at download
+                    } else {
+                        s->piece_done[k] = 1;
+                        while (s->pieces_issued < n_pieces && s->piece_done[s->pieces_issued]) ++s->pieces_issued;
                     }
-                    CUDA_CHECK(cudaMemcpyAsync(s->d_packed + off, buf, len, cudaMemcpyHostToDevice, s->copy_stream));
-                    CUDA_CHECK(cudaEventRecord(s->stage->ev[slot], s->copy_stream));
-                    slot = (slot + 1) % HostStage::kSlots;
-                    off += len;
                 }
-                CUDA_CHECK(cudaEventRecord(s->ev_piece[k], s->copy_stream));
-                note_pieces_issued(s, ++done);
+                s->up_cv.notify_all();
+            };
+            try {
+                CUDA_CHECK(cudaSetDevice(s->device));
+                const size_t slot_bytes = s->stage->bytes / HostStage::kSlots;
+                int flip = 0;
+                for (int32_t k = t; k < n_pieces; k += n_readers) {
+                    const int32_t r0 = k * s->piece_rows, r1 = std::min(s->n_load, r0 + s->piece_rows);
+                    size_t off = static_cast<size_t>(r0) * s->bps;
+                    const size_t end = static_cast<size_t>(r1) * s->bps;
+                    while (off < end) {                      // a piece may span several slots (very long rows)
+                        const int slot = 2 * t + flip;
+                        flip ^= 1;
+                        const size_t len = std::min(slot_bytes, end - off);
+                        char* buf = static_cast<char*>(s->stage->base) + slot * slot_bytes;
+                        CUDA_CHECK(cudaEventSynchronize(s->stage->ev[slot]));       // slot's previous copy has landed
+                        size_t got = 0;
+                        while (got < len) {
+                            const ssize_t r = pread(fd, buf + got, len - got,
+                                                    3 + static_cast<off_t>(s->load_begin) * s->bps + static_cast<off_t>(off + got));
+                            if (r <= 0) throw CudaError("short read on .bed file");
+                            got += static_cast<size_t>(r);
+                        }
+                        CUDA_CHECK(cudaMemcpyAsync(s->d_packed + off, buf, len, cudaMemcpyHostToDevice, s->copy_stream));
+                        CUDA_CHECK(cudaEventRecord(s->stage->ev[slot], s->copy_stream));
+                        off += len;
+                    }
+                    CUDA_CHECK(cudaEventRecord(s->ev_piece[k], s->copy_stream));
+                    publish(k, nullptr);
+                }
+            } catch (const std::exception& e) {
+                publish(-1, e.what());
             }
-        } catch (const std::exception& e) {
-            note_pieces_issued(s, n_pieces, e.what());   // unblock run(); the error surfaces there / at download
-        }
-    });
+        });
+    }
 }
 
 static void join_reader(nldsc_ld_session* s) {
-    if (s->reader.joinable()) s->reader.join();
+    for (auto& t : s->readers) if (t.joinable()) t.join();
 }
 
 // Stage 2: windows -> owned i-blocks -> plane ring -> chunks and supertiles, and their device copies.

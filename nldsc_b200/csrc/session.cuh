@@ -52,12 +52,13 @@ void arena_trim(int device);          // frees the cached blocks (device < 0: ev
 // Pinned staging ring for reading a .bed: kSlots slots the reader thread fills by pread and drains by
 // cudaMemcpyAsync; cached per device like the Arena (pinning memory costs tens of ms).
 struct HostStage {
-    static constexpr int kSlots = 4;
+    static constexpr int kReaders = 4;            // reader threads: one pread stream copies ~10 GB/s, PCIe takes 55
+    static constexpr int kSlots = 2 * kReaders;   // two slots per reader
     int device = -1;
     bool cached = false;
     void* base = nullptr;
     size_t bytes = 0;             // kSlots equal slots
-    cudaEvent_t ev[kSlots] = {nullptr, nullptr, nullptr, nullptr};   // slot's last H2D has landed
+    cudaEvent_t ev[kSlots] = {};                  // slot's last H2D has landed
 };
 HostStage* host_stage_acquire(int device);
 void host_stage_release(HostStage* h);
@@ -133,7 +134,8 @@ struct nldsc_ld_session {
     std::condition_variable up_cv;
     int32_t pieces_issued = 0;
     std::string up_error;
-    std::thread reader;                       // .bed reader (nldsc_ld_calculate only)
+    std::vector<std::thread> readers;         // .bed readers (nldsc_ld_calculate only): piece k belongs to reader k % kReaders
+    std::vector<char> piece_done;             // pieces_issued = length of the all-done prefix
     nldsc::HostStage* stage = nullptr;
     nldsc::PlanStage* pstage = nullptr;
     // host copies of the plan (sources of the asynchronous H2D copies)

@@ -160,6 +160,14 @@ def estimate_lds(bfile: str, ld_wind: float, wind_metric: str, maf_thr: float = 
         print("L2/L2D/MAF Correlation matrix\n" + str(d.corr()))
         print(f"- Number of additive non-null LD: {d['L2'].count()}\n"
               f"- Number of non-additive non-null LD: {d['L2D'].count()}")
+    if out and hasattr(lds, "write_l2") and bim["BP"].dtype.kind in "iu":
+        # same bytes as the pandas writer below (tests/test_host.py), without its seconds at genome scale
+        lds.write_l2(out, bim["CHR"].astype(str).tolist(), bim["SNP"].astype(str).tolist(), bim["BP"].to_numpy(np.int64),
+                     arrays["l2"], arrays["l2d"], arrays["maf"], arrays["residuals_std"], arrays["l2_ws"],
+                     arrays["l2d_ws"], arrays["l2d_wse"], extra)
+        if m_files:
+            write_m_files(out, arrays, bim["SNP"])
+        return None
     out_df = make_output(bim, arrays, extra=extra)
     if out:
         out_df.to_csv(out, sep="\t", index=False, float_format="%.5f")

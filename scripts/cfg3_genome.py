@@ -26,18 +26,20 @@ for c in range(1, 6):
     del packed
 torch.cuda.empty_cache()
 gen_s = time.perf_counter() - t0
-runs = []
+import hashlib
+runs, digests = [], []
 for rep in range(2):
     shutil.rmtree(f"{d}/out", ignore_errors=True)
     t0 = time.perf_counter()
     summ = ldscore.estimate_lds_genome(f"{d}/g.@", 1.0, "cm", 1e-4, 1e-5, out_dir=f"{d}/out", gpus=gpus)
     runs.append(time.perf_counter() - t0)
+    digests.append(hashlib.sha256(b"".join(open(f"{d}/out/{c}.L2", "rb").read() for c in range(1, 6))).hexdigest())
 pairs = 0
 for c in range(1, 6):
     df = pd.read_csv(f"{d}/out/{c}.L2", sep="\t")
     pairs += int(df["WSA"][df["WSA"] >= 0].sum())
 rec = {"config": "configs[2]: N=50,000 x 5 chromosomes x %d SNPs, 2%% missing, 1 cM" % n_snp, "gpus": gpus, "bed_bytes": 5 * n_snp * (N // 4),
-       "pairs": pairs, "wall_s": runs, "pairs_per_s_wall": pairs / min(runs), "generate_s": gen_s,
+       "pairs": pairs, "wall_s": runs, "outputs_identical_across_runs": digests[0] == digests[1], "l2_sha256": digests[0], "pairs_per_s_wall": pairs / min(runs), "generate_s": gen_s,
        "per_chromosome": summ.drop(columns=["file"]).to_dict(orient="records"),
        "note": "wall time of estimate_lds_genome: .bim/.fam parsing, .bed read from the page cache, GPU scoring, %.5f .L2 + .M files written"}
 print(json.dumps(rec))

@@ -281,3 +281,25 @@ def test_genome_driver_writes_l2_and_m_files(tmp_path):
         assert (int(got["M"].iloc[0]), int(got["MD"].iloc[0])) == (m, md)
         row = summary[summary["CHR"] == c].iloc[0]
         assert (row["M"], row["MD"], row["SNPs"]) == (m, md, n_snp)
+
+
+def test_multi_piece_bed_read_equals_host_buffer(tmp_path):
+    """The .bed path (parallel reader threads, several 8 MB pieces, pinned slot ring) must hand the kernels the
+    same bytes as a host buffer: results bitwise equal to nldsc_ld_calculate_packed on a 44 MB file."""
+    rng = np.random.default_rng(17)
+    n_org, n_snp = 20001, 8800
+    bps = (n_org + 3) // 4
+    # mostly hom-first / het / hom-second, a few missing codes (01); any byte pattern is a valid .bed row
+    codes = rng.choice(np.array([0, 2, 3, 1], dtype=np.uint8), size=(n_snp, bps * 4), p=[0.55, 0.3, 0.13, 0.02])
+    packed = (codes[:, 0::4] | (codes[:, 1::4] << 2) | (codes[:, 2::4] << 4) | (codes[:, 3::4] << 6)).astype(np.uint8)
+    pos = np.cumsum(rng.exponential(1 / 340.0, n_snp))
+    with open(tmp_path / "big.bed", "wb") as f:
+        f.write(synth.BED_MAGIC)
+        f.write(packed.tobytes())
+    args = (n_snp, n_org, pos, 0.3, 1e-4, 1e-5, 1.0 / n_snp)
+    mem = capi.calculate_packed(packed, *args)
+    for _ in range(2):
+        got = capi.calculate(str(tmp_path / "big.bed"), *args)
+        for key in RESULT_KEYS:
+            assert np.array_equal(got[key], mem[key], equal_nan=True), key
+    assert (mem["l2_ws"] >= 0).sum() > 8000

@@ -124,6 +124,31 @@ def test_result_arrays_are_views_and_m_files_follow_h2(tmp_path):
     assert (tmp_path / "22.M_5_50").read_text() == "M\tMD\n2\t1\n"
 
 
+@pytest.mark.parametrize("extra", [False, True])
+def test_l2_writer_matches_pandas_bytes(tmp_path, extra):
+    """`_ldscore.write_l2` = the reference's to_csv(sep='\\t', index=False, float_format='%.5f') (routine.py:99), byte for byte."""
+    import pandas as pd
+    from nldsc_b200 import ldscore
+    m = importlib.import_module("nldsc_b200._ldscore")
+    rng = np.random.default_rng(5)
+    n = 2000
+    a = {"l2": rng.normal(50, 30, n), "l2d": rng.normal(0, 1e-3, n), "maf": rng.uniform(0, 0.5, n).astype(np.float32).astype(np.float64),
+         "residuals_std": rng.uniform(0, 1, n), "l2_ws": rng.integers(0, 2000, n).astype(np.int32),
+         "l2d_ws": rng.integers(0, 2000, n).astype(np.int32), "l2d_wse": rng.integers(0, 2000, n).astype(np.int32)}
+    drop = rng.random(n) < 0.1
+    for k in ("l2", "l2d", "residuals_std"):
+        a[k][drop] = np.nan
+    for k in ("l2_ws", "l2d_ws", "l2d_wse"):
+        a[k][drop] = -1
+    a["l2d"][:4] = [0.0, -0.0, -4e-6, 0.000005]          # rounding and signed-zero cases
+    a["l2"][4:7] = [1e6 + 0.123456, 0.999995, 123.4]
+    bim = pd.DataFrame({"CHR": 22, "SNP": [f"rs{i}" for i in range(n)], "BP": np.arange(n, dtype=np.int64) * 997 + 1})
+    ldscore.make_output(bim, a, extra=extra).to_csv(tmp_path / "pandas.L2", sep="\t", index=False, float_format="%.5f")
+    m.write_l2(str(tmp_path / "native.L2"), bim["CHR"].astype(str).tolist(), bim["SNP"].tolist(), bim["BP"].to_numpy(),
+               a["l2"], a["l2d"], a["maf"], a["residuals_std"], a["l2_ws"], a["l2d_ws"], a["l2d_wse"], extra)
+    assert (tmp_path / "native.L2").read_bytes() == (tmp_path / "pandas.L2").read_bytes()
+
+
 def test_genome_bfile_pattern(tmp_path):
     from nldsc_b200 import ldscore
     for c in (2, 11, 21):
