@@ -580,6 +580,8 @@ static void session_upload_file(nldsc_ld_session* s, int fd) {
                 CUDA_CHECK(cudaSetDevice(s->device));
                 const size_t slot_bytes = s->stage->bytes / HostStage::kSlots;
                 int flip = 0;
+                // test hook: hold reader 0 back so that later pieces are queued before earlier ones
+                const useconds_t lag = t == 0 ? static_cast<useconds_t>(env_size("NLDSC_TEST_READER0_LAG_US", 0)) : 0;
                 for (int32_t k = t; k < n_pieces; k += n_readers) {
                     const int32_t r0 = k * s->piece_rows, r1 = std::min(s->n_load, r0 + s->piece_rows);
                     size_t off = static_cast<size_t>(r0) * s->bps;
@@ -590,6 +592,7 @@ static void session_upload_file(nldsc_ld_session* s, int fd) {
                         const size_t len = std::min(slot_bytes, end - off);
                         char* buf = static_cast<char*>(s->stage->base) + slot * slot_bytes;
                         CUDA_CHECK(cudaEventSynchronize(s->stage->ev[slot]));       // slot's previous copy has landed
+                        if (lag) usleep(lag);
                         size_t got = 0;
                         while (got < len) {
                             const ssize_t r = pread(fd, buf + got, len - got,
@@ -875,6 +878,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             s->ev_band.push_back(ev_get(s->device, false));
         }
     }
+    int32_t next_piece = 0;                 // pieces below this one have been waited for on the unpack stream
     for (size_t ci = 0; ci < s->chunks.size(); ++ci) {
         const Chunk& c = s->chunks[ci];
         const int32_t r0 = std::min(c.new_row0, s->n_load), r1 = std::min(c.new_row1, s->n_load);
@@ -887,7 +891,9 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
                 s->up_cv.wait(g, [&] { return s->pieces_issued > piece; });
                 if (!s->up_error.empty()) throw CudaError(s->up_error);
             }
-            CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_piece[piece], 0));
+            // every piece up to that one: the .bed readers queue their pieces on the copy stream out of order, so
+            // the event of piece k says nothing about piece k - 1
+            for (; next_piece <= piece; ++next_piece) CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_piece[next_piece], 0));
         }
         if (overlap && c.new_row1 > c.new_row0) {
             // ring hazard: rows [new_row0, new_row1) land in the slots of rows `plane_rows` earlier; the

@@ -283,7 +283,7 @@ def test_genome_driver_writes_l2_and_m_files(tmp_path):
         assert (row["M"], row["MD"], row["SNPs"]) == (m, md, n_snp)
 
 
-def test_multi_piece_bed_read_equals_host_buffer(tmp_path):
+def test_multi_piece_bed_read_equals_host_buffer(tmp_path, monkeypatch):
     """The .bed path (parallel reader threads, several 8 MB pieces, pinned slot ring) must hand the kernels the
     same bytes as a host buffer: results bitwise equal to nldsc_ld_calculate_packed on a 44 MB file."""
     rng = np.random.default_rng(17)
@@ -298,7 +298,8 @@ def test_multi_piece_bed_read_equals_host_buffer(tmp_path):
         f.write(packed.tobytes())
     args = (n_snp, n_org, pos, 0.3, 1e-4, 1e-5, 1.0 / n_snp)
     mem = capi.calculate_packed(packed, *args)
-    for _ in range(2):
+    for lag in ("0", "3000", "20000"):      # reader 0 held back: its pieces reach the copy stream after later ones
+        monkeypatch.setenv("NLDSC_TEST_READER0_LAG_US", lag)
         got = capi.calculate(str(tmp_path / "big.bed"), *args)
         for key in RESULT_KEYS:
             assert np.array_equal(got[key], mem[key], equal_nan=True), key
