@@ -37,7 +37,7 @@ def main():
         out.append("kernel: " + ", ".join(r[name_col].split("(")[0] for r in data))
         traffic = []
         for i, h in enumerate(hdr):
-            if h in KEEP:
+            if h in KEEP or any(h.endswith("." + k) or h.endswith(k) for k in KEEP if "tensor" in k or "fp64" in k):
                 out.append(f"{h} [{units[i]}]: " + ", ".join(r[i] for r in data))
         rd, wr = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
         scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
