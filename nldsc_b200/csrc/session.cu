@@ -713,8 +713,12 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // upload (`ramp`) a chunk cannot start before its last row has landed, so chunks start small, double,
     // and stop at half the regular size.
     const bool fixed_rows = getenv("NLDSC_CHUNK_ROWS") != nullptr;
+    // With a concurrent upload a chunk also waits for all of its bytes, and the last chunk is scored after the
+    // last byte has landed: cap it in BYTES (NLDSC_CHUNK_BYTES, default 256 MB = ~5 ms of PCIe) so that wait
+    // stays short when rows are long (N = 315,599: 16,384 rows would be 1.3 GB = 24 ms).
+    const size_t byte_rows = std::max<size_t>(2048, env_size("NLDSC_CHUNK_BYTES", size_t(256) << 20) / static_cast<size_t>(s->bps) / kBlk * kBlk);
     const int32_t chunk_rows = static_cast<int32_t>(
-        std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? 16384 : 32768),
+        std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? std::min<size_t>(16384, byte_rows) : 32768),
                          static_cast<size_t>(std::numeric_limits<int32_t>::max() / 2)));
     // without a concurrent upload a short first chunk still pays: its unpack is the only one that runs alone
     const char* rp = getenv("NLDSC_RAMP");
@@ -722,7 +726,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // first chunk with a concurrent upload: what has landed by the time the plan is built and shipped
     // (~0.7 ms of PCIe, ~40 MB), so its kernels neither wait for data nor start needlessly small
     const int64_t landed = static_cast<int64_t>(env_size("NLDSC_FIRST_BYTES", size_t(40) << 20)) / std::max<int64_t>(1, s->bps);
-    const int32_t first_rows = static_cast<int32_t>(std::min<int64_t>(chunk_rows, std::max<int64_t>(4096, landed / 4096 * 4096)));
+    const int32_t first_rows = static_cast<int32_t>(std::min<int64_t>(chunk_rows, std::max<int64_t>(512, landed / kBlk * kBlk)));
     int32_t ramp_rows = (ramp0 && !fixed_rows) ? (ramp ? first_rows : 8192) : chunk_rows;
     const char* tp = getenv("NLDSC_TAPER");
     // taper the chunk size towards the end of the shard only when the upload is clearly the longer pole
