@@ -454,6 +454,7 @@ static void session_free(nldsc_ld_session* s) {
     if (s->own_stream) cudaStreamSynchronize(s->own_stream);
     if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);
     if (s->unpack_stream) cudaStreamSynchronize(s->unpack_stream);
+    if (s->band2_stream) cudaStreamSynchronize(s->band2_stream);
     arena_release(s->arena);
     host_stage_release(s->stage);
     plan_stage_release(s->pstage);
@@ -467,6 +468,8 @@ static void session_free(nldsc_ld_session* s) {
     for (auto e : s->ev_band) ev_put(s->device, false, e);
     ev_put(s->device, false, s->ev_fork);
     stream_put(s->device, 2, s->unpack_stream);
+    stream_put(s->device, 0, s->band2_stream);
+    ev_put(s->device, false, s->ev_join);
     ev_put(s->device, true, s->ev_run0);
     ev_put(s->device, true, s->ev_run1);
     stream_put(s->device, 0, s->own_stream);
@@ -508,6 +511,8 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     s->own_stream = stream_get(device, 0);
     s->copy_stream = stream_get(device, 1);
     s->unpack_stream = stream_get(device, 2);
+    s->band2_stream = stream_get(device, 0);
+    s->ev_join = ev_get(device, false);
     s->ev_fork = ev_get(device, false);
     // the 16 bytes of slack the word-wise kernels may read past the last row
     CUDA_CHECK(cudaMemsetAsync(s->d_packed + static_cast<size_t>(s->n_load) * s->bps, 0, 16, s->copy_stream));
@@ -833,6 +838,11 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     s->part.wsa = amalloc<int32_t>(s->arena, np);
     s->part.wsd = amalloc<int32_t>(s->arena, np);
     s->part.wsde = amalloc<int32_t>(s->arena, np);
+    s->part2.add = amalloc<double>(s->arena, np);
+    s->part2.dom = amalloc<double>(s->arena, np);
+    s->part2.wsa = amalloc<int32_t>(s->arena, np);
+    s->part2.wsd = amalloc<int32_t>(s->arena, np);
+    s->part2.wsde = amalloc<int32_t>(s->arena, np);
     if (!s->use_simt) s->maps = band_maps_create(s->d_planes, s->plane_rows, s->npad);
     // the plan is consumed by kernels on the session's own stream or on a caller's stream
     s->ev_planned = ev_get(s->device, false);
@@ -874,9 +884,14 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     const char* ov = getenv("NLDSC_OVERLAP");
     const bool overlap = !(ov && ov[0] == '0');
     cudaStream_t us = overlap ? s->unpack_stream : st;
+    // band launches alternate between two streams: every launch is a full persistent grid, so the CTA pairs of
+    // chunk c+1 start on the SMs that chunk c's partial last wave leaves idle instead of after its slowest pair
+    const char* bsn = getenv("NLDSC_BAND_STREAMS");
+    const bool two_band = overlap && !(bsn && bsn[0] == '1') && s->chunks.size() > 1;
     if (overlap) {
         CUDA_CHECK(cudaEventRecord(s->ev_fork, st));
         CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_fork, 0));
+        if (two_band) CUDA_CHECK(cudaStreamWaitEvent(s->band2_stream, s->ev_fork, 0));
         while (s->ev_unpacked.size() < s->chunks.size()) {
             s->ev_unpacked.push_back(ev_get(s->device, false));
             s->ev_band.push_back(ev_get(s->device, false));
@@ -885,6 +900,8 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     int32_t next_piece = 0;                 // pieces below this one have been waited for on the unpack stream
     for (size_t ci = 0; ci < s->chunks.size(); ++ci) {
         const Chunk& c = s->chunks[ci];
+        const bool odd = two_band && (ci & 1);
+        cudaStream_t bs = odd ? s->band2_stream : st;
         const int32_t r0 = std::min(c.new_row0, s->n_load), r1 = std::min(c.new_row1, s->n_load);
         if (r1 > r0) {
             // the chunk's kernels wait on the device for the last piece they read; the event must have
@@ -910,6 +927,8 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
                 if (col0 < first_safe) wait_for = static_cast<int64_t>(k);
             }
             if (wait_for >= 0) CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_band[wait_for], 0));
+            // band launches alternate between two streams: the one before it ran on the other stream
+            if (wait_for >= 1 && two_band) CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_band[wait_for - 1], 0));
         }
         {
             // unpack the chunk's new rows into the ring; the same pass counts their genotypes
@@ -927,7 +946,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         }
         if (overlap) {
             CUDA_CHECK(cudaEventRecord(s->ev_unpacked[ci], us));
-            CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_unpacked[ci], 0));
+            CUDA_CHECK(cudaStreamWaitEvent(bs, s->ev_unpacked[ci], 0));
         }
         BandArgs a{};
         a.tiles = s->d_tiles + c.tile0;
@@ -942,24 +961,24 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         a.inv_n = 1.0 / n;
         a.adj_c = (n - 1.0) / (n - 2.0);
         a.rsq_thr = s->rsq_thr;
-        a.part = s->part;
+        a.part = odd ? s->part2 : s->part;
         a.dump = nullptr;
         {
-            SpanScope sc(s, st, kFamBand);
+            SpanScope sc(s, bs, kFamBand);
             if (s->use_simt)
-                launch_band_simt(s->d_planes, s->plane_rows * static_cast<int64_t>(s->npad), s->npad, a, st);
+                launch_band_simt(s->d_planes, s->plane_rows * static_cast<int64_t>(s->npad), s->npad, a, bs);
             else
-                launch_band_tc(s->maps, a, s->sm_count, st);
+                launch_band_tc(s->maps, a, s->sm_count, bs);
             ++s->launches;
         }
-        if (overlap) CUDA_CHECK(cudaEventRecord(s->ev_band[ci], st));
+        if (overlap) CUDA_CHECK(cudaEventRecord(s->ev_band[ci], bs));
         FinalizeArgs f{};
         f.tile_begin = s->d_tile_begin + c.tb0;
         f.iblock0 = c.iblock0;
         f.n_iblocks = c.n_iblocks;
         f.own_begin = s->own_begin;
         f.own_end = s->own_end;
-        f.part = s->part;
+        f.part = odd ? s->part2 : s->part;
         f.flags = s->d_flags;
         f.l2 = s->d_l2;
         f.l2d = s->d_l2d;
@@ -967,10 +986,14 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         f.wsd = s->d_wsd;
         f.wsde = s->d_wsde;
         {
-            SpanScope sc(s, st, kFamFinalize);
-            launch_finalize(f, st);
+            SpanScope sc(s, bs, kFamFinalize);
+            launch_finalize(f, bs);
             ++s->launches;
         }
+    }
+    if (two_band) {
+        CUDA_CHECK(cudaEventRecord(s->ev_join, s->band2_stream));
+        CUDA_CHECK(cudaStreamWaitEvent(st, s->ev_join, 0));
     }
     CUDA_CHECK(cudaEventRecord(s->ev_run1, st));
     s->ran = true;
@@ -1348,10 +1371,30 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* o) {
         cudaSetDevice(s->device);
         if (cudaEventSynchronize(s->ev_run1) != cudaSuccess) return NLDSC_ERR_RUNTIME;
         float fam[kFamN] = {0, 0, 0, 0, 0};
+        // band launches of consecutive chunks overlap (two streams): their time is the union of the spans, not the sum
+        std::vector<std::pair<float, float>> band;
         for (size_t i = 0; i < s->spans_used; ++i) {
             float ms = 0;
-            if (cudaEventElapsedTime(&ms, s->spans[i].a, s->spans[i].b) == cudaSuccess) fam[s->spans[i].family] += ms;
+            if (s->spans[i].family == kFamBand) {
+                float t0 = 0, t1 = 0;
+                if (cudaEventElapsedTime(&t0, s->ev_run0, s->spans[i].a) == cudaSuccess &&
+                    cudaEventElapsedTime(&t1, s->ev_run0, s->spans[i].b) == cudaSuccess)
+                    band.emplace_back(t0, t1);
+            } else if (cudaEventElapsedTime(&ms, s->spans[i].a, s->spans[i].b) == cudaSuccess) {
+                fam[s->spans[i].family] += ms;
+            }
         }
+        std::sort(band.begin(), band.end());
+        float cur0 = 0, cur1 = -1;
+        for (const auto& iv : band) {
+            if (cur1 < cur0 || iv.first > cur1) {
+                if (cur1 >= cur0) fam[kFamBand] += cur1 - cur0;
+                cur0 = iv.first; cur1 = iv.second;
+            } else {
+                cur1 = std::max(cur1, iv.second);
+            }
+        }
+        if (cur1 >= cur0) fam[kFamBand] += cur1 - cur0;
         o->ms_count = fam[kFamCount];
         o->ms_stats = fam[kFamStats];
         o->ms_unpack = fam[kFamUnpack];

@@ -113,6 +113,7 @@ struct nldsc_ld_session {
     nldsc::Tile* d_tiles = nullptr;
     int32_t* d_tile_begin = nullptr;
     nldsc::Partials part{};
+    nldsc::Partials part2{};                  // odd chunks (second band stream)
     double* d_l2 = nullptr;
     double* d_l2d = nullptr;
     int32_t* d_wsa = nullptr;
@@ -124,6 +125,8 @@ struct nldsc_ld_session {
     cudaStream_t unpack_stream = nullptr;     // unpack + stats of chunk c+1 run beside the band kernel of chunk c
     std::vector<cudaEvent_t> ev_unpacked;     // per chunk: planes, coefficients and flags are ready
     std::vector<cudaEvent_t> ev_band;         // per chunk: the band kernel no longer reads its ring rows
+    cudaStream_t band2_stream = nullptr;      // band + finalize of odd chunks: the next launch fills the SMs the last wave of this one leaves idle
+    cudaEvent_t ev_join = nullptr;
     cudaEvent_t ev_fork = nullptr;            // run() start on the compute stream, seen by the unpack stream
     int32_t piece_rows = 0;                   // rows per upload piece (multiple of 64)
     std::vector<cudaEvent_t> ev_piece;        // piece has landed in d_packed
