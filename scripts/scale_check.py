@@ -12,10 +12,12 @@ CASES = {
     "ukb_slice":  dict(n_org=315599, n_snp=40000, missing=0.02, density=340.0, wind=1.0, oracle_rows=2),
     "ukb_ring":   dict(n_org=315599, n_snp=40000, missing=0.02, density=340.0, wind=1.0, oracle_rows=0,
                        env={"NLDSC_PLANE_BYTES": "12e9"}),
+    # BASELINE.json configs[4] at full size: 7.5 GB .bed, interior window ~20,000 SNPs, ~5.8e9 ordered pairs
+    "cfg5_full":  dict(n_org=100000, n_snp=300000, missing=0.02, density=1000.0, wind=10.0, oracle_rows=1),
     "wide_band":  dict(n_org=100000, n_snp=40000, missing=0.02, density=200.0, wind=10.0, oracle_rows=1),
 }
 out = {}
-for name in (sys.argv[1:] or list(CASES)):
+for name in (sys.argv[1:] or [k for k in CASES if k != "cfg5_full"]):
     c = CASES[name]
     for k, v in c.get("env", {}).items():
         os.environ[k] = v
@@ -82,4 +84,4 @@ for name in (sys.argv[1:] or list(CASES)):
         os.environ.pop(k, None)
     del host
 os.makedirs("gpurun_out", exist_ok=True)
-json.dump(out, open("gpurun_out/scale_check.json", "w"), indent=1)
+json.dump(out, open("gpurun_out/scale_check%s.json" % ("_" + "_".join(sys.argv[1:]) if sys.argv[1:] else ""), "w"), indent=1)
