@@ -304,7 +304,7 @@ def main():
     barrier()
     e2e_wall = max_over_ranks(time.perf_counter() - t0)
     e2e = {"value": pairs_total * args.steps / e2e_wall, "unit": UNIT, "ms_per_step": 1e3 * e2e_wall / args.steps,
-           "h2d_bytes_per_step": int(N_SNP * bps + 8 * N_SNP + 16 * st["tiles"]),
+           "h2d_bytes_per_step": int(N_SNP * bps + 8 * N_SNP + 32 * st["tiles"]),
            "d2h_bytes_per_step": int(N_SNP * (4 * 8 + 3 * 4))}
     for k in res:
         assert np.array_equal(res[k], out[0][k], equal_nan=True), "e2e result differs from resident run: " + k

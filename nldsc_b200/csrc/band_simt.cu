@@ -94,7 +94,7 @@ band_simt_kernel(const int8_t* __restrict__ planes, int64_t plane_stride, int32_
         ra.wsde += __shfl_xor_sync(0xFFFFFFFFu, ra.wsde, o);
     }
     if (cg == 0) {
-        const int64_t o = (int64_t)blockIdx.x * kBlk + s;
+        const int64_t o = ((int64_t)tl.slot * 2 + rank) * kBlk + s;
         args.part.add[o] = ra.add;
         args.part.dom[o] = ra.dom;
         args.part.wsa[o] = ra.wsa;

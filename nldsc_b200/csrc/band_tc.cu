@@ -253,7 +253,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 tmem_ld16(taddr + col + 64, va);
                 tmem_ld_wait();
                 if (args.dump != nullptr) {
-                    int32_t* drow = args.dump + ((static_cast<int64_t>(t) * 2 + rank) * kARows + 32 * q + lane) * kBRows;
+                    int32_t* drow = args.dump + ((static_cast<int64_t>(tl.slot) * 2 + rank) * kARows + 32 * q + lane) * kBRows;
 #pragma unroll
                     for (int e = 0; e < 16; ++e) {
                         drow[16 * c + e] = vm[e];
@@ -288,7 +288,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
             acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
             if (is_g) {
-                const int64_t o = (static_cast<int64_t>(t) * 2 + rank) * kBlk + s;
+                const int64_t o = (static_cast<int64_t>(tl.slot) * 2 + rank) * kBlk + s;
                 args.part.add[o] = acc.add;
                 args.part.dom[o] = acc.dom;
                 args.part.wsa[o] = acc.wsa;

@@ -41,6 +41,10 @@ struct Tile {
     int32_t i0[2];     // first SNP (shard-local index) of each i-block, or kDeadBlock
     int32_t b_row;     // row of the j-block inside the plane ring
     int32_t j0;        // first SNP (shard-local index) of the j-block
+    int32_t slot;      // where its partial row sums go: position in i-pair-major order (what finalize walks), which is
+                       // NOT the execution order -- tiles of 8 i-pairs are interleaved by j-block so that concurrent
+                       // CTA pairs share B operands in L2 as well as A (wide windows would otherwise stream B from HBM)
+    int32_t pad_;
 };
 
 // Per-row partial sums a supertile contributes (SoA, index = (tile * 2 + rank) * 64 + row).

@@ -790,19 +790,39 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         c.new_row1 = std::max(col1, c.new_row0);
         unpacked_to = c.new_row1;
         // supertile rows: i-blocks (k, k+1) share their j-blocks; windows are monotone, so the union of
-        // the two j ranges is [jb_lo[k], jb_hi[k+1]] (pairs outside a block's own window score nothing)
-        for (int32_t k = b; k < e; k += 2) {
-            tile_begin.push_back(static_cast<int32_t>(tiles.size() - c.tile0));
-            const bool two = k + 1 < e;
-            for (int32_t jb = jb_lo[k]; jb <= (two ? jb_hi[k + 1] : jb_hi[k]); ++jb) {
-                Tile t;
-                t.i0[0] = (ib0 + k) * kBlk;
-                t.i0[1] = two ? (ib0 + k + 1) * kBlk : kDeadBlock;
-                t.a_row[0] = static_cast<int32_t>(t.i0[0] % cap);
-                t.a_row[1] = two ? static_cast<int32_t>(t.i0[1] % cap) : t.a_row[0];
-                t.j0 = jb * kBlk;
-                t.b_row = static_cast<int32_t>(t.j0 % cap);
-                tiles.push_back(t);
+        // the two j ranges is [jb_lo[k], jb_hi[k+1]] (pairs outside a block's own window score nothing).
+        // Slots (where partials go, what finalize walks) are i-pair-major; the EXECUTION order interleaves
+        // the tiles of kRaster consecutive i-pairs by j-block: the ~74 supertiles in flight then cover
+        // ~8 i-pairs x ~9 j-blocks, so every A slice is shared by ~9 CTA pairs and every B slice by ~8.
+        constexpr int32_t kRaster = 8;
+        std::vector<int32_t> slot0;                       // first slot of every i-pair of the chunk
+        {
+            int32_t nslots = 0;
+            for (int32_t k = b; k < e; k += 2) {
+                tile_begin.push_back(nslots);
+                slot0.push_back(nslots);
+                nslots += pair_tiles(k, e);
+            }
+        }
+        for (int32_t g0 = b; g0 < e; g0 += 2 * kRaster) {
+            const int32_t g1 = std::min(e, g0 + 2 * kRaster);
+            const int32_t last = g1 - 1 - ((g1 - 1 - g0) % 2);                    // first block of the group's last i-pair
+            const int32_t jb_first = jb_lo[g0], jb_last = (last + 1 < e ? jb_hi[last + 1] : jb_hi[last]);
+            for (int32_t jb = jb_first; jb <= jb_last; ++jb) {
+                for (int32_t k = g0; k < g1; k += 2) {
+                    const bool two = k + 1 < e;
+                    if (jb < jb_lo[k] || jb > (two ? jb_hi[k + 1] : jb_hi[k])) continue;
+                    Tile t;
+                    t.i0[0] = (ib0 + k) * kBlk;
+                    t.i0[1] = two ? (ib0 + k + 1) * kBlk : kDeadBlock;
+                    t.a_row[0] = static_cast<int32_t>(t.i0[0] % cap);
+                    t.a_row[1] = two ? static_cast<int32_t>(t.i0[1] % cap) : t.a_row[0];
+                    t.j0 = jb * kBlk;
+                    t.b_row = static_cast<int32_t>(t.j0 % cap);
+                    t.slot = slot0[(k - b) / 2] + (jb - jb_lo[k]);
+                    t.pad_ = 0;
+                    tiles.push_back(t);
+                }
             }
         }
         tile_begin.push_back(static_cast<int32_t>(tiles.size() - c.tile0));
@@ -1568,7 +1588,7 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         std::vector<Tile> tiles(n_tiles);
         for (int32_t t = 0; t < n_tiles; ++t) {       // band-like walk: 22 j-blocks per i-block pair
             const int32_t p = (t / 22) % (nb / 2), jb = (2 * p + t % 22) % nb;
-            tiles[t] = Tile{{2 * p * kBlk, (2 * p + 1) * kBlk}, {2 * p * kBlk, (2 * p + 1) * kBlk}, jb * kBlk, jb * kBlk};
+            tiles[t] = Tile{{2 * p * kBlk, (2 * p + 1) * kBlk}, {2 * p * kBlk, (2 * p + 1) * kBlk}, jb * kBlk, jb * kBlk, t, 0};
         }
         CUDA_CHECK(cudaMemcpy(d_tiles, tiles.data(), sizeof(Tile) * n_tiles, cudaMemcpyHostToDevice));
         BandArgs a{};
