@@ -1,0 +1,70 @@
+"""GPU (-m gpu): seeded random shapes x execution knobs against the CPU oracle.
+
+Every case draws organisms, SNPs, missingness, map density and window at random, then runs the C-ABI path
+under one randomly chosen execution variant (tiny chunks, a plane ring barely wider than a window, one
+stream, one band stream, SIMT band kernel, 2 shards when the box has 2 GPUs).  All variants must meet the
+parity bar against the oracle, and be bitwise equal to the default variant of the same case."""
+import numpy as np
+import pytest
+
+from conftest import RESULT_KEYS, assert_ld_close
+from nldsc_b200 import build, capi, synth
+from oracle import ld_oracle
+
+pytestmark = pytest.mark.gpu
+
+VARIANTS = [
+    {},
+    {"NLDSC_CHUNK_ROWS": "64"},
+    {"NLDSC_CHUNK_ROWS": "192", "NLDSC_PLANE_BYTES": "ring"},
+    {"NLDSC_OVERLAP": "0"},
+    {"NLDSC_BAND_STREAMS": "1", "NLDSC_CHUNK_ROWS": "128"},
+    {"NLDSC_BAND": "simt"},
+    {"NLDSC_GPUS": "2"},
+    {"NLDSC_CHUNK_ROWS": "128", "NLDSC_PLANE_BYTES": "ring", "NLDSC_GPUS": "2"},
+]
+
+
+@pytest.fixture(scope="module", autouse=True)
+def built():
+    build.build_module()
+
+
+def _draw(seed):
+    rng = np.random.default_rng(1000 + seed)
+    n_org = int(rng.choice([3, 5, 64, 127, 128, 129, 255, 300, 513, 777, 1001, 1026, 1500]))
+    n_snp = int(rng.choice([1, 2, 63, 64, 65, 127, 129, 200, 333, 640, 900]))
+    missing = float(rng.choice([0.0, 0.0, 0.01, 0.05, 0.3]))
+    density = float(rng.choice([20.0, 100.0, 340.0, 2000.0]))
+    wind = float(rng.choice([0.01, 0.1, 0.5, 1.0, 50.0]))
+    return n_org, n_snp, missing, density, wind
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_random_case_matches_oracle(seed, monkeypatch):
+    n_org, n_snp, missing, density, wind = _draw(seed)
+    spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=missing, seed=500 + seed, density=density)
+    packed = synth.generate_packed(spec, workers=1)
+    cm, _ = synth.genetic_map(spec)
+    args = (n_snp, n_org, cm, wind, 1e-4, 1e-5, 1.0 / max(n_snp, 11))
+    want = ld_oracle.ld_scores(packed, n_org, cm, wind, 1e-4, 1e-5, 1.0 / max(n_snp, 11))
+    base = capi.calculate_packed(packed, *args)
+    label = f"seed {seed}: N={n_org} M={n_snp} miss={missing} dens={density} wind={wind}"
+    # r2adj(dom) sits within rounding of rsq_thr for some pairs at tiny N: WSDE may differ there by design of the bar
+    assert_ld_close(base, want, exact_wsde=n_org >= 64, label=label)
+    variant = dict(VARIANTS[seed % len(VARIANTS)])
+    if variant.get("NLDSC_PLANE_BYTES") == "ring":
+        lo, hi = capi.plan_windows(cm, wind)
+        span = int(np.max(hi - lo)) + 1
+        rows = (span // 64 + 6) * 64                               # a block pair's columns, and little more
+        variant["NLDSC_PLANE_BYTES"] = str(rows * 4 * ((n_org + 127) // 128 * 128))
+    if variant.get("NLDSC_GPUS") == "2" and capi.device_count() < 2:
+        variant.pop("NLDSC_GPUS")
+    for k, v in variant.items():
+        monkeypatch.setenv(k, v)
+    got = capi.calculate_packed(packed, *args)
+    if variant.get("NLDSC_BAND") == "simt":
+        assert_ld_close(got, want, exact_wsde=n_org >= 64, label=label + " " + str(variant))
+    else:
+        for key in RESULT_KEYS:
+            assert np.array_equal(got[key], base[key], equal_nan=True), f"{label} {variant}: {key} differs from the default run"
