@@ -175,6 +175,13 @@ PYBIND11_MODULE(_ldscore, m) {
     m.def("calculate_on", &calculate_impl, py::arg("params"), py::arg("first_device"), py::arg("n_devices") = 1,
           "calculate() on GPUs first_device .. first_device + n_devices - 1 instead of NLDSC_DEVICE / NLDSC_GPUS; "
           "thread-safe, so one process can score several chromosomes at once");
+    m.def("device_count", [] {
+        int32_t n = 0;
+        char err[512] = {0};
+        const int rc = nldsc_ld_device_count(&n, err, sizeof(err));
+        if (rc != NLDSC_OK) throw std::runtime_error(err);
+        return n;
+    }, "usable sm_100 devices");
     m.def("as_arrays", [](py::object r) {
         LDScoreResult& v = r.cast<LDScoreResult&>();
         py::dict d;

@@ -794,7 +794,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         // Slots (where partials go, what finalize walks) are i-pair-major; the EXECUTION order interleaves
         // the tiles of kRaster consecutive i-pairs by j-block: the ~74 supertiles in flight then cover
         // ~8 i-pairs x ~9 j-blocks, so every A slice is shared by ~9 CTA pairs and every B slice by ~8.
-        constexpr int32_t kRaster = 8;
+        const int32_t kRaster = static_cast<int32_t>(std::max<size_t>(1, std::min<size_t>(64, env_size("NLDSC_RASTER", 8))));
         std::vector<int32_t> slot0;                       // first slot of every i-pair of the chunk
         {
             int32_t nslots = 0;

@@ -209,7 +209,7 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     os.makedirs(out_dir, exist_ok=True)
     if gpus is None:
         gpus = int(os.environ.get("NLDSC_GPUS", "1")) if os.environ.get("NLDSC_GPUS", "1") != "all" else 64
-    n_dev = max(1, min(int(gpus), len(jobs)))
+    n_dev = max(1, min(int(gpus), len(jobs), max(1, lds.device_count() - first_device)))
     jobs.sort(key=lambda j: -os.path.getsize(j[1] + ".bed"))          # longest first
     todo: queue.Queue = queue.Queue()
     for j in jobs:

@@ -14,10 +14,11 @@ CASES = {
                        env={"NLDSC_PLANE_BYTES": "12e9"}),
     # BASELINE.json configs[4] at full size: 7.5 GB .bed, interior window ~20,000 SNPs, ~5.8e9 ordered pairs
     "cfg5_full":  dict(n_org=100000, n_snp=300000, missing=0.02, density=1000.0, wind=10.0, oracle_rows=1),
+    "cfg5_slice": dict(n_org=100000, n_snp=49152, missing=0.02, density=1000.0, wind=10.0, oracle_rows=0),
     "wide_band":  dict(n_org=100000, n_snp=40000, missing=0.02, density=200.0, wind=10.0, oracle_rows=1),
 }
 out = {}
-for name in (sys.argv[1:] or [k for k in CASES if k != "cfg5_full"]):
+for name in (sys.argv[1:] or [k for k in CASES if k not in ("cfg5_full", "cfg5_slice")]):
     c = CASES[name]
     for k, v in c.get("env", {}).items():
         os.environ[k] = v
