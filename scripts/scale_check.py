@@ -18,6 +18,7 @@ CASES = {
     "wide_band":  dict(n_org=100000, n_snp=40000, missing=0.02, density=200.0, wind=10.0, oracle_rows=1),
 }
 out = {}
+kept_results = {}
 for name in (sys.argv[1:] or [k for k in CASES if k not in ("cfg5_full", "cfg5_slice")]):
     c = CASES[name]
     for k, v in c.get("env", {}).items():
@@ -62,6 +63,9 @@ for name in (sys.argv[1:] or [k for k in CASES if k not in ("cfg5_full", "cfg5_s
                        "tiles": st["tiles"], "band_algorithmic_top_s": ops / (st["ms_band"] * 1e-3) / 1e12,
                        "band_executed_top_s": st["tiles"] * 2 * 128 * 192 * 2.0 * st["npad"] / (st["ms_band"] * 1e-3) / 1e12,
                        "step_algorithmic_top_s": ops / (st["ms_total"] * 1e-3) / 1e12}
+    kept_results[name] = {k: v.copy() for k, v in got.items()}
+    if name == "ukb_ring" and "ukb_slice" in kept_results:      # a 12 GB ring that wraps vs all rows resident
+        rec["bitwise_equal_to_ukb_slice"] = bool(all(np.array_equal(got[k], kept_results["ukb_slice"][k], equal_nan=True) for k in got))
     hn = host.numpy()
     rng = np.random.default_rng(1)
     errs = []
