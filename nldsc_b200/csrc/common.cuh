@@ -96,7 +96,8 @@ void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n
 void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
                    int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
                    int32_t dst_row0, int32_t* counts, cudaStream_t st);   // counts != null: += genotype counts (zeroed by the caller)
-void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st);
+void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st,
+                    int32_t n_pad = 0, unsigned long long* total = nullptr);   // rows n..n_pad-1 get the empty window (1, 0)
 void launch_copy16(const void* src, void* dst, size_t bytes, cudaStream_t st);   // SM copy, either side may be pinned host memory
 void launch_zero_rows(int8_t* planes, int64_t plane_stride, int32_t npad, int32_t row0,
                       int32_t n_rows, cudaStream_t st);

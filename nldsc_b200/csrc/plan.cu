@@ -12,30 +12,47 @@
 
 namespace nldsc {
 
+// Threads n <= i < n_pad write the empty window (1, 0) of a padding row; `total` (optional) receives
+// sum_i (hi[i] - lo[i]) = the ordered in-window pairs before the MAF filter.
 __global__ void __launch_bounds__(256)
-windows_kernel(const double* __restrict__ pos, int32_t n, double wind, int32_t* __restrict__ lo,
-               int32_t* __restrict__ hi) {
+windows_kernel(const double* __restrict__ pos, int32_t n, int32_t n_pad, double wind, int32_t* __restrict__ lo,
+               int32_t* __restrict__ hi, unsigned long long* __restrict__ total) {
     const int32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const double pi = pos[i];
-    // the predicate is monotone on either side of i (sorted positions, monotone IEEE subtraction)
-    int32_t x = 0, y = i;                       // smallest l in [0, i] inside the window
-    while (x < y) {
-        const int32_t m = x + ((y - x) >> 1);
-        if (fabs(pos[m] - pi) <= wind) y = m; else x = m + 1;
+    int32_t width = 0;
+    if (i < n) {
+        const double pi = pos[i];
+        // the predicate is monotone on either side of i (sorted positions, monotone IEEE subtraction)
+        int32_t x = 0, y = i;                       // smallest l in [0, i] inside the window
+        while (x < y) {
+            const int32_t m = x + ((y - x) >> 1);
+            if (fabs(pos[m] - pi) <= wind) y = m; else x = m + 1;
+        }
+        lo[i] = x;
+        width = -x;
+        x = i; y = n - 1;                           // largest r in [i, n-1] inside the window
+        while (x < y) {
+            const int32_t m = x + ((y - x + 1) >> 1);
+            if (fabs(pos[m] - pi) <= wind) x = m; else y = m - 1;
+        }
+        hi[i] = x;
+        width += x;
+    } else if (i < n_pad) {
+        lo[i] = 1;
+        hi[i] = 0;
     }
-    lo[i] = x;
-    x = i; y = n - 1;                           // largest r in [i, n-1] inside the window
-    while (x < y) {
-        const int32_t m = x + ((y - x + 1) >> 1);
-        if (fabs(pos[m] - pi) <= wind) x = m; else y = m - 1;
+    if (total != nullptr) {                         // grid-uniform
+        unsigned long long w = static_cast<unsigned long long>(width);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) w += __shfl_xor_sync(0xFFFFFFFFu, w, o);
+        if ((threadIdx.x & 31) == 0 && w) atomicAdd(total, w);
     }
-    hi[i] = x;
 }
 
-void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st) {
+void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st,
+                    int32_t n_pad, unsigned long long* total) {
     if (n <= 0) return;
-    windows_kernel<<<(n + 255) / 256, 256, 0, st>>>(pos, n, wind, lo, hi);
+    if (n_pad < n) n_pad = n;
+    windows_kernel<<<(n_pad + 255) / 256, 256, 0, st>>>(pos, n, n_pad, wind, lo, hi, total);
     CUDA_CHECK(cudaGetLastError());
 }
 

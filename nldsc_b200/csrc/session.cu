@@ -626,12 +626,19 @@ static void join_reader(nldsc_ld_session* s) {
 // Stage 2: windows -> owned i-blocks -> plane ring -> chunks and supertiles, and their device copies.
 // `ramp`: start with small chunks and double up to the regular size -- for the calculate* entry points,
 // where the upload runs concurrently and the first kernels should start after a few MB have landed.
+// `whole_pos` (one shard = the whole file, load range [0, n_snp)): the per-row windows are computed ON the device
+// straight into d_win_lo / d_win_hi and never visit the host; the host only needs the j-block range of every
+// i-block, which it gets from two bisections per block with the same predicate.  `lo` / `hi` are not read then.
 static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end, const std::vector<int32_t>& lo,
-                         const std::vector<int32_t>& hi, bool ramp = false) {
+                         const std::vector<int32_t>& hi, bool ramp = false, const double* whole_pos = nullptr,
+                         double wind = 0.0) {
     if (row_begin < 0 || row_end > s->n_snp || row_begin >= row_end)
         throw InvalidArgument("shard row range is empty or outside [0, n_snp)");
+    const bool fast = whole_pos != nullptr;
+    if (fast && (s->load_begin != 0 || s->load_end != s->n_snp || row_begin != 0 || row_end != s->n_snp))
+        throw InvalidArgument("whole-file planning needs the shard to be the whole file");
     // rows this shard needs: owned range widened by the window halo, 64-aligned on the left
-    if (s->load_begin > floor64(lo[row_begin]) || s->load_end < hi[row_end - 1] + 1)
+    if (!fast && (s->load_begin > floor64(lo[row_begin]) || s->load_end < hi[row_end - 1] + 1))
         throw InvalidArgument("shard load range does not cover the window halo of its rows");
     CUDA_CHECK(cudaSetDevice(s->device));
     Tracer tr;
@@ -647,13 +654,32 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // live in the session until the async copies have been consumed.
     std::vector<int32_t>& wlo = s->h_win_lo;
     std::vector<int32_t>& whi = s->h_win_hi;
-    wlo.assign(n_load_pad, 1);
-    whi.assign(n_load_pad, 0);
-    for (int32_t i = 0; i < n_load; ++i) {
-        wlo[i] = std::max(lo[i + s->load_begin] - s->load_begin, 0);
-        whi[i] = std::min(hi[i + s->load_begin] - s->load_begin, n_load - 1);
+    if (!fast) {
+        wlo.assign(n_load_pad, 1);
+        whi.assign(n_load_pad, 0);
+        for (int32_t i = 0; i < n_load; ++i) {
+            wlo[i] = std::max(lo[i + s->load_begin] - s->load_begin, 0);
+            whi[i] = std::min(hi[i + s->load_begin] - s->load_begin, n_load - 1);
+        }
+        for (int32_t i = s->own_begin; i < s->own_end; ++i) s->total_pairs += whi[i] - wlo[i];
     }
-    for (int32_t i = s->own_begin; i < s->own_end; ++i) s->total_pairs += whi[i] - wlo[i];
+    // window edges of single rows on the host: the same bisections, the same IEEE expression as windows_kernel
+    auto row_lo = [&](int32_t i) {
+        int32_t x = 0, y = i;
+        while (x < y) {
+            const int32_t m = x + ((y - x) >> 1);
+            if (std::abs(whole_pos[m] - whole_pos[i]) <= wind) y = m; else x = m + 1;
+        }
+        return x;
+    };
+    auto row_hi = [&](int32_t i) {
+        int32_t x = i, y = n_load - 1;
+        while (x < y) {
+            const int32_t m = x + ((y - x + 1) >> 1);
+            if (std::abs(whole_pos[m] - whole_pos[i]) <= wind) x = m; else y = m - 1;
+        }
+        return x;
+    };
 
     // ---- owned i-blocks and the j-block range each one needs
     const int32_t ib0 = s->own_begin / kBlk, ib1 = (s->own_end - 1) / kBlk + 1;
@@ -662,9 +688,11 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     int32_t max_span = 0;
     for (int32_t b = ib0; b < ib1; ++b) {
         const int32_t r0 = std::max(b * kBlk, s->own_begin), r1 = std::min(b * kBlk + kBlk, s->own_end) - 1;
-        jb_lo[b - ib0] = wlo[r0] / kBlk;
-        jb_hi[b - ib0] = whi[r1] / kBlk;
+        jb_lo[b - ib0] = (fast ? row_lo(r0) : wlo[r0]) / kBlk;
+        jb_hi[b - ib0] = (fast ? row_hi(r1) : whi[r1]) / kBlk;
         max_span = std::max(max_span, (jb_hi[b - ib0] - jb_lo[b - ib0] + 1) * kBlk);
+        // the exact count comes back from the device with the results; this estimate only steers the chunk schedule
+        if (fast) s->total_pairs += static_cast<int64_t>(r1 - r0 + 1) * std::max(0, (jb_hi[b - ib0] - jb_lo[b - ib0]) * kBlk);
     }
     // a CTA pair scores two adjacent i-blocks against the union of their column ranges
     for (int32_t b = 0; b + 1 < n_ib; ++b)
@@ -687,6 +715,21 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     s->d_wsa = amalloc<int32_t>(s->arena, n_own);
     s->d_wsd = amalloc<int32_t>(s->arena, n_own);
     s->d_wsde = amalloc<int32_t>(s->arena, n_own);
+    int64_t tiles_bound = 0;                      // >= supertiles under any pairing: one per (i-block, j-block)
+    for (int32_t b = 0; b < n_ib; ++b) tiles_bound += jb_hi[b] - jb_lo[b] + 2;
+    auto pad16 = [](size_t b) { return (b + 15) & ~size_t(15); };
+    const size_t b_pos = fast ? pad16(sizeof(double) * n_load) : 0;
+    if (fast) {
+        // positions -> pinned -> device (SM copy), windows straight into d_win_lo / d_win_hi; the pinned buffer is
+        // sized once for everything this plan stages, because growing it would free memory the copy kernel reads
+        s->pstage->reserve(b_pos + pad16(sizeof(Tile) * static_cast<size_t>(tiles_bound)) + pad16(sizeof(int32_t) * (2 * static_cast<size_t>(n_ib) + 4)));
+        double* d_pos = amalloc<double>(s->arena, static_cast<size_t>(n_load) + 2);
+        s->d_total_pairs = amalloc<unsigned long long>(s->arena, 1);
+        CUDA_CHECK(cudaMemsetAsync(s->d_total_pairs, 0, sizeof(unsigned long long), st));
+        memcpy(s->pstage->base, whole_pos, sizeof(double) * n_load);
+        launch_copy16(s->pstage->base, d_pos, b_pos, st);
+        launch_windows(d_pos, n_load, wind, s->d_win_lo, s->d_win_hi, st, n_load_pad, s->d_total_pairs);
+    }
     tr.lap("fixed buffers");
 
     // ---- plane ring: as many SNP rows as needed, within the memory budget (4 int8 planes each)
@@ -740,6 +783,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     const double n_own_rows = std::max(1, s->own_end - s->own_begin);
     const double compute_ns_row = (static_cast<double>(s->total_pairs) / n_own_rows + 3.0 * kBlk) * s->npad * 12.0 / 2.6e6;
     const double upload_ns_row = static_cast<double>(s->bps) / 54.0;
+    const int32_t taper_min = static_cast<int32_t>(std::max<size_t>(kBlk, env_size("NLDSC_TAPER_MIN", 4096) / kBlk * kBlk));
     const bool taper = ramp && !fixed_rows && (tp ? tp[0] != '0' : compute_ns_row < 0.7 * upload_ns_row);
     const int32_t wave = std::max(1, s->sm_count / 2);       // supertiles scored concurrently (one per CTA pair)
     std::vector<Tile>& tiles = s->h_tiles;
@@ -758,7 +802,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         int32_t target = std::min(ramp_rows, chunk_rows);
         // with a concurrent upload the last chunk cannot start before the last byte has landed: taper the
         // chunk size towards the end of the shard so that tail is short
-        if (taper) target = std::min(target, std::max(4096, (n_ib - b) * kBlk / 2 / 4096 * 4096));
+        if (taper) target = std::min(target, std::max(taper_min, (n_ib - b) * kBlk / 2 / taper_min * taper_min));
         int32_t e = b;
         while (e < n_ib) {
             const int32_t col1 = (jb_hi[e] + 1) * kBlk;
@@ -838,17 +882,19 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     {
         // plan arrays -> pinned staging -> device by an SM copy: the H2D copy engine is busy with (or about to
         // be queued full of) the shard's packed rows, and these few MB must not wait behind them
-        auto pad16 = [](size_t b) { return (b + 15) & ~size_t(15); };
-        const size_t b_win = pad16(sizeof(int32_t) * n_load_pad), b_tiles = pad16(sizeof(Tile) * tiles.size()),
+        const size_t b_win = fast ? 0 : pad16(sizeof(int32_t) * n_load_pad), b_tiles = pad16(sizeof(Tile) * tiles.size()),
                      b_tb = pad16(sizeof(int32_t) * tile_begin.size());
-        s->pstage->reserve(2 * b_win + b_tiles + b_tb);
-        char* h = s->pstage->base;
-        memcpy(h, wlo.data(), sizeof(int32_t) * n_load_pad);
-        memcpy(h + b_win, whi.data(), sizeof(int32_t) * n_load_pad);
+        if (!fast) s->pstage->reserve(2 * b_win + b_tiles + b_tb);
+        else if (b_pos + b_tiles + b_tb > s->pstage->bytes) throw CudaError("plan staging bound exceeded");
+        char* h = s->pstage->base + b_pos;
+        if (!fast) {
+            memcpy(h, wlo.data(), sizeof(int32_t) * n_load_pad);
+            memcpy(h + b_win, whi.data(), sizeof(int32_t) * n_load_pad);
+            launch_copy16(h, s->d_win_lo, b_win, st);
+            launch_copy16(h + b_win, s->d_win_hi, b_win, st);
+        }
         memcpy(h + 2 * b_win, tiles.data(), sizeof(Tile) * tiles.size());
         memcpy(h + 2 * b_win + b_tiles, tile_begin.data(), sizeof(int32_t) * tile_begin.size());
-        launch_copy16(h, s->d_win_lo, b_win, st);
-        launch_copy16(h + b_win, s->d_win_hi, b_win, st);
         launch_copy16(h + 2 * b_win, s->d_tiles, b_tiles, st);
         launch_copy16(h + 2 * b_win + b_tiles, s->d_tile_begin, b_tb, st);
     }
@@ -1165,8 +1211,8 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
             t1 = now();
             start_upload(s);
             t2 = now();
-            if (whole) compute_windows_device(j.device, s->pstage, s->own_stream, p->positions, p->n_snp, p->ld_wind, lo, hi);
-            session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true);
+            if (whole) session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true, p->positions, p->ld_wind);
+            else session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true);
             t3 = now();
             session_run(s, nullptr);
             t4 = now();
@@ -1380,6 +1426,13 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* o) {
     if (!s || !o) return NLDSC_ERR_INVALID;
     memset(o, 0, sizeof(*o));
     o->pairs = s->total_pairs;
+    if (s->d_total_pairs && s->ran) {             // whole-file plan: the exact count was summed on the device
+        unsigned long long v = 0;
+        cudaSetDevice(s->device);
+        if (cudaEventSynchronize(s->ev_run1) == cudaSuccess &&
+            cudaMemcpy(&v, s->d_total_pairs, sizeof(v), cudaMemcpyDeviceToHost) == cudaSuccess)
+            o->pairs = static_cast<int64_t>(v);
+    }
     o->tiles = s->total_tiles;
     o->chunks = static_cast<int32_t>(s->chunks.size());
     o->kernel_launches = s->launches;

@@ -109,6 +109,7 @@ struct nldsc_ld_session {
     double* d_rstd = nullptr;
     int32_t* d_win_lo = nullptr;
     int32_t* d_win_hi = nullptr;
+    unsigned long long* d_total_pairs = nullptr;   // whole-file plan only: sum of window widths, summed by windows_kernel
     int8_t* d_planes = nullptr;
     nldsc::Tile* d_tiles = nullptr;
     int32_t* d_tile_begin = nullptr;

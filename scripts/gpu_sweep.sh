@@ -10,9 +10,9 @@ print('ms/step %.3f e2e %.3f ms frac %.3f band %.3f dev %.3f chunks %d' % (d['ms
 done <<'EOL'
 NLDSC_TAPER=0
 NLDSC_TAPER=1
-NLDSC_CHUNK_ROWS=8192
-NLDSC_CHUNK_ROWS=12288
-NLDSC_FIRST_BYTES=20e6
-NLDSC_FIRST_BYTES=20e6 NLDSC_TAPER=1
+NLDSC_TAPER=1 NLDSC_TAPER_MIN=2048
+NLDSC_TAPER=1 NLDSC_TAPER_MIN=1024
+NLDSC_TAPER=0
+NLDSC_TAPER=1 NLDSC_TAPER_MIN=2048
 EOL
 NLDSC_TRACE=1 python scripts/e2e_trace.py 2>&1 | grep -E "device:|gpu 0|call" | tail -6
