@@ -46,41 +46,52 @@ __device__ __forceinline__ RowCtx load_row_ctx(const BandArgs& a, int32_t gi) {
     return r;
 }
 
+// Exact int32 -> double without the conversion unit (I2F.F64 runs on the quarter-rate XU pipe): build the
+// double 2^52 + 2^31 + x from its bit pattern and subtract the bias.  Exact for every int32.
+__device__ __forceinline__ double i2d(int32_t x) {
+    return __hiloint2double(0x43300000, x ^ static_cast<int32_t>(0x80000000u)) - 4503601774854144.0;
+}
+
 // One ordered pair (i, j): the six cross-counts are exact integers from the int8 GEMM.
+// Branch-free: every pair is evaluated and its terms are SELECTED in or out, so the compiler can interleave the
+// FP64 chains of the unrolled j loop (with early returns each pair cost ~1,000 cycles of exposed latency).
+// A rejected pair may compute inf / NaN (a dropped SNP has 1/sd = 0 or inf); selects never propagate them.
 __device__ __forceinline__ void pair_eval(const BandArgs& a, const RowCtx& r, int32_t gj,
                                           int32_t Ggm, int32_t Ggh, int32_t Gga,
                                           int32_t Gmm, int32_t Gmh, int32_t Gma, RowAcc& acc) {
-    if (gj < r.lo || gj > r.hi || gj == r.gi) return;        // stream.h:145-147, tools.h:41-49
-    const uint8_t fj = __ldg(a.flags + gj);
-    if (!(fj & kFlagKeep)) return;                            // cache_[i] is false for dropped SNPs
-    const double2* cp = reinterpret_cast<const double2*>(a.coef + gj);
+    // stream.h:145-147, tools.h:41-49: in the window, not the SNP itself; cache_[j] is false for dropped SNPs
+    const bool in_win = gj >= r.lo && gj <= r.hi && gj != r.gi;
+    const int32_t gjc = in_win ? gj : 0;                        // a valid index: the loads below are unconditional
+    const uint8_t fj = __ldg(a.flags + gjc);
+    const bool use = in_win && (fj & kFlagKeep);
+    const bool use_d = use && (fj & kFlagDom);
+    const double2* cp = reinterpret_cast<const double2*>(a.coef + gjc);
     const double2 c0 = __ldg(cp), c1 = __ldg(cp + 1), c2 = __ldg(cp + 2), c3 = __ldg(cp + 3);
     const double mu_j = c0.x, xbar_j = c0.y, inv_sd_j = c1.x, ch = c1.y;
     const double ca = c2.x, cm = c2.y, rbar_j = c3.x, inv_rsd_j = c3.y;
 
-    const double dGgm = Ggm, dGgh = Ggh, dGga = Gga, dGmm = Gmm, dGmh = Gmh, dGma = Gma;
-    const double dGgg = (double)(Ggh + 2 * Gga);
-    const double dGmg = (double)(Gmh + 2 * Gma);
+    const double dGgm = i2d(Ggm), dGgh = i2d(Ggh), dGga = i2d(Gga), dGmm = i2d(Gmm), dGmh = i2d(Gmh), dGma = i2d(Gma);
+    const double dGgg = i2d(Ggh + 2 * Gga);
+    const double dGmg = i2d(Gmh + 2 * Gma);
 
     // additive: ldscalc.h:38
     const double sa = (dGgg + mu_j * dGgm) + r.mu * (dGmg + mu_j * dGmm) - r.nxbar * xbar_j;
     const double ra = sa * r.w * inv_sd_j;
     const double r2a = ra * ra;
-    acc.add += 1.0 - (1.0 - r2a) * a.adj_c;                   // tools.h:91
-    acc.wsa += 1;
+    const double adj_a = 1.0 - (1.0 - r2a) * a.adj_c;           // tools.h:91
+    acc.add += use ? adj_a : 0.0;
+    acc.wsa += use ? 1 : 0;
 
     // dominance: ldscalc.h:40-46
-    if (fj & kFlagDom) {
-        const double u0 = ch * dGgh + ca * dGga + cm * dGgm;
-        const double u1 = ch * dGmh + ca * dGma + cm * dGmm;
-        const double sd = (u0 + r.mu * u1) - r.nxbar * rbar_j;
-        const double rd = sd * r.w * inv_rsd_j;
-        const double r2d = rd * rd;
-        const double adj = 1.0 - (1.0 - r2d) * a.adj_c;
-        acc.dom += adj;
-        acc.wsd += 1;
-        acc.wsde += (adj > a.rsq_thr) ? 1 : 0;                // tools.h:36-38 (strict)
-    }
+    const double u0 = ch * dGgh + ca * dGga + cm * dGgm;
+    const double u1 = ch * dGmh + ca * dGma + cm * dGmm;
+    const double sd = (u0 + r.mu * u1) - r.nxbar * rbar_j;
+    const double rd = sd * r.w * inv_rsd_j;
+    const double r2d = rd * rd;
+    const double adj = 1.0 - (1.0 - r2d) * a.adj_c;
+    acc.dom += use_d ? adj : 0.0;
+    acc.wsd += use_d ? 1 : 0;
+    acc.wsde += (use_d && adj > a.rsq_thr) ? 1 : 0;             // tools.h:36-38 (strict)
 }
 
 }  // namespace nldsc

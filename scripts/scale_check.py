@@ -9,6 +9,8 @@ from nldsc_b200 import capi, synth
 from oracle import ld_oracle
 
 CASES = {
+    # BASELINE.json configs[0]: the reference's own CPU-runnable case
+    "cfg1":       dict(n_org=1000, n_snp=10000, missing=0.0, density=340.0, wind=1.0, oracle_rows=3),
     "ukb_slice":  dict(n_org=315599, n_snp=40000, missing=0.02, density=340.0, wind=1.0, oracle_rows=2),
     "ukb_ring":   dict(n_org=315599, n_snp=40000, missing=0.02, density=340.0, wind=1.0, oracle_rows=0,
                        env={"NLDSC_PLANE_BYTES": "12e9"}),
@@ -19,7 +21,7 @@ CASES = {
 }
 out = {}
 kept_results = {}
-for name in (sys.argv[1:] or [k for k in CASES if k not in ("cfg5_full", "cfg5_slice")]):
+for name in (sys.argv[1:] or [k for k in CASES if k not in ("cfg5_full", "cfg5_slice", "cfg1")]):
     c = CASES[name]
     for k, v in c.get("env", {}).items():
         os.environ[k] = v
