@@ -339,5 +339,22 @@ def main():
         dist.destroy_process_group()
 
 
+def _only_json_on_stdout():
+    """Libraries (NCCL prints its version banner on stdout) must not add lines to the one-JSON-line contract:
+    everything written to fd 1 goes to stderr; the returned file is the real stdout, for the JSON line alone."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
+    _real_stdout = _only_json_on_stdout()
+    _print = print
+
+    def print(*a, **k):          # noqa: A001 -- the JSON line (the only print in this file) goes to the real stdout
+        k.setdefault("file", _real_stdout)
+        _print(*a, **k)
+        _real_stdout.flush()
+
     main()
