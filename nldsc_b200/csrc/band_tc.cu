@@ -308,6 +308,183 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     }
 }
 
+// ---- wide supertiles: two j-blocks per A tile ---------------------------------------------------
+// Same roles and pipeline as band_tc_kernel, but a supertile may carry a SECOND j-block (Tile::b_row2): the A
+// tiles of a K-step are then multiplied with both B tiles, D0[256 x 192] in TMEM columns 0..191 and D1 in 192..383.
+// Operand bytes from L2 drop from 56 KB to 40 KB per 64 columns of a CTA pair, which lifts the L2 -> SM bound the
+// narrow kernel runs into.  Both accumulators belong to one supertile, so the epilogue is NOT hidden behind the
+// next supertile's MMAs (12 us against 2 x 2.4 us x N / 10,000 of MMA time): used for N >= 65,536 only.
+// Partials of the two j-blocks go to slots `slot` and `slot + 1`, exactly where the narrow kernel puts them, so both
+// kernels give bitwise identical scores.
+namespace {
+constexpr int kWStages = 5;
+constexpr int kWStageBytes = kABytes + 2 * kBBytes;          // 40 KB per CTA per stage
+constexpr int kWSmemBytes = kWStages * kWStageBytes + 1024 + 256;
+}  // namespace
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    const BandArgs args) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWStages * kWStageBytes);   // leader CTA only
+    uint64_t* empty = full + kWStages;         // one per CTA
+    uint64_t* tfull = empty + kWStages;        // one per CTA
+    uint64_t* tempty = tfull + 1;              // leader CTA only
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
+        for (int s = 0; s < kWStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_init(tfull, 1);
+        mbar_init(tempty, 8);                  // 4 epilogue warps x 2 CTAs
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer: own A block, own half of one or two B blocks =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = pair; t < args.n_tiles; t += n_pairs) {
+                const Tile tl = args.tiles[t];
+                const int32_t a_row = tl.a_row[rank];
+                const int32_t b_row = tl.b_row + 32 * static_cast<int32_t>(rank);
+                const bool two = tl.b_row2 >= 0;
+                const int32_t b_row2 = tl.b_row2 + 32 * static_cast<int32_t>(rank);
+                const uint32_t bytes = 2u * (kABytes + (two ? 2 : 1) * kBBytes);          // both CTAs' bytes
+                for (int k = 0; k < args.k_steps; ++k) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    if (rank == 0) mbar_expect_tx(&full[stage], bytes);
+                    uint8_t* sa = smem + stage * kWStageBytes;
+                    uint8_t* sb = sa + kABytes;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        tma_load_3d(sa + u * 4096, &map_a, &full[stage], k * kKStep, a_row + 16 * u, kPlaneG);
+                    tma_load_3d(sb, &map_b, &full[stage], k * kKStep, b_row, kPlaneM);
+                    if (two) tma_load_3d(sb + kBBytes, &map_b, &full[stage], k * kKStep, b_row2, kPlaneM);
+                    if (++stage == kWStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (rank == 0 && lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int n = 0;
+            for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
+                const bool two = args.tiles[t].b_row2 >= 0;
+                mbar_wait(tempty, (n & 1) ^ 1);                    // both CTAs' epilogues drained the accumulators
+                tc_fence_after();
+                for (int k = 0; k < args.k_steps; ++k) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * kWStageBytes);
+                    const uint64_t a_desc = make_smem_desc(sa);
+                    const uint64_t b_desc = make_smem_desc(sa + kABytes);
+                    const uint64_t b2_desc = make_smem_desc(sa + kABytes + kBBytes);
+#pragma unroll
+                    for (int kk = 0; kk < kKStep / 32; ++kk)
+                        tc_mma_i8(tmem_base, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (k | kk) != 0);
+                    if (two) {
+#pragma unroll
+                        for (int kk = 0; kk < kKStep / 32; ++kk)
+                            tc_mma_i8(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, kIdesc, (k | kk) != 0);
+                    }
+                    tc_commit_pair(&empty[stage]);
+                    if (++stage == kWStages) { stage = 0; phase ^= 1; }
+                }
+                tc_commit_pair(tfull);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue: as in band_tc_kernel, once per j-block of the supertile =====
+        const int q = warp & 3;
+        const bool is_g = lane < 16;
+        const int s = 16 * q + (lane & 15);
+        int n = 0;
+        for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
+            const Tile tl = args.tiles[t];
+            const int32_t i0 = tl.i0[rank];
+            const RowCtx row = load_row_ctx(args, i0 + s);
+            const int n_j = tl.b_row2 >= 0 ? 2 : 1;
+            mbar_wait(tfull, n & 1);
+            tc_fence_after();
+#pragma unroll 1
+            for (int jj = 0; jj < n_j; ++jj) {
+                RowAcc acc;
+                const uint32_t taddr = tmem_base + jj * kBRows + (static_cast<uint32_t>(32 * q) << 16);
+                const int32_t j0 = tl.j0 + kBlk * jj;
+#pragma unroll 1
+                for (int c = 0; c < 4; ++c) {
+                    const uint32_t col = 96 * (c >> 1) + 16 * (c & 1);
+                    int32_t vm[16], vh[16], va[16];
+                    tmem_ld16(taddr + col, vm);
+                    tmem_ld16(taddr + col + 32, vh);
+                    tmem_ld16(taddr + col + 64, va);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
+                        const int32_t sh_ = is_g ? vh[2 * u + 1] : vh[2 * u];
+                        const int32_t sa_ = is_g ? va[2 * u + 1] : va[2 * u];
+                        const int32_t rm = __shfl_xor_sync(0xFFFFFFFFu, sm_, 16);
+                        const int32_t rh = __shfl_xor_sync(0xFFFFFFFFu, sh_, 16);
+                        const int32_t ra = __shfl_xor_sync(0xFFFFFFFFu, sa_, 16);
+                        const int jl = 16 * c + 2 * u + (is_g ? 0 : 1);
+                        const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
+                        const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
+                        const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
+                        pair_eval(args, row, j0 + jl, Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
+                    }
+                }
+                acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
+                acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);
+                acc.wsa += __shfl_xor_sync(0xFFFFFFFFu, acc.wsa, 16);
+                acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
+                acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
+                if (is_g) {
+                    const int64_t o = (static_cast<int64_t>(tl.slot + jj) * 2 + rank) * kBlk + s;
+                    args.part.add[o] = acc.add;
+                    args.part.dom[o] = acc.dom;
+                    args.part.wsa[o] = acc.wsa;
+                    args.part.wsd[o] = acc.wsd;
+                    args.part.wsde[o] = acc.wsde;
+                }
+            }
+            // both accumulators read: hand them back to the leader's MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_leader(tempty);
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                     : "memory");
+    }
+}
 // ---- host side: TMA descriptors + launch ------------------------------------------------
 struct BandMaps {
     CUtensorMap a;   // box {128 B, 16 rows, 2 planes}
@@ -368,6 +545,14 @@ void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cu
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     const int pairs = args.n_tiles < sm_count / 2 ? args.n_tiles : sm_count / 2;     // one CTA pair per TPC
     band_tc_kernel<<<2 * pairs, kThreads, kSmemBytes, st>>>(maps->a, maps->b, args);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
+    if (args.n_tiles <= 0) return;
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
+    const int pairs = args.n_tiles < sm_count / 2 ? args.n_tiles : sm_count / 2;
+    band_tc_wide_kernel<<<2 * pairs, kThreads, kWSmemBytes, st>>>(maps->a, maps->b, args);
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -44,7 +44,8 @@ struct Tile {
     int32_t slot;      // where its partial row sums go: position in i-pair-major order (what finalize walks), which is
                        // NOT the execution order -- tiles of 8 i-pairs are interleaved by j-block so that concurrent
                        // CTA pairs share B operands in L2 as well as A (wide windows would otherwise stream B from HBM)
-    int32_t pad_;
+    int32_t b_row2;    // wide supertiles (band_tc_wide_kernel, large N): ring row of a SECOND j-block j0 + 64 scored from
+                       // the same A tiles (its partials go to slot + 1), or -1.  Unused (0) by the narrow kernel.
 };
 
 // Per-row partial sums a supertile contributes (SoA, index = (tile * 2 + rank) * 64 + row).
@@ -107,6 +108,7 @@ struct BandMaps;   // opaque: 2 x CUtensorMap
 BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npad);
 void band_maps_destroy(BandMaps*);
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);
+void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);   // tiles carry b_row2
 void launch_band_simt(const int8_t* planes, int64_t plane_stride, int32_t npad,
                       const BandArgs& args, cudaStream_t st);
 

@@ -502,6 +502,9 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     s->npad = static_cast<int32_t>(((static_cast<int64_t>(p->n_org) + kKAlign - 1) / kKAlign) * kKAlign);
     const char* band = getenv("NLDSC_BAND");
     s->use_simt = band && strcmp(band, "simt") == 0;
+    // two j-blocks per supertile pay once the MMA time of a supertile dwarfs the (then exposed) epilogue
+    const char* wd = getenv("NLDSC_WIDE");
+    s->wide = !s->use_simt && (wd ? wd[0] == '1' : s->npad / kKAlign >= 512);
     s->load_begin = load_begin;
     s->load_end = load_end;
     s->n_load = load_end - load_begin;
@@ -840,43 +843,48 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         // ~8 i-pairs x ~9 j-blocks, so every A slice is shared by ~9 CTA pairs and every B slice by ~8.
         const int32_t kRaster = static_cast<int32_t>(std::max<size_t>(1, std::min<size_t>(64, env_size("NLDSC_RASTER", 8))));
         std::vector<int32_t> slot0;                       // first slot of every i-pair of the chunk
-        {
-            int32_t nslots = 0;
-            for (int32_t k = b; k < e; k += 2) {
-                tile_begin.push_back(nslots);
-                slot0.push_back(nslots);
-                nslots += pair_tiles(k, e);
-            }
+        int32_t nslots_chunk = 0;
+        for (int32_t k = b; k < e; k += 2) {
+            tile_begin.push_back(nslots_chunk);
+            slot0.push_back(nslots_chunk);
+            nslots_chunk += pair_tiles(k, e);
         }
         for (int32_t g0 = b; g0 < e; g0 += 2 * kRaster) {
             const int32_t g1 = std::min(e, g0 + 2 * kRaster);
             const int32_t last = g1 - 1 - ((g1 - 1 - g0) % 2);                    // first block of the group's last i-pair
             const int32_t jb_first = jb_lo[g0], jb_last = (last + 1 < e ? jb_hi[last + 1] : jb_hi[last]);
-            for (int32_t jb = jb_first; jb <= jb_last; ++jb) {
+            // wide supertiles (large N) carry two adjacent j-blocks, paired on even block indices; a block left alone
+            // at either end of an i-pair's range is a supertile of its own, so nothing outside the band is scored
+            const int32_t step = s->wide ? 2 : 1;
+            for (int32_t jb = s->wide ? (jb_first & ~1) : jb_first; jb <= jb_last; jb += step) {
                 for (int32_t k = g0; k < g1; k += 2) {
                     const bool two = k + 1 < e;
-                    if (jb < jb_lo[k] || jb > (two ? jb_hi[k + 1] : jb_hi[k])) continue;
+                    const int32_t lo_k = jb_lo[k], hi_k = two ? jb_hi[k + 1] : jb_hi[k];
+                    const int32_t ja = std::max(jb, lo_k), jz = std::min(jb + step - 1, hi_k);
+                    if (ja > jz) continue;
                     Tile t;
                     t.i0[0] = (ib0 + k) * kBlk;
                     t.i0[1] = two ? (ib0 + k + 1) * kBlk : kDeadBlock;
                     t.a_row[0] = static_cast<int32_t>(t.i0[0] % cap);
                     t.a_row[1] = two ? static_cast<int32_t>(t.i0[1] % cap) : t.a_row[0];
-                    t.j0 = jb * kBlk;
+                    t.j0 = ja * kBlk;
                     t.b_row = static_cast<int32_t>(t.j0 % cap);
-                    t.slot = slot0[(k - b) / 2] + (jb - jb_lo[k]);
-                    t.pad_ = 0;
+                    t.slot = slot0[(k - b) / 2] + (ja - lo_k);
+                    t.b_row2 = jz > ja ? static_cast<int32_t>((static_cast<int64_t>(ja + 1) * kBlk) % cap) : -1;
                     tiles.push_back(t);
                 }
             }
         }
-        tile_begin.push_back(static_cast<int32_t>(tiles.size() - c.tile0));
+        s->max_chunk_slots = std::max(s->max_chunk_slots, nslots_chunk);
+        tile_begin.push_back(nslots_chunk);
         c.n_tiles = static_cast<int32_t>(tiles.size() - c.tile0);
         s->max_chunk_tiles = std::max(s->max_chunk_tiles, c.n_tiles);
         s->chunks.push_back(c);
         b = e;
     }
     tr.lap("tile plan");
-    s->total_tiles = static_cast<int64_t>(tiles.size());
+    s->total_tiles = 0;                            // in 64-wide supertiles (= partial slots), whichever kernel scores them
+    for (size_t k = 0; k + 1 < tile_begin.size(); ++k) s->total_tiles += std::max(0, tile_begin[k + 1] - tile_begin[k]);
     s->d_tiles = amalloc<Tile>(s->arena, tiles.size());
     s->d_tile_begin = amalloc<int32_t>(s->arena, tile_begin.size());
     {
@@ -898,7 +906,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         launch_copy16(h + 2 * b_win, s->d_tiles, b_tiles, st);
         launch_copy16(h + 2 * b_win + b_tiles, s->d_tile_begin, b_tb, st);
     }
-    const size_t np = static_cast<size_t>(s->max_chunk_tiles) * 2 * kBlk;
+    const size_t np = static_cast<size_t>(s->max_chunk_slots) * 2 * kBlk;
     s->part.add = amalloc<double>(s->arena, np);
     s->part.dom = amalloc<double>(s->arena, np);
     s->part.wsa = amalloc<int32_t>(s->arena, np);
@@ -1034,7 +1042,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             if (s->use_simt)
                 launch_band_simt(s->d_planes, s->plane_rows * static_cast<int64_t>(s->npad), s->npad, a, bs);
             else
-                launch_band_tc(s->maps, a, s->sm_count, bs);
+                (s->wide ? launch_band_tc_wide : launch_band_tc)(s->maps, a, s->sm_count, bs);
             ++s->launches;
         }
         if (overlap) CUDA_CHECK(cudaEventRecord(s->ev_band[ci], bs));

@@ -90,6 +90,7 @@ struct nldsc_ld_session {
     int32_t npad = 0;
     double maf_thr = 0, std_thr = 0, rsq_thr = 0;
     bool use_simt = false;
+    bool wide = false;                        // band_tc_wide_kernel: two j-blocks per supertile (N >= 65,536, or NLDSC_WIDE=1)
     bool upload_started = false;
     bool planned = false;
 
@@ -97,6 +98,7 @@ struct nldsc_ld_session {
     int64_t total_tiles = 0;
     int64_t total_pairs = 0;                  // sum over owned rows of (window size - 1) before the MAF filter
     int32_t max_chunk_tiles = 0;
+    int32_t max_chunk_slots = 0;              // partial-sum slots (= supertiles of the narrow kernel) of the largest chunk
     int64_t plane_rows = 0;                   // ring capacity in SNP rows (multiple of 64)
 
     // device (all carved from `arena`)

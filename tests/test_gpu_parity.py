@@ -304,3 +304,21 @@ def test_multi_piece_bed_read_equals_host_buffer(tmp_path, monkeypatch):
         for key in RESULT_KEYS:
             assert np.array_equal(got[key], mem[key], equal_nan=True), key
     assert (mem["l2_ws"] >= 0).sum() > 8000
+
+
+def test_wide_supertiles_equal_narrow_bitwise(monkeypatch):
+    """band_tc_wide_kernel (two j-blocks per A tile, chosen for N >= 65,536) puts its partial sums into the same
+    slots as the narrow kernel: forced on at a small N it must reproduce the default run bit for bit, also with
+    chunks and a wrapping ring, and its raw cross-counts must pass the oracle bar."""
+    g = _case(1003, 3000, 0.02, seed=21, wind=0.7)
+    base = _run(g)
+    assert_ld_close(base, _oracle(g), label="narrow")
+    monkeypatch.setenv("NLDSC_WIDE", "1")
+    wide = _run(g)
+    for k in RESULT_KEYS:
+        assert np.array_equal(base[k], wide[k], equal_nan=True), k
+    monkeypatch.setenv("NLDSC_CHUNK_ROWS", "256")
+    monkeypatch.setenv("NLDSC_PLANE_BYTES", str(1024 * 4 * 1024))
+    small = _run(g)
+    for k in RESULT_KEYS:
+        assert np.array_equal(base[k], small[k], equal_nan=True), k
