@@ -746,6 +746,13 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         budget = static_cast<size_t>(0.85 * static_cast<double>(free_b + reusable));
         budget = std::min(budget, env_size("NLDSC_PLANE_BYTES", budget));
     }
+    // Measured: past ~30 GB of planes the band kernel slows down (N = 315,599: 37 -> 50 ms per 40,000 SNPs; the
+    // 120 GB of full-size configs[4]: 2.87 -> 2.70 s), so the ring is kept to 24 GB unless one block pair's
+    // columns need more (3 x that, so that unpack can run a chunk ahead) or NLDSC_PLANE_BYTES says otherwise.
+    if (!getenv("NLDSC_PLANE_BYTES")) {
+        const size_t soft = std::max<size_t>(size_t(24) << 30, 3 * static_cast<size_t>(max_span) * row_bytes);
+        budget = std::min(budget, soft);
+    }
     int64_t cap = static_cast<int64_t>(budget / row_bytes) / kBlk * kBlk;
     cap = std::min<int64_t>(cap, n_load_pad);
     if (cap < max_span) {
@@ -990,6 +997,11 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             // the event of piece k says nothing about piece k - 1
             for (; next_piece <= piece; ++next_piece) CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_piece[next_piece], 0));
         }
+        // Wide supertiles run the tensor pipe close to its limit and lose more to a concurrent unpack (L2 / HBM
+        // traffic, issue slots) than the overlap saves (N = 315,599: 51 ms overlapped, 45 ms in turn): the unpack of
+        // chunk c then waits for the band kernel of chunk c-1, i.e. the two kernels take turns.
+        if (overlap && s->wide && ci >= 1 && !(getenv("NLDSC_WIDE_OVERLAP")))
+            CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_band[ci - 1], 0));
         if (overlap && c.new_row1 > c.new_row0) {
             // ring hazard: rows [new_row0, new_row1) land in the slots of rows `plane_rows` earlier; the
             // latest earlier chunk that still reads any of those must have finished its band kernel
