@@ -269,7 +269,7 @@ def main():
             traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
-    roofline = {"bound": "tensor", "kernel": "band_tc_kernel", "achieved": achieved, "peak": peak, "unit": "TOP/s",
+    roofline = {"bound": "tensor", "kernel": {0: "band_simt_kernel", 1: "band_tc_kernel", 2: "band_tc_wide_kernel"}[st["band_impl"]], "achieved": achieved, "peak": peak, "unit": "TOP/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_note,
                 "ms_band": st["ms_band"], "ms_unpack": st["ms_unpack"], "ms_count": st["ms_count"],
                 "ms_stats": st["ms_stats"], "ms_finalize": st["ms_finalize"], "ms_step_device": dev_ms,

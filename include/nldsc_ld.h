@@ -94,7 +94,7 @@ typedef struct nldsc_ld_stats {
     int32_t load_begin;       /* first SNP row the shard needs (owned range minus halo, 64-aligned) */
     int32_t load_end;         /* one past the last SNP row needed */
     int32_t npad;             /* padded organisms per plane row (bytes) */
-    int32_t band_impl;        /* 1 = tcgen05 kernel, 0 = SIMT yardstick (NLDSC_BAND=simt) */
+    int32_t band_impl;        /* 1 = tcgen05 kernel, 2 = its wide variant (N >= 8,192), 0 = SIMT yardstick (NLDSC_BAND=simt) */
     float ms_count;           /* CUDA-event times of the last run(), per kernel family; counting is fused
                                  into the unpack kernel, so this one stays 0 */
     float ms_stats;

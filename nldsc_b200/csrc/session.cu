@@ -502,9 +502,11 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     s->npad = static_cast<int32_t>(((static_cast<int64_t>(p->n_org) + kKAlign - 1) / kKAlign) * kKAlign);
     const char* band = getenv("NLDSC_BAND");
     s->use_simt = band && strcmp(band, "simt") == 0;
-    // two j-blocks per supertile pay once the MMA time of a supertile dwarfs the (then exposed) epilogue
+    // two j-blocks per supertile pay once the MMA time of a supertile outweighs the (then exposed) epilogue
     const char* wd = getenv("NLDSC_WIDE");
-    s->wide = !s->use_simt && (wd ? wd[0] == '1' : s->npad / kKAlign >= 512);
+    // Measured crossover: a wide supertile costs 0.50 us per K-step + 12 us of exposed epilogue, two narrow ones
+    // 2 x max(0.35 us per K-step, 6 us): wide wins from ~57 K-steps (N ~ 7,200) on.
+    s->wide = !s->use_simt && (wd ? wd[0] == '1' : s->npad / kKAlign >= 64);
     s->load_begin = load_begin;
     s->load_end = load_end;
     s->n_load = load_end - load_begin;
@@ -967,6 +969,11 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     cudaStream_t us = overlap ? s->unpack_stream : st;
     // band launches alternate between two streams: every launch is a full persistent grid, so the CTA pairs of
     // chunk c+1 start on the SMs that chunk c's partial last wave leaves idle instead of after its slowest pair
+    // With long rows (N >= 65,536) the wide band kernel loses more to a concurrent unpack than the overlap saves
+    // (N = 315,599: 46.7 ms side by side, 45.6 ms in turn; 10 cM band at N = 100,000: 65.9 vs 60.2 ms; at
+    // N = 10,000 it is the other way round: 4.09 vs 4.62 ms), so there the two kernels take turns.
+    const char* wo = getenv("NLDSC_WIDE_OVERLAP");
+    const bool turns = overlap && s->wide && (wo ? wo[0] == '0' : s->npad / kKAlign >= 512);
     const char* bsn = getenv("NLDSC_BAND_STREAMS");
     const bool two_band = overlap && !(bsn && bsn[0] == '1') && s->chunks.size() > 1;
     if (overlap) {
@@ -997,11 +1004,8 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             // the event of piece k says nothing about piece k - 1
             for (; next_piece <= piece; ++next_piece) CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_piece[next_piece], 0));
         }
-        // Wide supertiles run the tensor pipe close to its limit and lose more to a concurrent unpack (L2 / HBM
-        // traffic, issue slots) than the overlap saves (N = 315,599: 51 ms overlapped, 45 ms in turn): the unpack of
-        // chunk c then waits for the band kernel of chunk c-1, i.e. the two kernels take turns.
-        if (overlap && s->wide && ci >= 1 && !(getenv("NLDSC_WIDE_OVERLAP")))
-            CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_band[ci - 1], 0));
+        // long rows: the unpack of chunk c waits for the band kernel of chunk c-1, i.e. the two kernels take turns
+        if (turns && ci >= 1) CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_band[ci - 1], 0));
         if (overlap && c.new_row1 > c.new_row0) {
             // ring hazard: rows [new_row0, new_row1) land in the slots of rows `plane_rows` earlier; the
             // latest earlier chunk that still reads any of those must have finished its band kernel
@@ -1459,7 +1463,7 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* o) {
     o->load_begin = s->load_begin;
     o->load_end = s->load_end;
     o->npad = s->npad;
-    o->band_impl = s->use_simt ? 0 : 1;
+    o->band_impl = s->use_simt ? 0 : (s->wide ? 2 : 1);
     if (s->ran) {
         cudaSetDevice(s->device);
         if (cudaEventSynchronize(s->ev_run1) != cudaSuccess) return NLDSC_ERR_RUNTIME;
