@@ -84,17 +84,14 @@ band_simt_kernel(const int8_t* __restrict__ planes, int64_t plane_stride, int32_
 #pragma unroll
     for (int c = 0; c < 16; ++c)
         pair_eval(args, row, tl.j0 + cg * 16 + c, acc[0][c], acc[1][c], acc[2][c], acc[3][c], acc[4][c], acc[5][c], ra);
-    // the 4 threads of a row are adjacent lanes
-#pragma unroll
-    for (int o = 1; o < 4; o <<= 1) {
-        ra.add += __shfl_xor_sync(0xFFFFFFFFu, ra.add, o);
-        ra.dom += __shfl_xor_sync(0xFFFFFFFFu, ra.dom, o);
-        ra.wsa += __shfl_xor_sync(0xFFFFFFFFu, ra.wsa, o);
-        ra.wsd += __shfl_xor_sync(0xFFFFFFFFu, ra.wsd, o);
-        ra.wsde += __shfl_xor_sync(0xFFFFFFFFu, ra.wsde, o);
-    }
-    if (cg == 0) {
-        const int64_t o = ((int64_t)tl.slot * 2 + rank) * kBlk + s;
+    // the 4 threads of a row are adjacent lanes: cg 0,1 score j 0..31 (half 0), cg 2,3 score j 32..63 (half 1)
+    ra.add += __shfl_xor_sync(0xFFFFFFFFu, ra.add, 1);
+    ra.dom += __shfl_xor_sync(0xFFFFFFFFu, ra.dom, 1);
+    ra.wsa += __shfl_xor_sync(0xFFFFFFFFu, ra.wsa, 1);
+    ra.wsd += __shfl_xor_sync(0xFFFFFFFFu, ra.wsd, 1);
+    ra.wsde += __shfl_xor_sync(0xFFFFFFFFu, ra.wsde, 1);
+    if ((cg & 1) == 0) {
+        const int64_t o = part_index(tl.slot, rank, cg >> 1, s);
         args.part.add[o] = ra.add;
         args.part.dom[o] = ra.dom;
         args.part.wsa[o] = ra.wsa;
@@ -131,12 +128,15 @@ finalize_kernel(const FinalizeArgs a) {
     int wsa = 0, wsd = 0, wsde = 0;
     // i-block b of the chunk is rank b % 2 of supertile row b / 2
     for (int t = a.tile_begin[b >> 1]; t < a.tile_begin[(b >> 1) + 1]; ++t) {
-        const int64_t p = ((int64_t)t * 2 + (b & 1)) * kBlk + r;
-        add += a.part.add[p];
-        dom += a.part.dom[p];
-        wsa += a.part.wsa[p];
-        wsd += a.part.wsd[p];
-        wsde += a.part.wsde[p];
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const int64_t p = part_index(t, b & 1, half, r);
+            add += a.part.add[p];
+            dom += a.part.dom[p];
+            wsa += a.part.wsa[p];
+            wsd += a.part.wsd[p];
+            wsde += a.part.wsde[p];
+        }
     }
     a.l2[o] = add; a.l2d[o] = dom;
     a.wsa[o] = wsa; a.wsd[o] = wsd; a.wsde[o] = wsde;

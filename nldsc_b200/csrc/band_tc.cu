@@ -239,61 +239,67 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const Tile tl = args.tiles[t];
             const int32_t i0 = tl.i0[rank];
             const RowCtx row = load_row_ctx(args, i0 + s);
-            RowAcc acc;
             mbar_wait(&tfull[buf], (n >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(32 * q) << 16);
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {            // 16 j-SNPs per pass
-                // columns: [m h a] of j-SNPs 0-31 (staged by CTA 0), then [m h a] of j-SNPs 32-63 (CTA 1)
-                const uint32_t col = 96 * (c >> 1) + 16 * (c & 1);
-                int32_t vm[16], vh[16], va[16];
-                tmem_ld16(taddr + col, vm);
-                tmem_ld16(taddr + col + 32, vh);
-                tmem_ld16(taddr + col + 64, va);
-                tmem_ld_wait();
-                if (args.dump != nullptr) {
-                    int32_t* drow = args.dump + ((static_cast<int64_t>(tl.slot) * 2 + rank) * kARows + 32 * q + lane) * kBRows;
+            for (int half = 0; half < 2; ++half) {   // j-SNPs 0-31 (staged by CTA 0), then 32-63 (CTA 1): one partial each
+                RowAcc acc;
+#pragma unroll 1
+                for (int c2 = 0; c2 < 2; ++c2) {      // 16 j-SNPs per pass
+                    const int c = 2 * half + c2;
+                    // columns: [m h a] of j-SNPs 0-31, then [m h a] of j-SNPs 32-63
+                    const uint32_t col = 96 * half + 16 * c2;
+                    int32_t vm[16], vh[16], va[16];
+                    tmem_ld16(taddr + col, vm);
+                    tmem_ld16(taddr + col + 32, vh);
+                    tmem_ld16(taddr + col + 64, va);
+                    tmem_ld_wait();
+                    if (args.dump != nullptr) {
+                        int32_t* drow = args.dump + ((static_cast<int64_t>(tl.slot) * 2 + rank) * kARows + 32 * q + lane) * kBRows;
 #pragma unroll
-                    for (int e = 0; e < 16; ++e) {
-                        drow[16 * c + e] = vm[e];
-                        drow[64 + 16 * c + e] = vh[e];
-                        drow[128 + 16 * c + e] = va[e];
+                        for (int e = 0; e < 16; ++e) {
+                            drow[16 * c + e] = vm[e];
+                            drow[64 + 16 * c + e] = vh[e];
+                            drow[128 + 16 * c + e] = va[e];
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        // g-lane scores even j, its partner m-lane scores odd j; swap what the other needs
+                        const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
+                        const int32_t sh_ = is_g ? vh[2 * u + 1] : vh[2 * u];
+                        const int32_t sa_ = is_g ? va[2 * u + 1] : va[2 * u];
+                        const int32_t rm = __shfl_xor_sync(0xFFFFFFFFu, sm_, 16);
+                        const int32_t rh = __shfl_xor_sync(0xFFFFFFFFu, sh_, 16);
+                        const int32_t ra = __shfl_xor_sync(0xFFFFFFFFu, sa_, 16);
+                        const int jl = 16 * c + 2 * u + (is_g ? 0 : 1);
+                        const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
+                        const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
+                        const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
+                        pair_eval(args, row, tl.j0 + jl, Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
                     }
                 }
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    // g-lane scores even j, its partner m-lane scores odd j; swap what the other needs
-                    const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
-                    const int32_t sh_ = is_g ? vh[2 * u + 1] : vh[2 * u];
-                    const int32_t sa_ = is_g ? va[2 * u + 1] : va[2 * u];
-                    const int32_t rm = __shfl_xor_sync(0xFFFFFFFFu, sm_, 16);
-                    const int32_t rh = __shfl_xor_sync(0xFFFFFFFFu, sh_, 16);
-                    const int32_t ra = __shfl_xor_sync(0xFFFFFFFFu, sa_, 16);
-                    const int jl = 16 * c + 2 * u + (is_g ? 0 : 1);
-                    const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
-                    const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
-                    const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
-                    pair_eval(args, row, tl.j0 + jl, Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
+                if (half == 1) {
+                    // accumulator fully read: hand it back to the leader's MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_leader(&tempty[buf]);
                 }
-            }
-            // accumulator fully read: hand it back to the leader's MMA warp
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_leader(&tempty[buf]);
-            // even-j and odd-j halves of the row
-            acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
-            acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);
-            acc.wsa += __shfl_xor_sync(0xFFFFFFFFu, acc.wsa, 16);
-            acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
-            acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
-            if (is_g) {
-                const int64_t o = (static_cast<int64_t>(tl.slot) * 2 + rank) * kBlk + s;
-                args.part.add[o] = acc.add;
-                args.part.dom[o] = acc.dom;
-                args.part.wsa[o] = acc.wsa;
-                args.part.wsd[o] = acc.wsd;
-                args.part.wsde[o] = acc.wsde;
+                // even-j and odd-j halves of the row
+                acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
+                acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);
+                acc.wsa += __shfl_xor_sync(0xFFFFFFFFu, acc.wsa, 16);
+                acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
+                acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
+                if (is_g) {
+                    const int64_t o = part_index(tl.slot, static_cast<int>(rank), half, s);
+                    args.part.add[o] = acc.add;
+                    args.part.dom[o] = acc.dom;
+                    args.part.wsa[o] = acc.wsa;
+                    args.part.wsd[o] = acc.wsd;
+                    args.part.wsde[o] = acc.wsde;
+                }
             }
         }
     }
@@ -320,9 +326,12 @@ namespace {
 constexpr int kWStages = 5;
 constexpr int kWStageBytes = kABytes + 2 * kBBytes;          // 40 KB per CTA per stage
 constexpr int kWSmemBytes = kWStages * kWStageBytes + 1024 + 256;
+constexpr int kWThreads = 320;                               // TMA warp, MMA warp, 8 epilogue warps
 }  // namespace
 
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+// 128 registers x 320 threads leave a third of the register file to the unpack blocks that run beside this kernel
+// (at the 162 ptxas would take, only one unpack block fits per SM and the unpack becomes the critical path)
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
 band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const BandArgs args) {
     extern __shared__ uint8_t smem_raw[];
@@ -342,7 +351,7 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
         for (int s = 0; s < kWStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         mbar_init(tfull, 1);
-        mbar_init(tempty, 8);                  // 4 epilogue warps x 2 CTAs
+        mbar_init(tempty, 16);                 // 8 epilogue warps x 2 CTAs
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -416,8 +425,11 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
         __syncwarp();
     } else {
-        // ===== epilogue: as in band_tc_kernel, once per j-block of the supertile =====
+        // ===== epilogue: EIGHT warps per CTA.  Warps 2-5 score j-SNPs 0..31 of every j-block (TMEM columns of the
+        // half CTA 0 staged), warps 6-9 j-SNPs 32..63; warp w reads TMEM lanes 32 (w % 4) .. +31 as the hardware
+        // demands.  Each writes the partial of its half, so the exposed epilogue is half as long. =====
         const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
         const bool is_g = lane < 16;
         const int s = 16 * q + (lane & 15);
         int n = 0;
@@ -434,8 +446,9 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 const uint32_t taddr = tmem_base + jj * kBRows + (static_cast<uint32_t>(32 * q) << 16);
                 const int32_t j0 = tl.j0 + kBlk * jj;
 #pragma unroll 1
-                for (int c = 0; c < 4; ++c) {
-                    const uint32_t col = 96 * (c >> 1) + 16 * (c & 1);
+                for (int c2 = 0; c2 < 2; ++c2) {
+                    const int c = 2 * half + c2;
+                    const uint32_t col = 96 * half + 16 * c2;
                     int32_t vm[16], vh[16], va[16];
                     tmem_ld16(taddr + col, vm);
                     tmem_ld16(taddr + col + 32, vh);
@@ -456,13 +469,19 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                         pair_eval(args, row, j0 + jl, Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
                     }
                 }
+                if (jj == n_j - 1) {
+                    // this warp is done with both accumulators: tell the leader's MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_leader(tempty);
+                }
                 acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
                 acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);
                 acc.wsa += __shfl_xor_sync(0xFFFFFFFFu, acc.wsa, 16);
                 acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
                 acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
                 if (is_g) {
-                    const int64_t o = (static_cast<int64_t>(tl.slot + jj) * 2 + rank) * kBlk + s;
+                    const int64_t o = part_index(tl.slot + jj, static_cast<int>(rank), half, s);
                     args.part.add[o] = acc.add;
                     args.part.dom[o] = acc.dom;
                     args.part.wsa[o] = acc.wsa;
@@ -470,10 +489,6 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                     args.part.wsde[o] = acc.wsde;
                 }
             }
-            // both accumulators read: hand them back to the leader's MMA warp
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_leader(tempty);
         }
     }
 
@@ -552,7 +567,7 @@ void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_coun
     if (args.n_tiles <= 0) return;
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
     const int pairs = args.n_tiles < sm_count / 2 ? args.n_tiles : sm_count / 2;
-    band_tc_wide_kernel<<<2 * pairs, kThreads, kWSmemBytes, st>>>(maps->a, maps->b, args);
+    band_tc_wide_kernel<<<2 * pairs, kWThreads, kWSmemBytes, st>>>(maps->a, maps->b, args);
     CUDA_CHECK(cudaGetLastError());
 }
 

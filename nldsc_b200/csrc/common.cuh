@@ -48,7 +48,11 @@ struct Tile {
                        // the same A tiles (its partials go to slot + 1), or -1.  Unused (0) by the narrow kernel.
 };
 
-// Per-row partial sums a supertile contributes (SoA, index = (tile * 2 + rank) * 64 + row).
+// Per-row partial sums a (64 x 64 SNP) tile contributes, in two halves: j-SNPs 0..31 and 32..63 of the j-block
+// (the wide kernel scores the halves in different warps).  SoA, index = part_index(slot, rank, half, row).
+__host__ __device__ inline int64_t part_index(int64_t slot, int rank, int half, int row) {
+    return ((slot * 2 + rank) * 2 + half) * kBlk + row;
+}
 struct Partials {
     double* add;     // sum of r2adj(A_i, A_j)
     double* dom;     // sum of r2adj(A_i, D_j) over dominance-usable j

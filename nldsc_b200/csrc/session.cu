@@ -915,7 +915,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         launch_copy16(h + 2 * b_win, s->d_tiles, b_tiles, st);
         launch_copy16(h + 2 * b_win + b_tiles, s->d_tile_begin, b_tb, st);
     }
-    const size_t np = static_cast<size_t>(s->max_chunk_slots) * 2 * kBlk;
+    const size_t np = static_cast<size_t>(s->max_chunk_slots) * 4 * kBlk;      // [slot][rank][half][row]
     s->part.add = amalloc<double>(s->arena, np);
     s->part.dom = amalloc<double>(s->arena, np);
     s->part.wsa = amalloc<int32_t>(s->arena, np);
@@ -1557,8 +1557,8 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         SnpCoef* d_coef = dmalloc<SnpCoef>(rows);
         uint8_t* d_flags = dmalloc<uint8_t>(rows);
         int32_t* d_w = dmalloc<int32_t>(static_cast<size_t>(rows) * 2);
-        double* d_pd = dmalloc<double>(4 * kBlk);
-        int32_t* d_pi = dmalloc<int32_t>(6 * kBlk);
+        double* d_pd = dmalloc<double>(8 * kBlk);             // one slot: [rank][half][row] per field
+        int32_t* d_pi = dmalloc<int32_t>(12 * kBlk);
         struct Free {
             std::vector<void*> v;
             ~Free() { for (void* q : v) cudaFree(q); }
@@ -1586,10 +1586,10 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         a.adj_c = 1.0;
         a.rsq_thr = 0.0;
         a.part.add = d_pd;
-        a.part.dom = d_pd + 2 * kBlk;
+        a.part.dom = d_pd + 4 * kBlk;
         a.part.wsa = d_pi;
-        a.part.wsd = d_pi + 2 * kBlk;
-        a.part.wsde = d_pi + 4 * kBlk;
+        a.part.wsd = d_pi + 4 * kBlk;
+        a.part.wsde = d_pi + 8 * kBlk;
         a.dump = d_dump;
         const char* band = getenv("NLDSC_BAND");
         if (band && strcmp(band, "simt") == 0) {
@@ -1645,8 +1645,8 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         SnpCoef* d_coef = dmalloc<SnpCoef>(rows);
         uint8_t* d_flags = dmalloc<uint8_t>(rows);
         int32_t* d_w = dmalloc<int32_t>(static_cast<size_t>(rows) * 2);
-        double* d_pd = dmalloc<double>(static_cast<size_t>(n_tiles) * 4 * kBlk);
-        int32_t* d_pi = dmalloc<int32_t>(static_cast<size_t>(n_tiles) * 6 * kBlk);
+        double* d_pd = dmalloc<double>(static_cast<size_t>(n_tiles) * 8 * kBlk);
+        int32_t* d_pi = dmalloc<int32_t>(static_cast<size_t>(n_tiles) * 12 * kBlk);
         struct Free {
             std::vector<void*> v;
             ~Free() { for (void* q : v) cudaFree(q); }
@@ -1681,10 +1681,10 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         a.inv_n = 1.0 / n_org;
         a.adj_c = 1.0;
         a.part.add = d_pd;
-        a.part.dom = d_pd + static_cast<size_t>(n_tiles) * 2 * kBlk;
+        a.part.dom = d_pd + static_cast<size_t>(n_tiles) * 4 * kBlk;
         a.part.wsa = d_pi;
-        a.part.wsd = d_pi + static_cast<size_t>(n_tiles) * 2 * kBlk;
-        a.part.wsde = d_pi + static_cast<size_t>(n_tiles) * 4 * kBlk;
+        a.part.wsd = d_pi + static_cast<size_t>(n_tiles) * 4 * kBlk;
+        a.part.wsde = d_pi + static_cast<size_t>(n_tiles) * 8 * kBlk;
         a.probe = mode == 4 ? 0 : mode;
         BandMaps* maps = band_maps_create(d_planes, rows, npad);
         struct MapFree { BandMaps* m; ~MapFree() { band_maps_destroy(m); } } mf{maps};
