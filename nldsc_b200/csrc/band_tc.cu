@@ -69,6 +69,24 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         if (spins > (1u << 26)) __trap();
     }
 }
+// The same wait for warps that have nothing else to do for a long time (the epilogue warps during a supertile's
+// K loop): sleep between polls, so that eight polling warps do not take issue slots from the one thread that
+// issues the MMAs and the one that issues the TMA loads.
+__device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done = 0;
+    for (uint32_t spins = 0; !done; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(addr), "r"(parity)
+            : "memory");
+        if (!done) __nanosleep(256);
+        if (spins > (1u << 24)) __trap();
+    }
+}
 // remote arrive on the leader (even) CTA's copy of `bar`
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerMask) : "memory");
@@ -438,7 +456,7 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             const int32_t i0 = tl.i0[rank];
             const RowCtx row = load_row_ctx(args, i0 + s);
             const int n_j = tl.b_row2 >= 0 ? 2 : 1;
-            mbar_wait(tfull, n & 1);
+            mbar_wait_idle(tfull, n & 1);
             tc_fence_after();
 #pragma unroll 1
             for (int jj = 0; jj < n_j; ++jj) {
