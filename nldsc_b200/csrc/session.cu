@@ -769,7 +769,9 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     tr.lap("plane ring");
 
     // ---- chunks: greedy runs of i-blocks whose column span fits the ring
-    // Chunk size: big chunks amortise the band kernel's launch and its partial last wave; with a concurrent
+    // Chunk size: 8,192 rows measured best on configs[1] once consecutive band launches overlap (two streams): 3.65 ms
+    // per step against 3.74 (8,192 / 16,384 / 32,768 ...) and 3.96 (16,384).  Earlier reasoning, still true for the ramp:
+    // big chunks amortise the band kernel's launch and its partial last wave; with a concurrent
     // upload (`ramp`) a chunk cannot start before its last row has landed, so chunks start small, double,
     // and stop at half the regular size.
     const bool fixed_rows = getenv("NLDSC_CHUNK_ROWS") != nullptr;
@@ -778,7 +780,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // stays short when rows are long (N = 315,599: 16,384 rows would be 1.3 GB = 24 ms).
     const size_t byte_rows = std::max<size_t>(2048, env_size("NLDSC_CHUNK_BYTES", size_t(256) << 20) / static_cast<size_t>(s->bps) / kBlk * kBlk);
     const int32_t chunk_rows = static_cast<int32_t>(
-        std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? std::min<size_t>(8192, byte_rows) : 32768),
+        std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? std::min<size_t>(8192, byte_rows) : 8192),
                          static_cast<size_t>(std::numeric_limits<int32_t>::max() / 2)));
     // without a concurrent upload a short first chunk still pays: its unpack is the only one that runs alone
     const char* rp = getenv("NLDSC_RAMP");

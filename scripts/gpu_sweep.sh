@@ -8,11 +8,11 @@ import json,sys
 d=json.loads(sys.stdin.read()); r=d['roofline']
 print('ms/step %.3f e2e %.3f ms frac %.3f band %.3f dev %.3f chunks %d' % (d['ms_per_step'], d['e2e']['ms_per_step'], r['frac'], r['ms_band'], r['ms_step_device'], r['chunks']))"
 done <<'EOL'
+NLDSC_CHUNK_ROWS=6144
+NLDSC_CHUNK_ROWS=8192
+NLDSC_CHUNK_ROWS=10240
+NLDSC_CHUNK_ROWS=12288
+NLDSC_CHUNK_ROWS=16384
+NLDSC_CHUNK_ROWS=6144
 NLDSC_TAPER=0
-NLDSC_TAPER=1
-NLDSC_TAPER=1 NLDSC_TAPER_MIN=2048
-NLDSC_TAPER=1 NLDSC_TAPER_MIN=1024
-NLDSC_TAPER=0
-NLDSC_TAPER=1 NLDSC_TAPER_MIN=2048
 EOL
-NLDSC_TRACE=1 python scripts/e2e_trace.py 2>&1 | grep -E "device:|gpu 0|call" | tail -6
