@@ -14,7 +14,7 @@ CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
 timeout 600 $CMD > gpurun_out/plain.log 2>&1 && \
 timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -k "regex:band_|unpack_|count_kernel|stats_kernel|finalize_|zero_rows|windows_kernel|copy16_kernel|peak_probe" -c 600 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
 echo "ncu_launches rc=$?" >> gpurun_out/rc.txt
-timeout 1500 ncu --set full --clock-control none --import-source on -k regex:band_tc -s 15 -c 5 -f -o gpurun_out/band_tc $CMD > gpurun_out/ncu_full.log 2>&1
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:band_tc -s 39 -c 13 -f -o gpurun_out/band_tc $CMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu_full rc=$?" >> gpurun_out/rc.txt
 fi
 cat gpurun_out/rc.txt; tail -5 gpurun_out/t_all.log; cat gpurun_out/smoke.log | tail -2; cat gpurun_out/bench.log; tail -5 gpurun_out/bench.err; cat gpurun_out/bench_ref.log
