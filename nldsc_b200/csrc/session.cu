@@ -504,9 +504,10 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     s->use_simt = band && strcmp(band, "simt") == 0;
     // two j-blocks per supertile pay once the MMA time of a supertile outweighs the (then exposed) epilogue
     const char* wd = getenv("NLDSC_WIDE");
-    // Measured crossover: a wide supertile costs 0.50 us per K-step + 12 us of exposed epilogue, two narrow ones
-    // 2 x max(0.35 us per K-step, 6 us): wide wins from ~57 K-steps (N ~ 7,200) on.
-    s->wide = !s->use_simt && (wd ? wd[0] == '1' : s->npad / kKAlign >= 64);
+    // Measured: the wide kernel wins at every N tried (N = 2,504: 1.39 vs 1.60 ms per 100,000 SNPs; 5,000: 2.13 vs 2.41;
+    // 10,000: 3.65 vs 4.33; N >= 100,000: 10-35 %), also where the epilogue dominates -- it has twice the epilogue warps.
+    // NLDSC_WIDE=0 selects the narrow, double-buffered kernel (kept as the second implementation the tests compare).
+    s->wide = !s->use_simt && (wd ? wd[0] == '1' : true);
     s->load_begin = load_begin;
     s->load_end = load_end;
     s->n_load = load_end - load_begin;

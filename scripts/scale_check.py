@@ -11,6 +11,9 @@ from oracle import ld_oracle
 CASES = {
     # BASELINE.json configs[0]: the reference's own CPU-runnable case
     "cfg1":       dict(n_org=1000, n_snp=10000, missing=0.0, density=340.0, wind=1.0, oracle_rows=3),
+    # reference-panel sizes (1000 Genomes: 2,504 samples) and a mid-size cohort: which band kernel wins where
+    "kg_panel":   dict(n_org=2504, n_snp=100000, missing=0.0, density=340.0, wind=1.0, oracle_rows=0),
+    "mid_cohort": dict(n_org=5000, n_snp=100000, missing=0.02, density=340.0, wind=1.0, oracle_rows=0),
     "ukb_slice":  dict(n_org=315599, n_snp=40000, missing=0.02, density=340.0, wind=1.0, oracle_rows=2),
     "ukb_ring":   dict(n_org=315599, n_snp=40000, missing=0.02, density=340.0, wind=1.0, oracle_rows=0,
                        env={"NLDSC_PLANE_BYTES": "12e9"}),
@@ -21,7 +24,7 @@ CASES = {
 }
 out = {}
 kept_results = {}
-for name in (sys.argv[1:] or [k for k in CASES if k not in ("cfg5_full", "cfg5_slice", "cfg1")]):
+for name in (sys.argv[1:] or [k for k in CASES if k not in ("cfg5_full", "cfg5_slice", "cfg1", "kg_panel", "mid_cohort")]):
     c = CASES[name]
     for k, v in c.get("env", {}).items():
         os.environ[k] = v

@@ -109,9 +109,11 @@ def test_cross_counts_exact(impl, n_org, n_snp, monkeypatch):
 
 # ---- end to end ------------------------------------------------------------------------------
 
-@pytest.mark.parametrize("impl", ["simt", "tc"])
+@pytest.mark.parametrize("impl", ["simt", "tc", "tc_narrow"])
 def test_golden_reference_parity(golden, impl, monkeypatch):
-    monkeypatch.setenv("NLDSC_BAND", impl)
+    monkeypatch.setenv("NLDSC_BAND", impl.split("_")[0])
+    if impl == "tc_narrow":
+        monkeypatch.setenv("NLDSC_WIDE", "0")
     got = _run(golden)
     assert_ld_close(got, _ref64(golden), label=f"{golden['name']}[{impl}]")
 
@@ -307,18 +309,20 @@ def test_multi_piece_bed_read_equals_host_buffer(tmp_path, monkeypatch):
 
 
 def test_wide_supertiles_equal_narrow_bitwise(monkeypatch):
-    """band_tc_wide_kernel (two j-blocks per A tile, chosen for N >= 65,536) puts its partial sums into the same
-    slots as the narrow kernel: forced on at a small N it must reproduce the default run bit for bit, also with
-    chunks and a wrapping ring, and its raw cross-counts must pass the oracle bar."""
+    """band_tc_wide_kernel (two j-blocks per A tile, eight epilogue warps; the default) and band_tc_kernel (one j-block,
+    double-buffered accumulators; NLDSC_WIDE=0) put their partial sums into the same slots: they must agree bit for
+    bit, also with chunks and a wrapping ring, and pass the oracle bar."""
     g = _case(1003, 3000, 0.02, seed=21, wind=0.7)
-    base = _run(g)
-    assert_ld_close(base, _oracle(g), label="narrow")
-    monkeypatch.setenv("NLDSC_WIDE", "1")
     wide = _run(g)
+    assert_ld_close(wide, _oracle(g), label="wide")
+    monkeypatch.setenv("NLDSC_WIDE", "0")
+    narrow = _run(g)
     for k in RESULT_KEYS:
-        assert np.array_equal(base[k], wide[k], equal_nan=True), k
-    monkeypatch.setenv("NLDSC_CHUNK_ROWS", "256")
-    monkeypatch.setenv("NLDSC_PLANE_BYTES", str(1024 * 4 * 1024))
-    small = _run(g)
-    for k in RESULT_KEYS:
-        assert np.array_equal(base[k], small[k], equal_nan=True), k
+        assert np.array_equal(narrow[k], wide[k], equal_nan=True), k
+    for w in ("0", "1"):
+        monkeypatch.setenv("NLDSC_WIDE", w)
+        monkeypatch.setenv("NLDSC_CHUNK_ROWS", "256")
+        monkeypatch.setenv("NLDSC_PLANE_BYTES", str(1024 * 4 * 1024))
+        small = _run(g)
+        for k in RESULT_KEYS:
+            assert np.array_equal(wide[k], small[k], equal_nan=True), (w, k)
