@@ -337,7 +337,8 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 // tiles of a K-step are then multiplied with both B tiles, D0[256 x 192] in TMEM columns 0..191 and D1 in 192..383.
 // Operand bytes from L2 drop from 56 KB to 40 KB per 64 columns of a CTA pair, which lifts the L2 -> SM bound the
 // narrow kernel runs into.  Both accumulators belong to one supertile, so the epilogue is NOT hidden behind the
-// next supertile's MMAs (12 us against 2 x 2.4 us x N / 10,000 of MMA time): used for N >= 65,536 only.
+// next supertile's MMAs; eight epilogue warps (two per 32 TMEM lanes, one per half of a j-block) keep it to
+// 2 x 3 us per supertile.  Measured faster than the narrow kernel at every N from 2,504 up: the default.
 // Partials of the two j-blocks go to slots `slot` and `slot + 1`, exactly where the narrow kernel puts them, so both
 // kernels give bitwise identical scores.
 namespace {
