@@ -281,5 +281,5 @@ def debug_band_probe(mode: int, n_org: int, n_tiles: int, reps: int = 5) -> dict
     _raise(lib().nldsc_ld_debug_band_probe(C.c_int32(mode), C.c_int32(n_org), C.c_int32(n_tiles), C.c_int32(reps),
                                            C.byref(ms), err, C.c_size_t(512)), err)
     npad = (n_org + 127) // 128 * 128
-    ops = 2.0 * 256 * 192 * npad * n_tiles
-    return {"ms": ms.value, "tops": ops / (ms.value * 1e-3) / 1e12, "gbs_operands": n_tiles * 2 * 28672 * (npad // 128) / (ms.value * 1e-3) / 1e9}
+    ops = 2.0 * 256 * 192 * npad * n_tiles * (2 if mode >= 5 else 1)      # modes 5, 6: wide supertiles, two j-blocks each
+    return {"ms": ms.value, "tops": ops / (ms.value * 1e-3) / 1e12, "gbs_operands": n_tiles * 2 * (40960 if mode >= 5 else 28672) * (npad // 128) / (ms.value * 1e-3) / 1e9}

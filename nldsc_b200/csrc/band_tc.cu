@@ -398,6 +398,11 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 const uint32_t bytes = 2u * (kABytes + (two ? 2 : 1) * kBBytes);          // both CTAs' bytes
                 for (int k = 0; k < args.k_steps; ++k) {
                     mbar_wait(&empty[stage], phase ^ 1);
+                    if (args.probe == 1) {           // tensor-pipe probe: no loads, operands are whatever the stage holds
+                        if (rank == 0) mbar_expect_tx(&full[stage], 0);
+                        if (++stage == kWStages) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     if (rank == 0) mbar_expect_tx(&full[stage], bytes);
                     uint8_t* sa = smem + stage * kWStageBytes;
                     uint8_t* sb = sa + kABytes;

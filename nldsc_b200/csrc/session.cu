@@ -1631,7 +1631,7 @@ int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* l
 int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int32_t reps, float* ms_out, char* err,
                               size_t errlen) {
     return guarded(err, errlen, [&] {
-        if (mode < 0 || mode > 4 || n_org <= 0 || n_tiles <= 0 || reps <= 0 || !ms_out) throw InvalidArgument("bad arguments");
+        if (mode < 0 || mode > 6 || mode == 5 || n_org <= 0 || n_tiles <= 0 || reps <= 0 || !ms_out) throw InvalidArgument("bad arguments");
         usable_devices();
         const int dev = first_device_from_env();
         CUDA_CHECK(cudaSetDevice(dev));
@@ -1648,8 +1648,9 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         SnpCoef* d_coef = dmalloc<SnpCoef>(rows);
         uint8_t* d_flags = dmalloc<uint8_t>(rows);
         int32_t* d_w = dmalloc<int32_t>(static_cast<size_t>(rows) * 2);
-        double* d_pd = dmalloc<double>(static_cast<size_t>(n_tiles) * 8 * kBlk);
-        int32_t* d_pi = dmalloc<int32_t>(static_cast<size_t>(n_tiles) * 12 * kBlk);
+        const size_t n_slots = static_cast<size_t>(n_tiles) * (mode >= 5 ? 2 : 1);
+        double* d_pd = dmalloc<double>(n_slots * 8 * kBlk);
+        int32_t* d_pi = dmalloc<int32_t>(n_slots * 12 * kBlk);
         struct Free {
             std::vector<void*> v;
             ~Free() { for (void* q : v) cudaFree(q); }
@@ -1657,7 +1658,8 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         CUDA_CHECK(cudaMemset(d_packed, 0xB9, static_cast<size_t>(rows) * bps + 16));   // codes 01 10 11 10 per byte
         CUDA_CHECK(cudaMemset(d_coef, 0, sizeof(SnpCoef) * rows));
         // modes 0-2: every pair rejected (cheapest epilogue); 3 = epilogue only and 4 = whole kernel, every pair scored
-        const bool full_epi = mode >= 3;
+        const bool wide = mode >= 5;                 // 6 = wide kernel, whole, cheap epilogue (5, its MMA-only variant, deadlocks: rejected above)
+        const bool full_epi = mode == 3 || mode == 4;
         CUDA_CHECK(cudaMemset(d_flags, full_epi ? (kFlagKeep | kFlagDom) : 0, rows));
         CUDA_CHECK(cudaMemset(d_w, 0, sizeof(int32_t) * 2 * rows));
         if (full_epi) {
@@ -1668,7 +1670,8 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         std::vector<Tile> tiles(n_tiles);
         for (int32_t t = 0; t < n_tiles; ++t) {       // band-like walk: 22 j-blocks per i-block pair
             const int32_t p = (t / 22) % (nb / 2), jb = (2 * p + t % 22) % nb;
-            tiles[t] = Tile{{2 * p * kBlk, (2 * p + 1) * kBlk}, {2 * p * kBlk, (2 * p + 1) * kBlk}, jb * kBlk, jb * kBlk, t, 0};
+            tiles[t] = Tile{{2 * p * kBlk, (2 * p + 1) * kBlk}, {2 * p * kBlk, (2 * p + 1) * kBlk}, jb * kBlk, jb * kBlk,
+                            wide ? 2 * t : t, wide ? ((jb + 1) % nb) * kBlk : -1};
         }
         CUDA_CHECK(cudaMemcpy(d_tiles, tiles.data(), sizeof(Tile) * n_tiles, cudaMemcpyHostToDevice));
         BandArgs a{};
@@ -1684,19 +1687,20 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         a.inv_n = 1.0 / n_org;
         a.adj_c = 1.0;
         a.part.add = d_pd;
-        a.part.dom = d_pd + static_cast<size_t>(n_tiles) * 4 * kBlk;
+        a.part.dom = d_pd + n_slots * 4 * kBlk;
         a.part.wsa = d_pi;
-        a.part.wsd = d_pi + static_cast<size_t>(n_tiles) * 4 * kBlk;
-        a.part.wsde = d_pi + static_cast<size_t>(n_tiles) * 8 * kBlk;
-        a.probe = mode == 4 ? 0 : mode;
+        a.part.wsd = d_pi + n_slots * 4 * kBlk;
+        a.part.wsde = d_pi + n_slots * 8 * kBlk;
+        a.probe = mode == 4 ? 0 : (mode == 5 ? 1 : (mode == 6 ? 0 : mode));
         BandMaps* maps = band_maps_create(d_planes, rows, npad);
         struct MapFree { BandMaps* m; ~MapFree() { band_maps_destroy(m); } } mf{maps};
         cudaEvent_t e0, e1;
         CUDA_CHECK(cudaEventCreate(&e0));
         CUDA_CHECK(cudaEventCreate(&e1));
-        launch_band_tc(maps, a, sm_count, nullptr);                                      // warm-up
+        auto launch = wide ? launch_band_tc_wide : launch_band_tc;
+        launch(maps, a, sm_count, nullptr);                                              // warm-up
         CUDA_CHECK(cudaEventRecord(e0, nullptr));
-        for (int r = 0; r < reps; ++r) launch_band_tc(maps, a, sm_count, nullptr);
+        for (int r = 0; r < reps; ++r) launch(maps, a, sm_count, nullptr);
         CUDA_CHECK(cudaEventRecord(e1, nullptr));
         CUDA_CHECK(cudaEventSynchronize(e1));
         float ms = 0;
