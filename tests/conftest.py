@@ -36,7 +36,11 @@ def golden(request):
 def assert_ld_close(got, want, *, exact_wsde=True, rtol=1e-9, label=""):
     """The parity bar of BASELINE.json: filter decisions / retained lists / counts bit-exact,
     L2 within 1e-9 relative, L2D within 1e-9 absolute-or-relative-to-max(|L2D|, 1)
-    (L2D is a sum of bias-corrected terms and legitimately crosses zero)."""
+    (L2D is a sum of bias-corrected terms and legitimately crosses zero).  L2 gets the same
+    max(|L2|, 1) denominator: at N = 3 or 5 organisms the bias-corrected terms are of size 1 and
+    a row's sum cancels to an exact zero, where the oracle itself holds a 1e-15 rounding residue
+    and a pure relative error is 0/0 (found by the 600-seed soak, scripts/soak.sh).  For every
+    |L2| >= 1, which is every row of a real cohort, this is the plain relative bar."""
     keep_w = ~np.isnan(want["l2"])
     assert np.array_equal(np.isnan(got["l2"]), ~keep_w), label + " retained-SNP list"
     assert np.array_equal(np.isnan(got["l2d"]), ~keep_w), label + " l2d NaN pattern"
@@ -48,7 +52,7 @@ def assert_ld_close(got, want, *, exact_wsde=True, rtol=1e-9, label=""):
     assert np.array_equal(np.isnan(got["residuals_std"]), np.isnan(want["residuals_std"])), label + " rstd NaN"
     k = keep_w
     if k.any():
-        rel = np.max(np.abs(got["l2"][k] - want["l2"][k]) / np.abs(want["l2"][k]))
+        rel = np.max(np.abs(got["l2"][k] - want["l2"][k]) / np.maximum(np.abs(want["l2"][k]), 1.0))
         assert rel <= rtol, f"{label} L2 rel err {rel}"
         d = np.max(np.abs(got["l2d"][k] - want["l2d"][k]) / np.maximum(np.abs(want["l2d"][k]), 1.0))
         assert d <= rtol, f"{label} L2D err {d}"

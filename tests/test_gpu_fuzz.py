@@ -4,6 +4,8 @@ Every case draws organisms, SNPs, missingness, map density and window at random,
 under one randomly chosen execution variant (tiny chunks, a plane ring barely wider than a window, one
 stream, one band stream, SIMT band kernel, the narrow tcgen05 kernel, 2 shards when the box has 2 GPUs).  All variants must meet the
 parity bar against the oracle, and be bitwise equal to the default variant of the same case."""
+import os
+
 import numpy as np
 import pytest
 
@@ -42,7 +44,8 @@ def _draw(seed):
     return n_org, n_snp, missing, density, wind
 
 
-@pytest.mark.parametrize("seed", range(50))
+# NLDSC_FUZZ_SEEDS=500 turns the same test into a soak run (scripts/soak.sh)
+@pytest.mark.parametrize("seed", range(int(os.environ.get("NLDSC_FUZZ_SEEDS", "50"))))
 def test_random_case_matches_oracle(seed, monkeypatch):
     n_org, n_snp, missing, density, wind = _draw(seed)
     spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=missing, seed=500 + seed, density=density)
