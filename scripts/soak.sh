@@ -1,4 +1,4 @@
-# Soak: 600 fuzz seeds (60 per execution variant) against the oracle on one B200.
+# Soak on one B200: 600 small fuzz seeds (60 per execution variant) and 30 multi-chunk cases against the oracle.
 cd $GRAFT_REPO_ROOT; mkdir -p gpurun_out
-NLDSC_FUZZ_SEEDS=600 timeout 420 python -m pytest tests/test_gpu_fuzz.py -m gpu -q -p no:cacheprovider > gpurun_out/soak.log 2>&1; echo "soak rc=$?"
-tail -5 gpurun_out/soak.log
+NLDSC_FUZZ_SEEDS=${NLDSC_FUZZ_SEEDS:-600} NLDSC_FUZZ_MID=${NLDSC_FUZZ_MID:-30} timeout 400 python -m pytest tests/test_gpu_fuzz.py -m gpu -q -p no:cacheprovider > gpurun_out/soak.log 2>&1; echo "soak rc=$?"
+grep -n "^E  .*Error\|^FAILED" gpurun_out/soak.log | head -20; tail -3 gpurun_out/soak.log

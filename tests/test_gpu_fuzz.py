@@ -73,3 +73,58 @@ def test_random_case_matches_oracle(seed, monkeypatch):
     else:
         for key in RESULT_KEYS:
             assert np.array_equal(got[key], base[key], equal_nan=True), f"{label} {variant}: {key} differs from the default run"
+
+
+MID_VARIANTS = [
+    {"NLDSC_CHUNK_ROWS": "512"},
+    {"NLDSC_CHUNK_ROWS": "1024", "NLDSC_PLANE_BYTES": "ring"},
+    {"NLDSC_WIDE": "0"},
+    {"NLDSC_OVERLAP": "0", "NLDSC_CHUNK_ROWS": "2048"},
+    {"NLDSC_GPUS": "2"},
+    {"NLDSC_BAND_STREAMS": "1", "NLDSC_WIDE_OVERLAP": "0"},
+    {"NLDSC_FIRST_BYTES": "1000000", "NLDSC_CHUNK_BYTES": "3000000"},
+]
+
+
+# Multi-chunk shapes (thousands of SNPs, windows hundreds of SNPs wide): every execution variant must
+# reproduce the default run bit for bit, and 12 random rows must meet the oracle's bar.
+# Off by default (each case costs ~5 s of host-side generation); NLDSC_FUZZ_MID=30 is the soak setting (scripts/soak.sh).
+@pytest.mark.parametrize("seed", range(int(os.environ.get("NLDSC_FUZZ_MID", "0"))))
+def test_midsize_case_variants_bitwise(seed, monkeypatch):
+    rng = np.random.default_rng(7000 + seed)
+    n_org = int(rng.choice([500, 1027, 2048, 3001, 5000]))
+    n_snp = int(rng.choice([3000, 7777, 12000, 20000]))
+    density = float(rng.choice([340.0, 2000.0, 6000.0]))
+    wind = float(rng.choice([0.05, 0.2, 1.0]))
+    spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=float(rng.choice([0.0, 0.02])), seed=900 + seed,
+                           density=density)
+    packed = synth.generate_packed(spec, workers=4)
+    cm, _ = synth.genetic_map(spec)
+    args = (n_snp, n_org, cm, wind, 1e-4, 1e-5, 1.0 / n_snp)
+    label = f"mid seed {seed}: N={n_org} M={n_snp} dens={density} wind={wind}"
+    base = capi.calculate_packed(packed, *args)
+    rows = np.sort(rng.choice(n_snp, size=12, replace=False))
+    want = ld_oracle.ld_scores(packed, n_org, cm, wind, 1e-4, 1e-5, 1.0 / n_snp, rows=rows)
+    assert np.array_equal(np.isnan(base["l2"]), ~want["keep"]), label + " retained-SNP list"
+    assert np.array_equal(base["maf"], want["maf"], equal_nan=True), label + " maf"
+    for r in rows:
+        if not want["keep"][r]:
+            continue
+        assert base["l2_ws"][r] == want["l2_ws"][r] and base["l2d_ws"][r] == want["l2d_ws"][r], f"{label} row {r} counts"
+        assert base["l2d_wse"][r] == want["l2d_wse"][r], f"{label} row {r} WSDE"
+        assert abs(base["l2"][r] - want["l2"][r]) <= 1e-9 * max(abs(want["l2"][r]), 1.0), f"{label} row {r} L2"
+        assert abs(base["l2d"][r] - want["l2d"][r]) <= 1e-9 * max(abs(want["l2d"][r]), 1.0), f"{label} row {r} L2D"
+    for variant in (MID_VARIANTS[seed % len(MID_VARIANTS)], MID_VARIANTS[(seed + 3) % len(MID_VARIANTS)]):
+        variant = dict(variant)
+        if variant.get("NLDSC_PLANE_BYTES") == "ring":
+            lo, hi = capi.plan_windows(cm, wind)
+            rows_ring = ((int(np.max(hi - lo)) + 1) // 64 + 6) * 64 + 2048
+            variant["NLDSC_PLANE_BYTES"] = str(rows_ring * 4 * ((n_org + 127) // 128 * 128))
+        if variant.get("NLDSC_GPUS") == "2" and capi.device_count() < 2:
+            variant.pop("NLDSC_GPUS")
+        with monkeypatch.context() as mp:
+            for k, v in variant.items():
+                mp.setenv(k, v)
+            got = capi.calculate_packed(packed, *args)
+        for key in RESULT_KEYS:
+            assert np.array_equal(got[key], base[key], equal_nan=True), f"{label} {variant}: {key} differs from the default run"
