@@ -88,8 +88,8 @@ MID_VARIANTS = [
 
 # Multi-chunk shapes (thousands of SNPs, windows hundreds of SNPs wide): every execution variant must
 # reproduce the default run bit for bit, and 12 random rows must meet the oracle's bar.
-# Off by default (each case costs ~5 s of host-side generation); NLDSC_FUZZ_MID=30 is the soak setting (scripts/soak.sh).
-@pytest.mark.parametrize("seed", range(int(os.environ.get("NLDSC_FUZZ_MID", "0"))))
+# Four cases by default; NLDSC_FUZZ_MID=30 is the soak setting (scripts/soak.sh).
+@pytest.mark.parametrize("seed", range(int(os.environ.get("NLDSC_FUZZ_MID", "4"))))
 def test_midsize_case_variants_bitwise(seed, monkeypatch):
     rng = np.random.default_rng(7000 + seed)
     n_org = int(rng.choice([500, 1027, 2048, 3001, 5000]))
