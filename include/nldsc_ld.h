@@ -94,7 +94,7 @@ typedef struct nldsc_ld_stats {
     int32_t load_begin;       /* first SNP row the shard needs (owned range minus halo, 64-aligned) */
     int32_t load_end;         /* one past the last SNP row needed */
     int32_t npad;             /* padded organisms per plane row (bytes) */
-    int32_t band_impl;        /* 1 = tcgen05 kernel, 2 = its wide variant (N >= 8,192), 0 = SIMT yardstick (NLDSC_BAND=simt) */
+    int32_t band_impl;        /* 1 = tcgen05 kernel, 2 = its wide variant (two j-blocks per supertile; the default at every N), 0 = SIMT yardstick (NLDSC_BAND=simt) */
     float ms_count;           /* CUDA-event times of the last run(), per kernel family; counting is fused
                                  into the unpack kernel, so this one stays 0 */
     float ms_stats;
@@ -124,6 +124,27 @@ int nldsc_ld_session_sync(nldsc_ld_session* s, char* err, size_t errlen);
 int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* out);
 void nldsc_ld_session_destroy(nldsc_ld_session* s);
 
+/* What the last nldsc_ld_calculate* call made on the CALLING THREAD did, one record per shard (= per GPU, or per
+ * NLDSC_TEST_SHARDS shard): host wall time of every phase and the CUDA-event times of the device work.  Written
+ * whether or not NLDSC_TRACE is set; the records are what the genome driver and bench.py report as per-GPU busy time. */
+typedef struct nldsc_ld_shard_report {
+    int32_t device;
+    int32_t row_begin, row_end;      /* owned rows */
+    int32_t load_begin, load_end;    /* rows read and unpacked: owned rows + window halo */
+    int32_t chunks;
+    int64_t pairs;                   /* ordered in-window pairs of the owned rows before the MAF filter */
+    int64_t bytes_h2d;               /* packed genotype bytes this shard uploaded */
+    float ms_open, ms_upload_start, ms_plan, ms_run_issue, ms_download, ms_free;   /* host phases, in call order */
+    float ms_wall;                   /* the shard's thread, start to end */
+    float ms_dev_upload;             /* first to last byte of the H2D copy (host-buffer uploads; 0 for the .bed readers) */
+    float ms_dev_run, ms_dev_band, ms_dev_unpack;   /* run() on the device; its band / unpack kernel families */
+} nldsc_ld_shard_report;
+/* n = number of shards of that call; the first min(n, max) records are written to `out` (may be NULL). */
+int nldsc_ld_last_call_report(nldsc_ld_shard_report* out, int32_t max, int32_t* n);
+/* Releases the device memory cached between calls (the per-device workspace arena: packed rows, plane ring, ...)
+ * on `device`, or on every device when device < 0.  Blocks in use by a running call are left alone. */
+int nldsc_ld_arena_trim(int32_t device);
+
 /* ---- parity hooks (used by tests/ only; they run the same kernels as the session) -- */
 /* Unpack + count `n_snp` packed rows: planes_out = int8 [4][n_snp][npad] in plane order
  * g,m,h,a (npad returned), counts_out = int32 [n_snp][3] = n_het, n_hom2, n_missing. */
@@ -145,6 +166,12 @@ int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* l
  * tensor-pipe ceiling of this tile shape), 2 = TMA loads only (no MMAs: the operand-feed ceiling). */
 int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int32_t reps, float* ms_out,
                               char* err, size_t errlen);
+/* Measurement hook: the int8 tensor-pipe ceiling on this box.  Every CTA pair issues `iters` groups of `per_commit`
+ * back-to-back tcgen05.mma.cta_group::2.kind::i8 (M = 256, N = n_cols, K = 32) on operands resident in shared
+ * memory -- no loads, no epilogue.  ms_out = mean time of one launch, tops_out = int8 TOP/s it sustained
+ * ("the int8 peak must be measured on the box"). */
+int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t iters, int32_t reps, float* ms_out,
+                           double* tops_out, char* err, size_t errlen);
 /* Number of usable CUDA devices (0 and an error message when none). */
 int nldsc_ld_device_count(int32_t* count, char* err, size_t errlen);
 

@@ -23,7 +23,7 @@ EXPORTS = [
     "nldsc_ld_session_sync", "nldsc_ld_session_stats", "nldsc_ld_session_destroy",
     "nldsc_ld_debug_unpack", "nldsc_ld_debug_cross_counts", "nldsc_ld_device_count",
     "nldsc_ld_plan_windows", "nldsc_ld_plan_shards", "nldsc_ld_debug_band_probe", "nldsc_ld_debug_plan_windows_device",
-    "nldsc_ld_calculate_on",
+    "nldsc_ld_calculate_on", "nldsc_ld_debug_i8_peak", "nldsc_ld_last_call_report", "nldsc_ld_arena_trim",
 ]
 
 
@@ -46,6 +46,15 @@ class Stats(C.Structure):
                 ("npad", C.c_int32), ("band_impl", C.c_int32), ("ms_count", C.c_float),
                 ("ms_stats", C.c_float), ("ms_unpack", C.c_float), ("ms_band", C.c_float),
                 ("ms_finalize", C.c_float), ("ms_total", C.c_float)]
+
+
+class ShardReport(C.Structure):
+    _fields_ = [("device", C.c_int32), ("row_begin", C.c_int32), ("row_end", C.c_int32), ("load_begin", C.c_int32),
+                ("load_end", C.c_int32), ("chunks", C.c_int32), ("pairs", C.c_int64), ("bytes_h2d", C.c_int64),
+                ("ms_open", C.c_float), ("ms_upload_start", C.c_float), ("ms_plan", C.c_float),
+                ("ms_run_issue", C.c_float), ("ms_download", C.c_float), ("ms_free", C.c_float),
+                ("ms_wall", C.c_float), ("ms_dev_upload", C.c_float), ("ms_dev_run", C.c_float),
+                ("ms_dev_band", C.c_float), ("ms_dev_unpack", C.c_float)]
 
 
 _lib = None
@@ -283,3 +292,27 @@ def debug_band_probe(mode: int, n_org: int, n_tiles: int, reps: int = 5) -> dict
     npad = (n_org + 127) // 128 * 128
     ops = 2.0 * 256 * 192 * npad * n_tiles * (2 if mode >= 5 else 1)      # modes 5, 6: wide supertiles, two j-blocks each
     return {"ms": ms.value, "tops": ops / (ms.value * 1e-3) / 1e12, "gbs_operands": n_tiles * 2 * (40960 if mode >= 5 else 28672) * (npad // 128) / (ms.value * 1e-3) / 1e9}
+
+
+def debug_i8_peak(n_cols: int = 192, per_commit: int = 8, iters: int = 20000, reps: int = 3) -> dict:
+    """Back-to-back tcgen05 int8 MMAs (M=256, N=n_cols, K=32) from shared memory on every CTA pair: the tensor-pipe
+    ceiling of the box for the band kernel's instruction shape.  -> {ms, tops}"""
+    ms, tops = C.c_float(0), C.c_double(0)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_i8_peak(C.c_int32(n_cols), C.c_int32(per_commit), C.c_int32(iters), C.c_int32(reps),
+                                        C.byref(ms), C.byref(tops), err, C.c_size_t(512)), err)
+    return {"ms": ms.value, "tops": tops.value, "n_cols": n_cols, "per_commit": per_commit, "iters": iters}
+
+
+def last_call_report() -> list[dict]:
+    """Per-shard record of the last calculate* call made on this thread (nldsc_ld_last_call_report)."""
+    n = C.c_int32(0)
+    lib().nldsc_ld_last_call_report(None, C.c_int32(0), C.byref(n))
+    arr = (ShardReport * max(1, n.value))()
+    lib().nldsc_ld_last_call_report(arr, C.c_int32(n.value), C.byref(n))
+    return [{k: getattr(arr[i], k) for k, _ in ShardReport._fields_} for i in range(n.value)]
+
+
+def arena_trim(device: int = -1) -> None:
+    """Give the device memory cached between calls back to the driver (all devices when device < 0)."""
+    lib().nldsc_ld_arena_trim(C.c_int32(device))

@@ -25,6 +25,8 @@
 #include "epilogue.cuh"
 
 #include <cuda.h>
+#include <mutex>
+#include <string>
 
 namespace nldsc {
 
@@ -54,38 +56,60 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    uint32_t done = 0;
-    // bounded spin: a protocol bug must trap, not hang the GPU box
-    for (uint32_t spins = 0; !done; ++spins) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(addr), "r"(parity)
-            : "memory");
-        if (spins > (1u << 26)) __trap();
+// A protocol bug must end the kernel with a diagnostic, not hang the GPU box -- but a legitimately long wait (under
+// cuda-gdb, compute-sanitizer, an ncu replay or heavy co-tenancy) must not be mistaken for one: the bound is
+// ELAPSED TIME (%globaltimer, kHangNs), not a spin count.  Before trapping, the waiter leaves
+// (site << 24 | block) in a word of mapped host memory, which the host appends to its error message.
+constexpr unsigned long long kHangNs = 20ull * 1000000000ull;
+__device__ uint32_t* g_hang_word = nullptr;      // set per device by band_set_hang_word()
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __noinline__ void hang_trap(uint32_t site) {
+    if (g_hang_word != nullptr) {
+        *reinterpret_cast<volatile uint32_t*>(g_hang_word) = (site << 24) | (blockIdx.x & 0xFFFFFFu) | 0x800000u;
+        __threadfence_system();
     }
+    __trap();
+}
+__device__ __forceinline__ uint32_t mbar_try(uint32_t addr, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    return done;
+}
+// out of line, so that its clock and counters take no registers from the callers' hot loops
+__device__ __noinline__ void mbar_wait_slow(uint32_t addr, uint32_t parity, uint32_t site, uint32_t sleep_ns) {
+    const unsigned long long t0 = global_ns();
+    for (uint32_t spins = 0;; ++spins) {
+        if (mbar_try(addr, parity)) return;
+        if (sleep_ns) __nanosleep(sleep_ns);
+        if ((spins & 0x3FFu) == 0x3FFu && global_ns() - t0 > kHangNs) hang_trap(site);
+    }
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity, uint32_t site = 0) {
+    const uint32_t addr = smem_u32(bar);
+    for (uint32_t spins = 0; spins < (1u << 16); ++spins)
+        if (mbar_try(addr, parity)) return;
+    mbar_wait_slow(addr, parity, site, 0);
 }
 // The same wait for warps that have nothing else to do for a long time (the epilogue warps during a supertile's
 // K loop): sleep between polls, so that eight polling warps do not take issue slots from the one thread that
 // issues the MMAs and the one that issues the TMA loads.
-__device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity) {
+__device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity, uint32_t site = 0) {
     const uint32_t addr = smem_u32(bar);
-    uint32_t done = 0;
-    for (uint32_t spins = 0; !done; ++spins) {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(addr), "r"(parity)
-            : "memory");
-        if (!done) __nanosleep(256);
-        if (spins > (1u << 24)) __trap();
+    for (uint32_t spins = 0; spins < (1u << 14); ++spins) {
+        if (mbar_try(addr, parity)) return;
+        __nanosleep(256);
     }
+    mbar_wait_slow(addr, parity, site, 256);
 }
 // remote arrive on the leader (even) CTA's copy of `bar`
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
@@ -199,7 +223,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                 const int32_t a_row = tl.a_row[rank];
                 const int32_t b_row = tl.b_row + 32 * static_cast<int32_t>(rank);
                 for (int k = 0; k < args.k_steps; ++k) {
-                    mbar_wait(&empty[stage], phase ^ 1);
+                    mbar_wait(&empty[stage], phase ^ 1, 1);
                     if (args.probe == 1 || args.probe == 3) {   // no loads: operands are whatever the stage holds
                         if (rank == 0) mbar_expect_tx(&full[stage], 0);
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -225,11 +249,11 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             int n = 0;
             for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
                 const int buf = n & 1;
-                mbar_wait(&tempty[buf], ((n >> 1) & 1) ^ 1);       // both CTAs' epilogues drained this accumulator
+                mbar_wait(&tempty[buf], ((n >> 1) & 1) ^ 1, 2);       // both CTAs' epilogues drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * 256;
                 for (int k = 0; k < args.k_steps; ++k) {
-                    mbar_wait(&full[stage], phase);
+                    mbar_wait(&full[stage], phase, 3);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + stage * kStageBytes);
                     const uint64_t a_desc = make_smem_desc(sa);
@@ -257,7 +281,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             const Tile tl = args.tiles[t];
             const int32_t i0 = tl.i0[rank];
             const RowCtx row = load_row_ctx(args, i0 + s);
-            mbar_wait(&tfull[buf], (n >> 1) & 1);
+            mbar_wait(&tfull[buf], (n >> 1) & 1, 4);
             tc_fence_after();
             const uint32_t taddr = tmem_base + buf * 256 + (static_cast<uint32_t>(32 * q) << 16);
 #pragma unroll 1
@@ -397,7 +421,7 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 const int32_t b_row2 = tl.b_row2 + 32 * static_cast<int32_t>(rank);
                 const uint32_t bytes = 2u * (kABytes + (two ? 2 : 1) * kBBytes);          // both CTAs' bytes
                 for (int k = 0; k < args.k_steps; ++k) {
-                    mbar_wait(&empty[stage], phase ^ 1);
+                    mbar_wait(&empty[stage], phase ^ 1, 5);
                     if (args.probe == 1) {           // tensor-pipe probe: no loads, operands are whatever the stage holds
                         if (rank == 0) mbar_expect_tx(&full[stage], 0);
                         if (++stage == kWStages) { stage = 0; phase ^= 1; }
@@ -424,10 +448,10 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             int n = 0;
             for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
                 const bool two = args.tiles[t].b_row2 >= 0;
-                mbar_wait(tempty, (n & 1) ^ 1);                    // both CTAs' epilogues drained the accumulators
+                mbar_wait(tempty, (n & 1) ^ 1, 6);                    // both CTAs' epilogues drained the accumulators
                 tc_fence_after();
                 for (int k = 0; k < args.k_steps; ++k) {
-                    mbar_wait(&full[stage], phase);
+                    mbar_wait(&full[stage], phase, 7);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + stage * kWStageBytes);
                     const uint64_t a_desc = make_smem_desc(sa);
@@ -462,7 +486,7 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             const int32_t i0 = tl.i0[rank];
             const RowCtx row = load_row_ctx(args, i0 + s);
             const int n_j = tl.b_row2 >= 0 ? 2 : 1;
-            mbar_wait_idle(tfull, n & 1);
+            mbar_wait_idle(tfull, n & 1, 8);
             tc_fence_after();
 #pragma unroll 1
             for (int jj = 0; jj < n_j; ++jj) {
@@ -578,8 +602,46 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
 }
 void band_maps_destroy(BandMaps* m) { delete m; }
 
+// One word of mapped host memory per device for hang_trap()'s diagnostic; installed on first launch.
+namespace {
+uint32_t* g_hang_host[64] = {nullptr};
+std::mutex g_hang_mu;
+const char* const kSiteNames[] = {"?", "narrow/producer:empty", "narrow/mma:tmem-empty", "narrow/mma:full", "narrow/epilogue:tmem-full",
+                                  "wide/producer:empty", "wide/mma:tmem-empty", "wide/mma:full", "wide/epilogue:tmem-full", "i8-peak"};
+void install_hang_word() {
+    int dev = 0;
+    CUDA_CHECK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> g(g_hang_mu);
+    if (g_hang_host[dev & 63]) return;
+    uint32_t* h = nullptr;
+    CUDA_CHECK(cudaHostAlloc(reinterpret_cast<void**>(&h), sizeof(uint32_t), cudaHostAllocMapped | cudaHostAllocPortable));
+    *h = 0;
+    uint32_t* d = nullptr;
+    CUDA_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&d), h, 0));
+    CUDA_CHECK(cudaMemcpyToSymbol(g_hang_word, &d, sizeof(d)));
+    g_hang_host[dev & 63] = h;
+}
+}  // namespace
+
+std::string band_hang_note() {
+    std::lock_guard<std::mutex> g(g_hang_mu);
+    std::string note;
+    for (int d = 0; d < 64; ++d) {
+        if (!g_hang_host[d]) continue;
+        const uint32_t w = *reinterpret_cast<volatile uint32_t*>(g_hang_host[d]);
+        if (!w) continue;
+        char buf[160];
+        const uint32_t site = w >> 24;
+        snprintf(buf, sizeof(buf), " [band kernel on device %d gave up after 20 s at barrier %s, block %u]", d,
+                 site < sizeof(kSiteNames) / sizeof(kSiteNames[0]) ? kSiteNames[site] : "?", w & 0x7FFFFFu);
+        note += buf;
+    }
+    return note;
+}
+
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
     if (args.n_tiles <= 0) return;
+    install_hang_word();
     // per device (several GPUs may be driven from one process), so not cached in a static
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     const int pairs = args.n_tiles < sm_count / 2 ? args.n_tiles : sm_count / 2;     // one CTA pair per TPC
@@ -589,9 +651,82 @@ void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cu
 
 void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
     if (args.n_tiles <= 0) return;
+    install_hang_word();
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
     const int pairs = args.n_tiles < sm_count / 2 ? args.n_tiles : sm_count / 2;
     band_tc_wide_kernel<<<2 * pairs, kWThreads, kWSmemBytes, st>>>(maps->a, maps->b, args);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+// ---- int8 tensor-pipe ceiling (measurement only) ------------------------------------------------
+// Back-to-back tcgen05.mma.cta_group::2.kind::i8 (M = 256, N = n_cols, K = 32) from shared memory on every CTA
+// pair: no TMA, no epilogue, operands resident.  What the tensor pipe sustains on this instruction shape at the
+// clocks the box runs it at -- the denominator SURVEY section 8(d) asks to be MEASURED, not derived from bf16.
+// Operands are filled with genotype-like bytes (0/1/2 left, 0/1 right) so that the datapath toggles as it does on
+// real planes.  `per_commit` MMAs are issued per tcgen05.commit (the wide band kernel issues 8, the narrow one 4),
+// alternating between two accumulators; at most 4 commits are in flight.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+i8_peak_kernel(int iters, int n_cols, int per_commit) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    constexpr int kDepth = 4;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 2 * kABytes);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + kDepth);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    // A: 128 rows x 128 B, B: up to 128 rows x 128 B (n_cols / 2 used)
+    for (int i = threadIdx.x; i < 2 * kABytes / 4; i += blockDim.x) {
+        uint32_t h = (i * 2654435761u) ^ (blockIdx.x * 40503u);
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        const uint32_t m = i < kABytes / 4 ? 0x03030303u : 0x01010101u;
+        uint32_t v = h & m;
+        if (i < kABytes / 4) v -= (v >> 1) & v & 0x01010101u;          // 3 -> 2: dosages 0/1/2
+        reinterpret_cast<uint32_t*>(smem)[i] = v;
+    }
+    if (warp == 0 && lane == 0) {
+        for (int d = 0; d < kDepth; ++d) mbar_init(&bar[d], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy fills visible to the MMA's async proxy
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (warp == 1 && lane == 0 && rank == 0) {
+        const uint32_t idesc = (2u << 4) | ((static_cast<uint32_t>(n_cols) >> 3) << 17) | (((2 * kARows) >> 4) << 24);
+        const uint64_t a_desc = make_smem_desc(smem_u32(smem));
+        const uint64_t b_desc = make_smem_desc(smem_u32(smem) + kABytes);
+        for (int it = 0; it < iters; ++it) {
+            const int d = it % kDepth;
+            if (it >= kDepth) mbar_wait(&bar[d], ((it / kDepth) - 1) & 1, 9);
+            tc_fence_after();
+            for (int m = 0; m < per_commit; ++m)
+                tc_mma_i8(tmem_base + ((m >> 2) & 1) * 256, a_desc + 2 * (m & 3), b_desc + 2 * (m & 3), idesc, 1u);
+            tc_commit_pair(&bar[d]);
+        }
+        for (int it = iters > kDepth ? iters - kDepth : 0; it < iters; ++it) mbar_wait(&bar[it % kDepth], (it / kDepth) & 1, 9);
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                     : "memory");
+    }
+}
+
+void launch_i8_peak(int iters, int n_cols, int per_commit, int sm_count, cudaStream_t st) {
+    const int smem = 2 * kABytes + 1024 + 256;
+    CUDA_CHECK(cudaFuncSetAttribute(i8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    i8_peak_kernel<<<(sm_count / 2) * 2, 128, smem, st>>>(iters, n_cols, per_commit);
     CUDA_CHECK(cudaGetLastError());
 }
 

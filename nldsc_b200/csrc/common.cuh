@@ -84,11 +84,13 @@ struct CudaError : std::runtime_error {
     using std::runtime_error::runtime_error;
 };
 
+std::string band_hang_note();   // band_tc.cu: which barrier a band kernel gave up on, if one did ("" otherwise)
+
 inline void cuda_check(cudaError_t e, const char* what, const char* file, int line) {
     if (e != cudaSuccess) {
         char buf[512];
         snprintf(buf, sizeof(buf), "CUDA error %s at %s:%d: %s", what, file, line, cudaGetErrorString(e));
-        throw CudaError(buf);
+        throw CudaError(std::string(buf) + band_hang_note());
     }
 }
 #define CUDA_CHECK(x) ::nldsc::cuda_check((x), #x, __FILE__, __LINE__)
@@ -113,6 +115,7 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
 void band_maps_destroy(BandMaps*);
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);
 void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);   // tiles carry b_row2
+void launch_i8_peak(int iters, int n_cols, int per_commit, int sm_count, cudaStream_t st);   // measurement only
 void launch_band_simt(const int8_t* planes, int64_t plane_stride, int32_t npad,
                       const BandArgs& args, cudaStream_t st);
 

@@ -94,9 +94,32 @@ void* Arena::alloc(size_t bytes) {
     // small requests share 64 MB blocks; large ones (packed rows, plane ring) get their own
     const size_t sz = std::max<size_t>(bytes, size_t(64) << 20);
     void* p = nullptr;
-    CUDA_CHECK(cudaMalloc(&p, sz));
+    cudaError_t e = cudaMalloc(&p, sz);
+    if (e == cudaErrorMemoryAllocation) {
+        // cached blocks of an earlier, differently shaped call that nothing of this session lives in are only
+        // holding memory: give them back and try once more
+        cudaGetLastError();
+        bool freed = false;
+        for (size_t i = 0; i < blocks.size();) {
+            if (blocks[i].used == 0) {
+                cudaFree(blocks[i].base);
+                blocks.erase(blocks.begin() + static_cast<long>(i));
+                freed = true;
+            } else {
+                ++i;
+            }
+        }
+        if (freed) e = cudaMalloc(&p, sz);
+    }
+    CUDA_CHECK(e);
     blocks.push_back(Block{static_cast<char*>(p), sz, bytes});
     return p;
+}
+
+size_t Arena::largest_free() const {
+    size_t m = 0;
+    for (const Block& b : blocks) m = std::max(m, b.size - b.used);
+    return m;
 }
 
 size_t Arena::capacity() const {
@@ -740,13 +763,16 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
 
     // ---- plane ring: as many SNP rows as needed, within the memory budget (4 int8 planes each)
     const size_t row_bytes = static_cast<size_t>(kPlanes) * s->npad;
-    size_t reusable = 0;      // blocks cached from an earlier call are reusable, so they count as free
-    for (const Arena::Block& b : s->arena->blocks) reusable += b.size - b.used;
+    // A block cached from an earlier call is reusable -- but the ring is ONE allocation, so only the largest free
+    // block counts; when that does not hold the shard, budget from what the device has free (blocks this session
+    // does not use are released by Arena::alloc before it gives up).
+    const size_t reusable = s->arena->largest_free();
     size_t budget = reusable;
     if (static_cast<size_t>(n_load_pad) * row_bytes > reusable || getenv("NLDSC_PLANE_BYTES")) {
-        size_t free_b = 0, total_b = 0;
+        size_t free_b = 0, total_b = 0, idle = 0;
         CUDA_CHECK(cudaMemGetInfo(&free_b, &total_b));
-        budget = static_cast<size_t>(0.85 * static_cast<double>(free_b + reusable));
+        for (const Arena::Block& b : s->arena->blocks) if (b.used == 0) idle += b.size;
+        budget = std::max(reusable, static_cast<size_t>(0.85 * static_cast<double>(free_b + idle)));
         budget = std::min(budget, env_size("NLDSC_PLANE_BYTES", budget));
     }
     // Measured: past ~30 GB of planes the band kernel slows down (N = 315,599: 37 -> 50 ms per 40,000 SNPs; the
@@ -1145,7 +1171,11 @@ struct ShardJob {
     int32_t row_begin, row_end;
     int rc = NLDSC_OK;
     std::string msg;
+    nldsc_ld_shard_report rep{};
 };
+
+// what the last calculate* call made on this thread did, shard by shard (nldsc_ld_last_call_report)
+thread_local std::vector<nldsc_ld_shard_report> tl_report;
 
 // placement chosen by the caller of nldsc_ld_calculate_on for the calls made on this thread
 thread_local int tl_first_device = -1;
@@ -1214,7 +1244,13 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
         throw InvalidArgument("result arrays must all be non-null");
     const int ndev = usable_devices();
     const int dev0 = first_device_from_env();
-    int parts = gpus_from_env(std::max(1, ndev - dev0));
+    const int ndev_use = gpus_from_env(std::max(1, ndev - dev0));
+    int parts = ndev_use;
+    // Test hook (NLDSC_TEST_SHARDS=k): cut k shards whatever the number of GPUs and deal them round-robin to the
+    // devices in use, so that a ONE-GPU box still runs the thread-per-shard / halo / gather code of the multi-GPU
+    // path (several sessions then share a device: private arenas and staging buffers, pooled streams).
+    const int test_shards = static_cast<int>(env_size("NLDSC_TEST_SHARDS", 0));
+    if (test_shards > 0) parts = test_shards;
     parts = std::max(1, std::min<int>(parts, (p->n_snp + kBlk - 1) / kBlk));
     tr.lap("validate+devices");
 
@@ -1249,14 +1285,26 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
             sub.l2d_wse += j.row_begin;
             session_download(s, &sub, nullptr);
             t5 = now();
-            if (trace) {
+            {
+                // everything has completed: reading the event times costs microseconds
                 nldsc_ld_stats st;
                 nldsc_ld_session_stats(s, &st);
                 float up = 0, gap = 0, lag = 0;
-                cudaEventElapsedTime(&up, s->ev_up0, s->ev_up1);       // memory uploads only (the .bed reader records none)
-                cudaEventElapsedTime(&gap, s->ev_up0, s->ev_run0);
-                cudaEventElapsedTime(&lag, s->ev_up1, s->ev_run1);
-                fprintf(stderr, "[nldsc_ld]   device: upload %.2f ms, run %.2f ms (band %.2f unpack %.2f count %.2f stats %.2f "
+                if (s->readers.empty()) {                              // memory uploads only (the .bed readers record none)
+                    cudaEventElapsedTime(&up, s->ev_up0, s->ev_up1);
+                    cudaEventElapsedTime(&gap, s->ev_up0, s->ev_run0);
+                    cudaEventElapsedTime(&lag, s->ev_up1, s->ev_run1);
+                }
+                j.rep.load_begin = s->load_begin;
+                j.rep.load_end = s->load_end;
+                j.rep.chunks = st.chunks;
+                j.rep.pairs = st.pairs;
+                j.rep.bytes_h2d = static_cast<int64_t>(s->n_load) * s->bps;
+                j.rep.ms_dev_upload = up;
+                j.rep.ms_dev_run = st.ms_total;
+                j.rep.ms_dev_band = st.ms_band;
+                j.rep.ms_dev_unpack = st.ms_unpack;
+                if (trace) fprintf(stderr, "[nldsc_ld]   device: upload %.2f ms, run %.2f ms (band %.2f unpack %.2f count %.2f stats %.2f "
                                 "finalize %.2f), run starts %.2f after upload start, ends %.2f after upload end, %d chunks\n",
                         up, st.ms_total, st.ms_band, st.ms_unpack, st.ms_count, st.ms_stats, st.ms_finalize, gap, lag, st.chunks);
             }
@@ -1266,6 +1314,16 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
             j.rc = NLDSC_ERR_RUNTIME; j.msg = e.what();
         }
         session_free(s);
+        j.rep.device = j.device;
+        j.rep.row_begin = j.row_begin;
+        j.rep.row_end = j.row_end;
+        j.rep.ms_open = static_cast<float>(ms(t0, t1));
+        j.rep.ms_upload_start = static_cast<float>(ms(t1, t2));
+        j.rep.ms_plan = static_cast<float>(ms(t2, t3));
+        j.rep.ms_run_issue = static_cast<float>(ms(t3, t4));
+        j.rep.ms_download = static_cast<float>(ms(t4, t5));
+        j.rep.ms_free = static_cast<float>(ms(t5, now()));
+        j.rep.ms_wall = static_cast<float>(ms(t0, now()));
         if (trace)
             fprintf(stderr, "[nldsc_ld] gpu %d rows [%d,%d): open %.2f ms, upload-start %.2f, windows+plan %.2f, run-issue %.2f, "
                             "download+sync %.2f, free %.2f\n",
@@ -1289,7 +1347,7 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
         tr.lap("windows (device)");
         const std::vector<int32_t> cut = split_rows(lo, hi, parts);
         for (int k = 0; k < parts; ++k)
-            if (cut[k + 1] > cut[k]) jobs.push_back({dev0 + k, cut[k], cut[k + 1]});
+            if (cut[k + 1] > cut[k]) jobs.push_back({dev0 + k % ndev_use, cut[k], cut[k + 1]});
     }
     if (jobs.size() == 1) {
         work(jobs[0]);
@@ -1298,6 +1356,8 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
         for (auto& j : jobs) th.emplace_back(work, std::ref(j));
         for (auto& t : th) t.join();
     }
+    tl_report.clear();
+    for (auto& j : jobs) tl_report.push_back(j.rep);
     for (auto& j : jobs) {
         if (j.rc == NLDSC_ERR_INVALID) throw InvalidArgument(j.msg);
         if (j.rc != NLDSC_OK) throw CudaError(j.msg);
@@ -1507,6 +1567,18 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* o) {
 
 void nldsc_ld_session_destroy(nldsc_ld_session* s) { session_free(s); }
 
+int nldsc_ld_last_call_report(nldsc_ld_shard_report* out, int32_t max, int32_t* n) {
+    if (!n) return NLDSC_ERR_INVALID;
+    *n = static_cast<int32_t>(tl_report.size());
+    for (int32_t k = 0; out && k < max && k < *n; ++k) out[k] = tl_report[k];
+    return NLDSC_OK;
+}
+
+int nldsc_ld_arena_trim(int32_t device) {
+    arena_trim(device);
+    return NLDSC_OK;
+}
+
 // ---- parity hooks ----------------------------------------------------------------------------
 
 int nldsc_ld_debug_unpack(const uint8_t* packed, int32_t n_snp, int32_t n_org, int8_t* planes_out, int32_t* counts_out,
@@ -1708,6 +1780,36 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
         *ms_out = ms / reps;
+    });
+}
+
+int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t iters, int32_t reps, float* ms_out, double* tops_out,
+                           char* err, size_t errlen) {
+    return guarded(err, errlen, [&] {
+        if (n_cols < 16 || n_cols > 256 || (n_cols % 16) != 0 || per_commit < 1 || per_commit > 8 || iters < 1 || reps < 1 ||
+            !ms_out)
+            throw InvalidArgument("bad arguments");
+        usable_devices();
+        const int dev = first_device_from_env();
+        CUDA_CHECK(cudaSetDevice(dev));
+        require_sm100(dev);
+        const int sms = device_sm_count(dev);
+        cudaEvent_t e0, e1;
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        launch_i8_peak(iters, n_cols, per_commit, sms, nullptr);                         // warm-up
+        CUDA_CHECK(cudaEventRecord(e0, nullptr));
+        for (int r = 0; r < reps; ++r) launch_i8_peak(iters, n_cols, per_commit, sms, nullptr);
+        CUDA_CHECK(cudaEventRecord(e1, nullptr));
+        CUDA_CHECK(cudaEventSynchronize(e1));
+        float ms = 0;
+        CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        *ms_out = ms / reps;
+        // int8 ops of one launch: CTA pairs x commits x MMAs x (2 x 256 x n_cols x 32)
+        if (tops_out)
+            *tops_out = static_cast<double>(sms / 2) * iters * per_commit * 2.0 * 256.0 * n_cols * 32.0 / (*ms_out * 1e-3) / 1e12;
     });
 }
 

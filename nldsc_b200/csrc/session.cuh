@@ -43,6 +43,7 @@ struct Arena {
     std::vector<Block> blocks;
     void* alloc(size_t bytes);    // 512-byte aligned; grows by cudaMalloc when no block has room
     size_t capacity() const;
+    size_t largest_free() const;  // the most one further allocation can take without a cudaMalloc
 };
 Arena* arena_acquire(int device);     // the device's cached arena, or a private one if that is in use
 void arena_release(Arena* a);         // resets the bump pointers; private arenas free their blocks

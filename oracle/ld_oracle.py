@@ -142,3 +142,30 @@ def cross_counts(codes_i: np.ndarray, codes_j: np.ndarray) -> np.ndarray:
         for b, right in enumerate(planes_j):
             out[a, b] = left @ right.astype(np.int64).T
     return out
+
+
+def ld_scores_rows(packed: np.ndarray, n_org: int, positions: np.ndarray, ld_wind: float, maf_thr: float,
+                   std_thr: float, rsq_thr: float, rows, max_span: int = 4096) -> dict:
+    """ld_scores() for a few rows of a bfile too large to score whole: every requested row is scored on the
+    sub-bfile that holds its complete window (rows whose windows overlap share one sub-bfile, up to `max_span`
+    SNPs), which is all calculate() ever looks at for that row (stream.h:142-155, ldscalc.h:34-47).
+    Returns the seven result arrays restricted to `rows` (same order), plus "rows"."""
+    positions = np.asarray(positions, dtype=np.float64)
+    rows = np.asarray(sorted(int(r) for r in rows), dtype=np.int64)
+    lo = np.searchsorted(positions, positions[rows] - ld_wind, side="left")
+    hi = np.searchsorted(positions, positions[rows] + ld_wind, side="right")      # exclusive
+    keys = ("l2", "l2d", "maf", "residuals_std", "l2_ws", "l2d_ws", "l2d_wse", "keep")
+    out = {k: [] for k in keys}
+    k = 0
+    while k < len(rows):
+        a, b, e = int(lo[k]), int(hi[k]), k + 1
+        while e < len(rows) and max(b, int(hi[e])) - a <= max_span:
+            b = max(b, int(hi[e]))
+            e += 1
+        sub = ld_scores(packed[a:b], n_org, positions[a:b], ld_wind, maf_thr, std_thr, rsq_thr, rows=rows[k:e] - a)
+        for key in keys:
+            out[key].append(sub[key][rows[k:e] - a])
+        k = e
+    res = {key: np.concatenate(v) for key, v in out.items()}
+    res["rows"] = rows
+    return res

@@ -2,7 +2,9 @@
 
 Every case draws organisms, SNPs, missingness, map density and window at random, then runs the C-ABI path
 under one randomly chosen execution variant (tiny chunks, a plane ring barely wider than a window, one
-stream, one band stream, SIMT band kernel, the narrow tcgen05 kernel, 2 shards when the box has 2 GPUs).  All variants must meet the
+stream, one band stream, SIMT band kernel, the narrow tcgen05 kernel, 2 or 3 shards -- one per GPU when the box has
+as many, otherwise through the NLDSC_TEST_SHARDS hook, which runs the same thread-per-shard / halo / gather code with the
+shards dealt round-robin to the GPUs there are).  All variants must meet the
 parity bar against the oracle, and be bitwise equal to the default variant of the same case."""
 import os
 
@@ -26,7 +28,18 @@ VARIANTS = [
     {"NLDSC_WIDE": "0"},
     {"NLDSC_WIDE": "0", "NLDSC_CHUNK_ROWS": "128", "NLDSC_PLANE_BYTES": "ring"},
     {"NLDSC_CHUNK_ROWS": "128", "NLDSC_PLANE_BYTES": "ring", "NLDSC_GPUS": "2"},
+    {"NLDSC_TEST_SHARDS": "3"},
 ]
+
+
+def _shards_for_this_box(variant):
+    """NLDSC_GPUS=k needs k devices; on a smaller box the same k-shard cut runs through NLDSC_TEST_SHARDS
+    (threads, halos and the gather are the same code; only the device every shard lands on differs)."""
+    k = variant.get("NLDSC_GPUS")
+    if k is not None and capi.device_count() < int(k):
+        variant.pop("NLDSC_GPUS")
+        variant["NLDSC_TEST_SHARDS"] = k
+    return variant
 
 
 @pytest.fixture(scope="module", autouse=True)
@@ -63,8 +76,7 @@ def test_random_case_matches_oracle(seed, monkeypatch):
         span = int(np.max(hi - lo)) + 1
         rows = (span // 64 + 6) * 64                               # a block pair's columns, and little more
         variant["NLDSC_PLANE_BYTES"] = str(rows * 4 * ((n_org + 127) // 128 * 128))
-    if variant.get("NLDSC_GPUS") == "2" and capi.device_count() < 2:
-        variant.pop("NLDSC_GPUS")
+    variant = _shards_for_this_box(variant)
     for k, v in variant.items():
         monkeypatch.setenv(k, v)
     got = capi.calculate_packed(packed, *args)
@@ -83,6 +95,7 @@ MID_VARIANTS = [
     {"NLDSC_GPUS": "2"},
     {"NLDSC_BAND_STREAMS": "1", "NLDSC_WIDE_OVERLAP": "0"},
     {"NLDSC_FIRST_BYTES": "1000000", "NLDSC_CHUNK_BYTES": "3000000"},
+    {"NLDSC_TEST_SHARDS": "4", "NLDSC_CHUNK_ROWS": "1024"},
 ]
 
 
@@ -120,8 +133,7 @@ def test_midsize_case_variants_bitwise(seed, monkeypatch):
             lo, hi = capi.plan_windows(cm, wind)
             rows_ring = ((int(np.max(hi - lo)) + 1) // 64 + 6) * 64 + 2048
             variant["NLDSC_PLANE_BYTES"] = str(rows_ring * 4 * ((n_org + 127) // 128 * 128))
-        if variant.get("NLDSC_GPUS") == "2" and capi.device_count() < 2:
-            variant.pop("NLDSC_GPUS")
+        variant = _shards_for_this_box(variant)
         with monkeypatch.context() as mp:
             for k, v in variant.items():
                 mp.setenv(k, v)

@@ -181,15 +181,29 @@ def test_sharded_equals_single_bitwise():
         assert np.array_equal(base[key][1000:1777], part[key], equal_nan=True), key
 
 
-def test_multi_gpu_env_matches_single(monkeypatch):
-    if capi.device_count() < 2:
-        pytest.skip("one GPU")
+@pytest.mark.parametrize("shards", [2, 3, 5])
+def test_run_sharded_matches_single(shards, monkeypatch, tmp_path):
+    """run_sharded (session.cu): one host thread per shard, halo reads, host-side gather -- bitwise equal to the
+    one-shard call, from a host buffer and from a .bed.  One shard per GPU when the box has `shards` GPUs
+    (NLDSC_GPUS); otherwise the NLDSC_TEST_SHARDS hook deals the same shards round-robin to the GPUs there are, so
+    this never skips."""
     g = _case(900, 3000, 0.02, seed=8)
     base = _run(g)
-    monkeypatch.setenv("NLDSC_GPUS", "2")
-    two = _run(g)
+    with open(tmp_path / "s.bed", "wb") as f:
+        f.write(synth.BED_MAGIC)
+        f.write(g["packed"].tobytes())
+    if capi.device_count() >= shards:
+        monkeypatch.setenv("NLDSC_GPUS", str(shards))
+    else:
+        monkeypatch.setenv("NLDSC_TEST_SHARDS", str(shards))
+    sharded = _run(g)
+    from_file = capi.calculate(str(tmp_path / "s.bed"), 3000, g["n_org"], g["positions"], g["ld_wind"], g["maf"],
+                               g["std_thr"], g["rsq_thr"])
     for key in RESULT_KEYS:
-        assert np.array_equal(base[key], two[key], equal_nan=True), key
+        assert np.array_equal(base[key], sharded[key], equal_nan=True), key
+        assert np.array_equal(base[key], from_file[key], equal_nan=True), key
+    cuts = capi.plan_shards(g["positions"], g["ld_wind"], shards)
+    assert len(set(cuts.tolist())) == shards + 1                 # every shard owns rows: the cut really is `shards` wide
 
 
 def test_degenerate_snps():

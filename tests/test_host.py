@@ -21,7 +21,7 @@ def built():
 
 def test_library_exports_every_declared_symbol():
     hdr = open(os.path.join(ROOT, "include", "nldsc_ld.h")).read()
-    declared = set(re.findall(r"\b(nldsc_ld_[a-z_]+)\s*\(", hdr))
+    declared = set(re.findall(r"\b(nldsc_ld_[a-z0-9_]+)\s*\(", hdr))
     declared -= {"nldsc_ld_params", "nldsc_ld_result", "nldsc_ld_stats", "nldsc_ld_session"}
     assert len(declared) >= 12
     L = capi.lib()
