@@ -57,7 +57,9 @@ typedef struct nldsc_ld_result {
  * (magic 6c 1b 01 and, unlike the reference, the exact size 3 + n_snp*ceil(n_org/4)),
  * streams it to the GPU(s) and fills `out` (arrays of length n_snp).
  * GPUs: environment NLDSC_GPUS (default 1) contiguous SNP shards with a window
- * halo, one host thread per GPU, no collective; results gathered host-side. */
+ * halo, one host thread per GPU, no collective; results gathered host-side.
+ * Reading: NLDSC_READERS pread threads per shard (default 4) through the page cache, or past it with
+ * NLDSC_ODIRECT=1 (O_DIRECT, 4 KB-aligned supersets of every piece) for genomes larger than host memory. */
 int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char* err, size_t errlen);
 
 /* nldsc_ld_calculate with the GPUs named by the caller instead of the environment: shards go to devices
@@ -72,6 +74,17 @@ int nldsc_ld_calculate_on(const nldsc_ld_params* params, nldsc_ld_result* out, i
  * BedStreamReader::read consumes, stream.h:43-69). */
 int nldsc_ld_calculate_packed(const uint8_t* packed, const nldsc_ld_params* params,
                               nldsc_ld_result* out, char* err, size_t errlen);
+
+/* nldsc_ld_calculate_packed with the GPUs named by the caller (thread-safe placement, like nldsc_ld_calculate_on):
+ * several host threads can each score a chromosome that is already in host memory, one GPU (group) each. */
+int nldsc_ld_calculate_packed_on(const uint8_t* packed, const nldsc_ld_params* params, nldsc_ld_result* out,
+                                 int32_t first_device, int32_t n_devices, char* err, size_t errlen);
+
+/* Prepares devices first_device .. first_device + n_devices - 1 for the calls above, every device on its own host
+ * thread: CUDA context, pinned staging buffers, stream pool, kernel images.  Optional -- the first call on a device
+ * does the same -- but a driver that is about to keep 8 GPUs busy pays these 0.3-1 s per device once and in parallel
+ * instead of inside the first chromosome of every GPU. */
+int nldsc_ld_warmup(int32_t first_device, int32_t n_devices, char* err, size_t errlen);
 
 /* ---- host-side planning (no GPU needed) --------------------------------------------------- */
 /* Inclusive window [lo[i], hi[i]] of every SNP: {j : |pos_j - pos_i| <= ld_wind}, the
@@ -166,12 +179,12 @@ int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* l
  * tensor-pipe ceiling of this tile shape), 2 = TMA loads only (no MMAs: the operand-feed ceiling). */
 int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int32_t reps, float* ms_out,
                               char* err, size_t errlen);
-/* Measurement hook: the int8 tensor-pipe ceiling on this box.  Every CTA pair issues `iters` groups of `per_commit`
- * back-to-back tcgen05.mma.cta_group::2.kind::i8 (M = 256, N = n_cols, K = 32) on operands resident in shared
+/* Measurement hook: the int8 tensor-pipe ceiling on this box.  Every CTA pair issues `iters` groups of `per_commit` (4, 8 or 16; at
+ * most `depth` <= 8 groups in flight) back-to-back tcgen05.mma.cta_group::2.kind::i8 (M = 256, N = n_cols, K = 32) on operands resident in shared
  * memory -- no loads, no epilogue.  ms_out = mean time of one launch, tops_out = int8 TOP/s it sustained
  * ("the int8 peak must be measured on the box"). */
-int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t iters, int32_t reps, float* ms_out,
-                           double* tops_out, char* err, size_t errlen);
+int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t depth, int32_t iters, int32_t reps,
+                           float* ms_out, double* tops_out, char* err, size_t errlen);
 /* Number of usable CUDA devices (0 and an error message when none). */
 int nldsc_ld_device_count(int32_t* count, char* err, size_t errlen);
 

@@ -24,6 +24,7 @@ EXPORTS = [
     "nldsc_ld_debug_unpack", "nldsc_ld_debug_cross_counts", "nldsc_ld_device_count",
     "nldsc_ld_plan_windows", "nldsc_ld_plan_shards", "nldsc_ld_debug_band_probe", "nldsc_ld_debug_plan_windows_device",
     "nldsc_ld_calculate_on", "nldsc_ld_debug_i8_peak", "nldsc_ld_last_call_report", "nldsc_ld_arena_trim",
+    "nldsc_ld_calculate_packed_on", "nldsc_ld_warmup",
 ]
 
 
@@ -188,6 +189,24 @@ def calculate_packed(packed, n_snp, n_org, positions, ld_wind, maf, std_thr, rsq
     return out
 
 
+def calculate_packed_on(packed, n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr, first_device, n_devices=1,
+                        out=None) -> dict:
+    """nldsc_ld_calculate_packed on GPUs first_device .. first_device + n_devices - 1 (thread-safe placement)."""
+    p = make_params(n_snp, n_org, positions, ld_wind, maf, std_thr, rsq_thr)
+    out, r = alloc_result(n_snp) if out is None else out
+    err = C.create_string_buffer(512)
+    ptr = C.c_void_p(_host_ptr(packed))
+    _raise(lib().nldsc_ld_calculate_packed_on(ptr, C.byref(p), C.byref(r), C.c_int32(first_device), C.c_int32(n_devices),
+                                              err, C.c_size_t(512)), err)
+    return out
+
+
+def warmup(first_device: int = 0, n_devices: int = 1) -> None:
+    """Contexts, pinned staging, stream pools and kernel images of the devices, prepared in parallel."""
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_warmup(C.c_int32(first_device), C.c_int32(n_devices), err, C.c_size_t(512)), err)
+
+
 class Session:
     """One shard on one GPU, device-resident between calls (nldsc_ld_session_*)."""
 
@@ -294,14 +313,14 @@ def debug_band_probe(mode: int, n_org: int, n_tiles: int, reps: int = 5) -> dict
     return {"ms": ms.value, "tops": ops / (ms.value * 1e-3) / 1e12, "gbs_operands": n_tiles * 2 * (40960 if mode >= 5 else 28672) * (npad // 128) / (ms.value * 1e-3) / 1e9}
 
 
-def debug_i8_peak(n_cols: int = 192, per_commit: int = 8, iters: int = 20000, reps: int = 3) -> dict:
+def debug_i8_peak(n_cols: int = 192, per_commit: int = 8, iters: int = 20000, reps: int = 3, depth: int = 4) -> dict:
     """Back-to-back tcgen05 int8 MMAs (M=256, N=n_cols, K=32) from shared memory on every CTA pair: the tensor-pipe
     ceiling of the box for the band kernel's instruction shape.  -> {ms, tops}"""
     ms, tops = C.c_float(0), C.c_double(0)
     err = C.create_string_buffer(512)
-    _raise(lib().nldsc_ld_debug_i8_peak(C.c_int32(n_cols), C.c_int32(per_commit), C.c_int32(iters), C.c_int32(reps),
+    _raise(lib().nldsc_ld_debug_i8_peak(C.c_int32(n_cols), C.c_int32(per_commit), C.c_int32(depth), C.c_int32(iters), C.c_int32(reps),
                                         C.byref(ms), C.byref(tops), err, C.c_size_t(512)), err)
-    return {"ms": ms.value, "tops": tops.value, "n_cols": n_cols, "per_commit": per_commit, "iters": iters}
+    return {"ms": ms.value, "tops": tops.value, "n_cols": n_cols, "per_commit": per_commit, "depth": depth, "iters": iters}
 
 
 def last_call_report() -> list[dict]:

@@ -639,6 +639,12 @@ std::string band_hang_note() {
     return note;
 }
 
+void install_band_kernels() {
+    install_hang_word();
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
+}
+
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
     if (args.n_tiles <= 0) return;
     install_hang_word();
@@ -665,13 +671,14 @@ void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_coun
 // Operands are filled with genotype-like bytes (0/1/2 left, 0/1 right) so that the datapath toggles as it does on
 // real planes.  `per_commit` MMAs are issued per tcgen05.commit (the wide band kernel issues 8, the narrow one 4),
 // alternating between two accumulators; at most 4 commits are in flight.
+template <int kPerCommit>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
-i8_peak_kernel(int iters, int n_cols, int per_commit) {
+i8_peak_kernel(int iters, int n_cols, int depth) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    constexpr int kDepth = 4;
+    constexpr int kMaxDepth = 8;
     uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 2 * kABytes);
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + kDepth);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + kMaxDepth);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
     // A: 128 rows x 128 B, B: up to 128 rows x 128 B (n_cols / 2 used)
@@ -684,7 +691,7 @@ i8_peak_kernel(int iters, int n_cols, int per_commit) {
         reinterpret_cast<uint32_t*>(smem)[i] = v;
     }
     if (warp == 0 && lane == 0) {
-        for (int d = 0; d < kDepth; ++d) mbar_init(&bar[d], 1);
+        for (int d = 0; d < kMaxDepth; ++d) mbar_init(&bar[d], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -704,14 +711,15 @@ i8_peak_kernel(int iters, int n_cols, int per_commit) {
         const uint64_t a_desc = make_smem_desc(smem_u32(smem));
         const uint64_t b_desc = make_smem_desc(smem_u32(smem) + kABytes);
         for (int it = 0; it < iters; ++it) {
-            const int d = it % kDepth;
-            if (it >= kDepth) mbar_wait(&bar[d], ((it / kDepth) - 1) & 1, 9);
+            const int d = it % depth;
+            if (it >= depth) mbar_wait(&bar[d], ((it / depth) - 1) & 1, 9);
             tc_fence_after();
-            for (int m = 0; m < per_commit; ++m)
+#pragma unroll
+            for (int m = 0; m < kPerCommit; ++m)       // 4 K-slices into accumulator 0, then 4 into accumulator 1, ...
                 tc_mma_i8(tmem_base + ((m >> 2) & 1) * 256, a_desc + 2 * (m & 3), b_desc + 2 * (m & 3), idesc, 1u);
             tc_commit_pair(&bar[d]);
         }
-        for (int it = iters > kDepth ? iters - kDepth : 0; it < iters; ++it) mbar_wait(&bar[it % kDepth], (it / kDepth) & 1, 9);
+        for (int it = iters > depth ? iters - depth : 0; it < iters; ++it) mbar_wait(&bar[it % depth], (it / depth) & 1, 9);
     }
     tc_fence_before();
     __syncthreads();
@@ -723,11 +731,17 @@ i8_peak_kernel(int iters, int n_cols, int per_commit) {
     }
 }
 
-void launch_i8_peak(int iters, int n_cols, int per_commit, int sm_count, cudaStream_t st) {
+void launch_i8_peak(int iters, int n_cols, int per_commit, int depth, int sm_count, cudaStream_t st) {
     const int smem = 2 * kABytes + 1024 + 256;
-    CUDA_CHECK(cudaFuncSetAttribute(i8_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    i8_peak_kernel<<<(sm_count / 2) * 2, 128, smem, st>>>(iters, n_cols, per_commit);
-    CUDA_CHECK(cudaGetLastError());
+    auto go = [&](auto kernel) {
+        CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        kernel<<<(sm_count / 2) * 2, 128, smem, st>>>(iters, n_cols, depth);
+        CUDA_CHECK(cudaGetLastError());
+    };
+    if (per_commit == 4) go(i8_peak_kernel<4>);
+    else if (per_commit == 8) go(i8_peak_kernel<8>);
+    else if (per_commit == 16) go(i8_peak_kernel<16>);
+    else throw CudaError("i8 peak probe: per_commit must be 4, 8 or 16");
 }
 
 }  // namespace nldsc

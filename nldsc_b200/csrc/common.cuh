@@ -115,7 +115,8 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
 void band_maps_destroy(BandMaps*);
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);
 void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);   // tiles carry b_row2
-void launch_i8_peak(int iters, int n_cols, int per_commit, int sm_count, cudaStream_t st);   // measurement only
+void install_band_kernels();   // per device: function attributes + module load of the band kernels (warm-up)
+void launch_i8_peak(int iters, int n_cols, int per_commit, int depth, int sm_count, cudaStream_t st);   // measurement only
 void launch_band_simt(const int8_t* planes, int64_t plane_stride, int32_t npad,
                       const BandArgs& args, cudaStream_t st);
 

@@ -182,6 +182,16 @@ PYBIND11_MODULE(_ldscore, m) {
         if (rc != NLDSC_OK) throw std::runtime_error(err);
         return n;
     }, "usable sm_100 devices");
+    m.def("warmup", [](int first_device, int n_devices) {
+        char err[512] = {0};
+        int rc;
+        {
+            py::gil_scoped_release nogil;
+            rc = nldsc_ld_warmup(first_device, n_devices, err, sizeof(err));
+        }
+        if (rc != NLDSC_OK) throw std::runtime_error(err);
+    }, py::arg("first_device") = 0, py::arg("n_devices") = 1,
+       "prepare the devices (context, pinned staging, kernel images) in parallel before the first calculate_on");
     m.def("as_arrays", [](py::object r) {
         LDScoreResult& v = r.cast<LDScoreResult&>();
         py::dict d;

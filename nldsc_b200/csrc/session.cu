@@ -473,6 +473,7 @@ static void session_free(nldsc_ld_session* s) {
     if (!s) return;
     cudaSetDevice(s->device);
     for (auto& t : s->readers) if (t.joinable()) t.join();
+    if (s->fd_direct >= 0) close(s->fd_direct);
     // every buffer lives in the arena; make sure nothing queued still touches it before it is reused
     if (s->own_stream) cudaStreamSynchronize(s->own_stream);
     if (s->copy_stream) cudaStreamSynchronize(s->copy_stream);
@@ -594,9 +595,19 @@ static void session_upload_file(nldsc_ld_session* s, int fd) {
     s->upload_started = true;
     const int32_t n_pieces = static_cast<int32_t>(s->ev_piece.size());
     s->piece_done.assign(n_pieces, 0);
-    const int n_readers = std::max(1, std::min<int>(HostStage::kReaders, n_pieces));
+    // NLDSC_READERS: reader threads of this shard (default and maximum 4).  A driver that keeps several GPUs busy
+    // from one host sets it to cores / GPUs, so that the readers of all shards together do not oversubscribe the host.
+    const int want_readers = static_cast<int>(std::min<size_t>(HostStage::kReaders, std::max<size_t>(1, env_size("NLDSC_READERS", HostStage::kReaders))));
+    const int n_readers = std::max(1, std::min<int>(want_readers, n_pieces));
+    // NLDSC_ODIRECT=1: read the .bed past the page cache (O_DIRECT), for files that are read once and are larger than
+    // the host's memory can usefully cache (a 94.7 GB UK-Biobank-scale genome).  The byte range of a slot is widened
+    // to 4 KB boundaries (the pinned slots are page-aligned and carry 8 KB of slack); when the file system refuses
+    // O_DIRECT the buffered descriptor is used.
+    int fd_direct = -1;
+    if (env_size("NLDSC_ODIRECT", 0) != 0 && s->bed_path) fd_direct = open(s->bed_path, O_RDONLY | O_DIRECT);
+    s->fd_direct = fd_direct;
     for (int t = 0; t < n_readers; ++t) {
-        s->readers.emplace_back([s, fd, t, n_readers, n_pieces] {
+        s->readers.emplace_back([s, fd, fd_direct, t, n_readers, n_pieces] {
             auto publish = [&](int32_t k, const char* error) {        // piece k is queued (or the upload has failed)
                 {
                     std::lock_guard<std::mutex> g(s->up_mu);
@@ -612,7 +623,8 @@ static void session_upload_file(nldsc_ld_session* s, int fd) {
             };
             try {
                 CUDA_CHECK(cudaSetDevice(s->device));
-                const size_t slot_bytes = s->stage->bytes / HostStage::kSlots;
+                const size_t slot_cap = s->stage->bytes / HostStage::kSlots;
+                const size_t slot_bytes = slot_cap - 8192;       // payload; the rest is the O_DIRECT alignment slack
                 int flip = 0;
                 // test hook: hold reader 0 back so that later pieces are queued before earlier ones
                 const useconds_t lag = t == 0 ? static_cast<useconds_t>(env_size("NLDSC_TEST_READER0_LAG_US", 0)) : 0;
@@ -624,15 +636,30 @@ static void session_upload_file(nldsc_ld_session* s, int fd) {
                         const int slot = 2 * t + flip;
                         flip ^= 1;
                         const size_t len = std::min(slot_bytes, end - off);
-                        char* buf = static_cast<char*>(s->stage->base) + slot * slot_bytes;
+                        char* buf = static_cast<char*>(s->stage->base) + slot * slot_cap;
                         CUDA_CHECK(cudaEventSynchronize(s->stage->ev[slot]));       // slot's previous copy has landed
                         if (lag) usleep(lag);
-                        size_t got = 0;
-                        while (got < len) {
-                            const ssize_t r = pread(fd, buf + got, len - got,
-                                                    3 + static_cast<off_t>(s->load_begin) * s->bps + static_cast<off_t>(off + got));
-                            if (r <= 0) throw CudaError("short read on .bed file");
-                            got += static_cast<size_t>(r);
+                        const off_t file_off = 3 + static_cast<off_t>(s->load_begin) * s->bps + static_cast<off_t>(off);
+                        if (fd_direct >= 0) {
+                            // aligned superset [a0, a1) of [file_off, file_off + len); the last block may end at EOF
+                            const off_t a0 = file_off & ~static_cast<off_t>(4095);
+                            const off_t a1 = (file_off + static_cast<off_t>(len) + 4095) & ~static_cast<off_t>(4095);
+                            size_t got = 0;
+                            const size_t need = static_cast<size_t>(file_off - a0) + len;
+                            while (got < need) {
+                                const ssize_t r = pread(fd_direct, buf + got, static_cast<size_t>(a1 - a0) - got, a0 + static_cast<off_t>(got));
+                                if (r <= 0) throw CudaError("short O_DIRECT read on .bed file");
+                                got += static_cast<size_t>(r);
+                                if ((got & 4095) != 0 && got < need) throw CudaError("unaligned O_DIRECT read on .bed file");
+                            }
+                            buf += file_off - a0;
+                        } else {
+                            size_t got = 0;
+                            while (got < len) {
+                                const ssize_t r = pread(fd, buf + got, len - got, file_off + static_cast<off_t>(got));
+                                if (r <= 0) throw CudaError("short read on .bed file");
+                                got += static_cast<size_t>(r);
+                            }
                         }
                         CUDA_CHECK(cudaMemcpyAsync(s->d_packed + off, buf, len, cudaMemcpyHostToDevice, s->copy_stream));
                         CUDA_CHECK(cudaEventRecord(s->stage->ev[slot], s->copy_stream));
@@ -650,6 +677,7 @@ static void session_upload_file(nldsc_ld_session* s, int fd) {
 
 static void join_reader(nldsc_ld_session* s) {
     for (auto& t : s->readers) if (t.joinable()) t.join();
+    if (s->fd_direct >= 0) { close(s->fd_direct); s->fd_direct = -1; }
 }
 
 // Stage 2: windows -> owned i-blocks -> plane ring -> chunks and supertiles, and their device copies.
@@ -1434,7 +1462,10 @@ int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char
             throw InvalidArgument(buf);
         }
         // every shard streams its own byte range: reader thread -> pinned slot ring -> H2D (session_upload_file)
-        run_sharded(params, out, [&](nldsc_ld_session* s) { session_upload_file(s, fd); });
+        run_sharded(params, out, [&](nldsc_ld_session* s) {
+            s->bed_path = params->bedfile;
+            session_upload_file(s, fd);
+        });
     });
 }
 
@@ -1456,6 +1487,57 @@ int nldsc_ld_calculate_on(const nldsc_ld_params* params, nldsc_ld_result* out, i
         return NLDSC_ERR_RUNTIME;
     }
     return nldsc_ld_calculate(params, out, err, errlen);
+}
+
+int nldsc_ld_calculate_packed_on(const uint8_t* packed, const nldsc_ld_params* params, nldsc_ld_result* out,
+                                 int32_t first_device, int32_t n_devices, char* err, size_t errlen) {
+    if (first_device < 0 || n_devices < 1) {
+        set_err(err, errlen, "first_device must be >= 0 and n_devices >= 1");
+        return NLDSC_ERR_INVALID;
+    }
+    struct Placement {
+        Placement(int d, int n) { tl_first_device = d; tl_n_devices = n; }
+        ~Placement() { tl_first_device = -1; tl_n_devices = 0; }
+    } placement(first_device, n_devices);
+    int32_t have = 0;
+    const int rc = nldsc_ld_device_count(&have, err, errlen);
+    if (rc != NLDSC_OK) return rc;
+    if (first_device >= have) {
+        set_err(err, errlen, "first_device is not a usable CUDA device");
+        return NLDSC_ERR_RUNTIME;
+    }
+    return nldsc_ld_calculate_packed(packed, params, out, err, errlen);
+}
+
+int nldsc_ld_warmup(int32_t first_device, int32_t n_devices, char* err, size_t errlen) {
+    return guarded(err, errlen, [&] {
+        const int ndev = usable_devices();
+        if (first_device < 0 || n_devices < 1 || first_device >= ndev) throw InvalidArgument("device range outside the usable devices");
+        const int last = std::min(ndev, first_device + n_devices);
+        // CUDA context creation, the pinned .bed staging ring and the stream pool cost 0.3-1 s per device when the
+        // first chromosome pays for them one device after the other; here every device is prepared by its own thread
+        std::vector<std::thread> th;
+        std::vector<std::string> errs(static_cast<size_t>(last - first_device));
+        for (int d = first_device; d < last; ++d) {
+            th.emplace_back([d, first_device, &errs] {
+                try {
+                    CUDA_CHECK(cudaSetDevice(d));
+                    CUDA_CHECK(cudaFree(nullptr));
+                    require_sm100(d);
+                    host_stage_release(host_stage_acquire(d));
+                    PlanStage* ps = plan_stage_acquire(d);
+                    ps->reserve(size_t(8) << 20);
+                    plan_stage_release(ps);
+                    for (int k = 0; k < 3; ++k) stream_put(d, k, stream_get(d, k));
+                    install_band_kernels();
+                } catch (const std::exception& e) {
+                    errs[static_cast<size_t>(d - first_device)] = e.what();
+                }
+            });
+        }
+        for (auto& t : th) t.join();
+        for (const auto& e : errs) if (!e.empty()) throw CudaError(e);
+    });
 }
 
 int nldsc_ld_session_create(nldsc_ld_session** out, int device, const nldsc_ld_params* params, int32_t row_begin,
@@ -1703,7 +1785,7 @@ int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* l
 int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int32_t reps, float* ms_out, char* err,
                               size_t errlen) {
     return guarded(err, errlen, [&] {
-        if (mode < 0 || mode > 6 || mode == 5 || n_org <= 0 || n_tiles <= 0 || reps <= 0 || !ms_out) throw InvalidArgument("bad arguments");
+        if (mode < 0 || mode > 6 || n_org <= 0 || n_tiles <= 0 || reps <= 0 || !ms_out) throw InvalidArgument("bad arguments");
         usable_devices();
         const int dev = first_device_from_env();
         CUDA_CHECK(cudaSetDevice(dev));
@@ -1783,11 +1865,11 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
     });
 }
 
-int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t iters, int32_t reps, float* ms_out, double* tops_out,
-                           char* err, size_t errlen) {
+int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t depth, int32_t iters, int32_t reps, float* ms_out,
+                           double* tops_out, char* err, size_t errlen) {
     return guarded(err, errlen, [&] {
-        if (n_cols < 16 || n_cols > 256 || (n_cols % 16) != 0 || per_commit < 1 || per_commit > 8 || iters < 1 || reps < 1 ||
-            !ms_out)
+        if (n_cols < 16 || n_cols > 256 || (n_cols % 16) != 0 || (per_commit != 4 && per_commit != 8 && per_commit != 16) || depth < 1 ||
+            depth > 8 || iters < 1 || reps < 1 || !ms_out)
             throw InvalidArgument("bad arguments");
         usable_devices();
         const int dev = first_device_from_env();
@@ -1797,9 +1879,9 @@ int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t iters, in
         cudaEvent_t e0, e1;
         CUDA_CHECK(cudaEventCreate(&e0));
         CUDA_CHECK(cudaEventCreate(&e1));
-        launch_i8_peak(iters, n_cols, per_commit, sms, nullptr);                         // warm-up
+        launch_i8_peak(iters, n_cols, per_commit, depth, sms, nullptr);                         // warm-up
         CUDA_CHECK(cudaEventRecord(e0, nullptr));
-        for (int r = 0; r < reps; ++r) launch_i8_peak(iters, n_cols, per_commit, sms, nullptr);
+        for (int r = 0; r < reps; ++r) launch_i8_peak(iters, n_cols, per_commit, depth, sms, nullptr);
         CUDA_CHECK(cudaEventRecord(e1, nullptr));
         CUDA_CHECK(cudaEventSynchronize(e1));
         float ms = 0;

@@ -143,6 +143,8 @@ struct nldsc_ld_session {
     std::string up_error;
     std::vector<std::thread> readers;         // .bed readers (nldsc_ld_calculate only): piece k belongs to reader k % kReaders
     std::vector<char> piece_done;             // pieces_issued = length of the all-done prefix
+    const char* bed_path = nullptr;           // .bed uploads: the path, for the optional O_DIRECT descriptor
+    int fd_direct = -1;
     nldsc::HostStage* stage = nullptr;
     nldsc::PlanStage* pstage = nullptr;
     // host copies of the plan (sources of the asynchronous H2D copies)

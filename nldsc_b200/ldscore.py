@@ -194,55 +194,139 @@ def _genome_bfiles(bfile: str) -> list[tuple[str, str]]:
     return found
 
 
+def _parse_bfile_meta(path: str) -> dict:
+    """Everything the scoring call needs from the .bim / .fam of one chromosome (runs in a worker process, so that
+    22 pandas parses neither run one after the other nor hold the GIL of the process that feeds the GPUs)."""
+    import time
+    t0 = time.perf_counter()
+    bed, bim_path, fam_path = _bfile_paths(path)
+    bim = pd.read_csv(bim_path, sep="\t", names=BIM_COLUMNS)
+    if len(bim["CHR"].unique()) != 1:
+        raise NLDSCParameterError("The current version of the program can only work with one chromosome in one file.")
+    with open(fam_path, "rb") as f:
+        fam = f.read()
+    n_org = fam.count(b"\n") + (1 if fam and not fam.endswith(b"\n") else 0)
+    return {"bed": bed, "n_org": n_org, "n_snp": len(bim), "chr": bim["CHR"].astype(str).tolist(),
+            "snp": bim["SNP"].astype(str).tolist(), "bp": bim["BP"].to_numpy(np.int64) if bim["BP"].dtype.kind in "iu" else None,
+            "cm": bim["CM"].to_numpy(dtype=np.float64), "bp_f": bim["BP"].to_numpy(dtype=np.float64),
+            "bed_bytes": os.path.getsize(bed), "seconds": time.perf_counter() - t0}
+
+
 def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: float = 1e-5, std_thr: float = 1e-5,
                         rsq_thr: float | None = None, *, out_dir: str, extra: bool = True, gpus: int | None = None,
-                        first_device: int = 0) -> pd.DataFrame:
+                        first_device: int = 0, parse_workers: int | None = None) -> pd.DataFrame:
     """Score every chromosome bfile of a genome in ONE process.
 
     The reference scores one chromosome per invocation (ldscore/common.py:114-117) and never writes the
-    `.M` files `h2` looks for.  Here the chromosomes are dealt, largest .bed first, to one host thread per
-    GPU (`_ldscore.calculate_on`, no collective: chromosomes are independent); each writes
-    `<out_dir>/<chr>.L2` (+ `.M`, `.M_5_50`), the folder layout LDScoreReader._read_folder globs
-    (h2/common.py:98-112).  Returns one row per chromosome: CHR, file, SNPs, M, MD, seconds, device."""
+    `.M` files `h2` looks for.  Here
+      1. every .bim / .fam is parsed up front by a pool of worker PROCESSES (pandas holds the GIL),
+         while the GPUs are warmed up in parallel (`_ldscore.warmup`: contexts, pinned staging, kernel images);
+      2. the chromosomes are dealt, largest .bed first, to one host thread per GPU (`_ldscore.calculate_on`, GIL
+         released, no collective: chromosomes are independent); NLDSC_READERS is set to cores / GPUs so that the
+         .bed reader threads of all GPUs together do not oversubscribe the host;
+      3. every result goes to a writer pool: `<out_dir>/<chr>.L2` (native writer, GIL released) + `.M`, `.M_5_50`,
+         the folder layout LDScoreReader._read_folder globs (h2/common.py:98-112).
+    Returns one row per chromosome: CHR, file, SNPs, M, MD, seconds (scoring call), device; `.attrs["phases"]` holds
+    the wall time of every phase (parse, warmup, score, write) and `.attrs["per_gpu_busy_s"]` the scoring seconds per GPU."""
+    import time
+    from concurrent.futures import ProcessPoolExecutor, ThreadPoolExecutor
     lds = _module()
+    t_start = time.perf_counter()
     jobs = _genome_bfiles(bfile)
     os.makedirs(out_dir, exist_ok=True)
     if gpus is None:
         gpus = int(os.environ.get("NLDSC_GPUS", "1")) if os.environ.get("NLDSC_GPUS", "1") != "all" else 64
     n_dev = max(1, min(int(gpus), len(jobs), max(1, lds.device_count() - first_device)))
-    jobs.sort(key=lambda j: -os.path.getsize(j[1] + ".bed"))          # longest first
+    wind, metric = _window(ld_wind, wind_metric)
+    maf = _unit_interval(maf_thr, 1.0, "Minor allele frequency")
+    std = _unit_interval(std_thr, 1.0, "standard deviation threshold")
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    if "NLDSC_READERS" not in os.environ and n_dev > 1:
+        os.environ["NLDSC_READERS"] = str(max(1, min(4, cores // n_dev)))
+
+    # ---- 1. parse (processes) beside the device warm-up (threads inside the library)
+    phases = {}
+    warm = threading.Thread(target=lambda: lds.warmup(first_device, n_dev) if hasattr(lds, "warmup") else None)
+    warm.start()
+    t0 = time.perf_counter()
+    n_parse = max(1, min(len(jobs), parse_workers if parse_workers is not None else max(1, cores - n_dev)))
+    if n_parse > 1:
+        with ProcessPoolExecutor(max_workers=n_parse) as ex:
+            metas = list(ex.map(_parse_bfile_meta, [p for _, p in jobs]))
+    else:
+        metas = [_parse_bfile_meta(p) for _, p in jobs]
+    phases["parse_s"] = time.perf_counter() - t0
+    warm.join()
+    phases["parse_and_warmup_s"] = time.perf_counter() - t0
+    meta = {label: m for (label, _), m in zip(jobs, metas)}
+    order = sorted(jobs, key=lambda j: -meta[j[0]]["bed_bytes"])          # longest first
     todo: queue.Queue = queue.Queue()
-    for j in jobs:
+    for j in order:
         todo.put(j)
     rows, errors, lock = [], [], threading.Lock()
+    busy = {first_device + d: 0.0 for d in range(n_dev)}
+    writers = ThreadPoolExecutor(max_workers=max(2, min(8, cores // 2)))
+    pending = []
+
+    def write(label, m, arrays, seconds, device):
+        t = time.perf_counter()
+        l2_path = os.path.join(out_dir, f"{label}.L2")
+        if hasattr(lds, "write_l2") and m["bp"] is not None:
+            lds.write_l2(l2_path, m["chr"], m["snp"], m["bp"], arrays["l2"], arrays["l2d"], arrays["maf"],
+                         arrays["residuals_std"], arrays["l2_ws"], arrays["l2d_ws"], arrays["l2d_wse"], extra)
+        else:
+            bim = pd.DataFrame({"CHR": m["chr"], "SNP": m["snp"], "BP": m["bp_f"]})
+            make_output(bim, arrays, extra=extra).to_csv(l2_path, sep="\t", index=False, float_format="%.5f")
+        mm = write_m_files(l2_path, arrays, m["snp"])
+        with lock:
+            rows.append({"CHR": label, "file": l2_path, "SNPs": m["n_snp"], "M": mm[".M"][0], "MD": mm[".M"][1],
+                         "seconds": seconds, "device": device, "write_seconds": time.perf_counter() - t})
 
     def worker(device: int) -> None:
-        import time
         while True:
             try:
                 label, path = todo.get_nowait()
             except queue.Empty:
                 return
             try:
+                m = meta[label]
+                rsq = _unit_interval(1.0 / m["n_snp"] if rsq_thr is None else rsq_thr, 0.1, "r-squared threshold")
+                params = lds.LDScoreParams(bfile=m["bed"], n_snp=m["n_snp"], n_org=m["n_org"], ld_wind=wind, maf=maf,
+                                           std_thr=std, rsq_thr=rsq, positions=m["cm"] if metric == "cm" else m["bp_f"])
                 t0 = time.perf_counter()
-                l2_path = os.path.join(out_dir, f"{label}.L2")
-                estimate_lds(path, ld_wind, wind_metric, maf_thr, std_thr, rsq_thr, out=l2_path, extra=extra,
-                             device=device, gpus=1, m_files=True)
-                m, md = (int(x) for x in open(os.path.splitext(l2_path)[0] + ".M").read().split()[2:4])
+                ld = lds.calculate_on(params, device, 1)
+                dt = time.perf_counter() - t0
                 with lock:
-                    rows.append({"CHR": label, "file": l2_path, "SNPs": sum(1 for _ in open(path + ".bim")),
-                                 "M": m, "MD": md, "seconds": time.perf_counter() - t0, "device": device})
+                    busy[device] += dt
+                pending.append(writers.submit(write, label, m, result_arrays(ld), dt, device))
             except Exception as e:          # one bad chromosome must not hide behind the others
                 with lock:
                     errors.append((label, e))
 
+    t0 = time.perf_counter()
     threads = [threading.Thread(target=worker, args=(first_device + d,)) for d in range(n_dev)]
     for t in threads:
         t.start()
     for t in threads:
         t.join()
+    phases["score_s"] = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    for f in pending:
+        try:
+            f.result()
+        except Exception as e:
+            errors.append(("write", e))
+    writers.shutdown()
+    phases["write_tail_s"] = time.perf_counter() - t0
+    phases["total_s"] = time.perf_counter() - t_start
     if errors:
         label, e = errors[0]
         raise RuntimeError(f"chromosome {label}: {e}") from e
-    order = {label: i for i, (label, _) in enumerate(_genome_bfiles(bfile))}
-    return pd.DataFrame(sorted(rows, key=lambda r: order[r["CHR"]]))
+    pos = {label: i for i, (label, _) in enumerate(jobs)}
+    df = pd.DataFrame(sorted(rows, key=lambda r: pos[r["CHR"]]))
+    df.attrs["phases"] = phases
+    df.attrs["per_gpu_busy_s"] = busy
+    if os.environ.get("NLDSC_TRACE"):
+        import sys
+        print(f"[nldsc_ld] genome: {phases}  busy per GPU: {busy}", file=sys.stderr)
+    return df

@@ -145,27 +145,59 @@ def cross_counts(codes_i: np.ndarray, codes_j: np.ndarray) -> np.ndarray:
 
 
 def ld_scores_rows(packed: np.ndarray, n_org: int, positions: np.ndarray, ld_wind: float, maf_thr: float,
-                   std_thr: float, rsq_thr: float, rows, max_span: int = 4096) -> dict:
-    """ld_scores() for a few rows of a bfile too large to score whole: every requested row is scored on the
-    sub-bfile that holds its complete window (rows whose windows overlap share one sub-bfile, up to `max_span`
-    SNPs), which is all calculate() ever looks at for that row (stream.h:142-155, ldscalc.h:34-47).
-    Returns the seven result arrays restricted to `rows` (same order), plus "rows"."""
+                   std_thr: float, rsq_thr: float, rows, max_span: int = 4096, block: int = 1024) -> dict:
+    """calculate() (ldscalc.h:8-65) for a few rows of a bfile too large to score whole.  Every requested row is scored
+    against its complete window and nothing else, which is all the reference ever looks at for that row
+    (stream.h:142-155, ldscalc.h:34-47).  Rows whose windows overlap share one pass over the union of their windows
+    (up to `max_span` SNPs); the window SNPs are decoded and standardised `block` at a time, so memory stays at
+    block x n_org doubles however wide the window is (configs[4]: 20,000 SNPs x 100,000 organisms).
+    Returns the seven result arrays restricted to `rows` (ascending), plus "keep" and "rows"."""
     positions = np.asarray(positions, dtype=np.float64)
+    assert np.all(positions >= 0) and np.all(np.diff(positions) >= 0)
     rows = np.asarray(sorted(int(r) for r in rows), dtype=np.int64)
     lo = np.searchsorted(positions, positions[rows] - ld_wind, side="left")
     hi = np.searchsorted(positions, positions[rows] + ld_wind, side="right")      # exclusive
-    keys = ("l2", "l2d", "maf", "residuals_std", "l2_ws", "l2d_ws", "l2d_wse", "keep")
-    out = {k: [] for k in keys}
+    n = float(n_org)
+    nr = len(rows)
+    l2 = np.full(nr, np.nan); l2d = np.full(nr, np.nan)
+    wsa = np.full(nr, -1, dtype=np.int32); wsd = np.full(nr, -1, dtype=np.int32); wsde = np.full(nr, -1, dtype=np.int32)
+    st_r = snp_stats(decode_bed_msb_first(packed[rows], n_org), maf_thr)
+    keep_r, A_r = st_r["keep"], st_r["A"]
     k = 0
-    while k < len(rows):
+    while k < nr:
         a, b, e = int(lo[k]), int(hi[k]), k + 1
-        while e < len(rows) and max(b, int(hi[e])) - a <= max_span:
+        while e < nr and max(b, int(hi[e])) - a <= max_span:
             b = max(b, int(hi[e]))
             e += 1
-        sub = ld_scores(packed[a:b], n_org, positions[a:b], ld_wind, maf_thr, std_thr, rsq_thr, rows=rows[k:e] - a)
-        for key in keys:
-            out[key].append(sub[key][rows[k:e] - a])
+        idx = [q for q in range(k, e) if keep_r[q]]
+        add = {q: 1.0 for q in idx}                     # ldscalc.h:27-28
+        dom = {q: 0.0 for q in idx}
+        cnt = {q: [0, 0, 0] for q in idx}
+        for s0 in range(a, b, block):
+            s1 = min(b, s0 + block)
+            st = snp_stats(decode_bed_msb_first(packed[s0:s1], n_org), maf_thr)
+            with np.errstate(all="ignore"):
+                dom_ok = st["rstd"] > std_thr                                   # tools.h:31-33 (NaN -> False)
+            js_all = np.arange(s0, s1)
+            for q in idx:
+                i = rows[q]
+                # the reference's own predicate at the edges (tools.h:43-44), kept SNPs only, not the SNP itself
+                m = st["keep"] & (np.abs(positions[js_all] - positions[i]) <= ld_wind) & (js_all != i)
+                if not m.any():
+                    continue
+                with np.errstate(all="ignore"):
+                    ca = st["A"][m] @ A_r[q] / n                                # tools.h:89
+                    add[q] += float(np.sum(1.0 - (1.0 - ca * ca) * (n - 1) / (n - 2)))   # tools.h:91, ldscalc.h:38
+                    md = m & dom_ok
+                    cd = st["D"][md] @ A_r[q] / n                               # ldscalc.h:41
+                    adj = 1.0 - (1.0 - cd * cd) * (n - 1) / (n - 2)
+                    dom[q] += float(np.sum(adj))
+                cnt[q][0] += int(m.sum())
+                cnt[q][1] += int(md.sum())
+                cnt[q][2] += int(np.sum(adj > rsq_thr))                         # tools.h:36-38 (strict)
+        for q in idx:
+            l2[q], l2d[q] = add[q], dom[q]
+            wsa[q], wsd[q], wsde[q] = cnt[q]
         k = e
-    res = {key: np.concatenate(v) for key, v in out.items()}
-    res["rows"] = rows
-    return res
+    return {"l2": l2, "l2d": l2d, "maf": st_r["maf"], "residuals_std": np.where(keep_r, st_r["rstd"], np.nan),
+            "l2_ws": wsa, "l2d_ws": wsd, "l2d_wse": wsde, "keep": keep_r, "rows": rows}

@@ -51,12 +51,14 @@ for c in CHROMS:
     df = pd.read_csv(f"{d}/out/{c}.L2", sep="\t")
     pairs += int(df["WSA"][df["WSA"] >= 0].sum())
 total_snps = sum(SIZES.values())
-rec = {"config": "%s: N=%d x %d chromosomes, %d SNPs in total, 2%% missing, 1 cM" % (TAG, N, len(CHROMS), total_snps), "gpus": gpus,
+phases = dict(summ.attrs.get("phases", {}))
+busy = {str(k): v for k, v in summ.attrs.get("per_gpu_busy_s", {}).items()}
+rec = {"phases_last_run": phases, "per_gpu_busy_s_last_run": busy, "config": "%s: N=%d x %d chromosomes, %d SNPs in total, 2%% missing, 1 cM" % (TAG, N, len(CHROMS), total_snps), "gpus": gpus,
        "bed_bytes": total_snps * ((N + 3) // 4),
        "pairs": pairs, "wall_s": runs, "outputs_identical_across_runs": digests[0] == digests[1], "l2_sha256": digests[0], "pairs_per_s_wall": pairs / min(runs), "generate_s": gen_s,
        "per_chromosome": summ.drop(columns=["file"]).to_dict(orient="records"),
        "note": "wall time of estimate_lds_genome: .bim/.fam parsing, .bed read from the page cache, GPU scoring, %.5f .L2 + .M files written"}
 print(json.dumps(rec))
 os.makedirs("gpurun_out", exist_ok=True)
-json.dump(rec, open("gpurun_out/%s.json" % TAG, "w"), indent=1)
+json.dump(rec, open("gpurun_out/%s_%dgpu.json" % (TAG, gpus), "w"), indent=1)
 shutil.rmtree(d, ignore_errors=True)

@@ -340,3 +340,76 @@ def test_wide_supertiles_equal_narrow_bitwise(monkeypatch):
         small = _run(g)
         for k in RESULT_KEYS:
             assert np.array_equal(wide[k], small[k], equal_nan=True), (w, k)
+
+
+# ---- BASELINE.json configs at full / near-full size: oracle on many rows ---------------------------------------
+# The workloads are drawn on the GPU (synth.generate_packed_cuda: torch RNG + elementwise ops, plumbing only) because the
+# NumPy generator needs minutes at these sizes; the oracle then scores random rows, each against its complete window.
+
+def _gpu_case(n_org, n_snp, missing, seed, density, wind):
+    import torch
+    spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=missing, seed=seed, density=density)
+    packed = synth.generate_packed_cuda(spec, "cuda:0").cpu().numpy()
+    torch.cuda.empty_cache()
+    cm, _ = synth.genetic_map(spec)
+    return {"packed": packed, "n_org": n_org, "positions": cm, "ld_wind": wind, "maf": 1e-4, "std_thr": 1e-5,
+            "rsq_thr": 1.0 / n_snp}
+
+
+def _check_rows(g, out, n_clusters, per_cluster, spread, max_span, seed=0):
+    """Oracle on n_clusters x per_cluster random rows (rows of a cluster lie within `spread` SNPs of each other, so
+    they share one pass over the union of their windows)."""
+    n_snp = g["packed"].shape[0]
+    rng = np.random.default_rng(seed)
+    centres = rng.choice(max(1, n_snp - spread), size=n_clusters, replace=False)
+    rows = np.unique(np.concatenate([c + rng.choice(spread, per_cluster, replace=False) for c in centres]))
+    want = ld_oracle.ld_scores_rows(g["packed"], g["n_org"], g["positions"], g["ld_wind"], g["maf"], g["std_thr"],
+                                    g["rsq_thr"], rows, max_span=max_span)
+    r, kw = want["rows"], want["keep"]
+    assert np.array_equal(~np.isnan(out["l2"][r]), kw), "retained-SNP list"
+    assert np.array_equal(out["maf"][r], want["maf"], equal_nan=True), "maf bit-exact"
+    for k in ("l2_ws", "l2d_ws", "l2d_wse"):
+        assert np.array_equal(out[k][r][kw], want[k][kw]), k
+    assert np.all(out["l2_ws"][r][~kw] == -1)
+    l2e = np.max(np.abs(out["l2"][r][kw] - want["l2"][kw]) / np.maximum(np.abs(want["l2"][kw]), 1.0))
+    l2de = np.max(np.abs(out["l2d"][r][kw] - want["l2d"][kw]) / np.maximum(np.abs(want["l2d"][kw]), 1.0))
+    rse = np.max(np.abs(out["residuals_std"][r][kw] - want["residuals_std"][kw]))
+    assert l2e <= 1e-9 and l2de <= 1e-9 and rse <= 1e-9, (l2e, l2de, rse)
+    return int(kw.sum())
+
+
+def _window_count_property(g, out):
+    keep = out["l2_ws"] >= 0
+    lo, hi = capi.plan_windows(g["positions"], g["ld_wind"])
+    ck = np.concatenate([[0], np.cumsum(keep)])
+    assert np.array_equal(out["l2_ws"][keep], (ck[hi + 1] - ck[lo])[keep] - 1)          # ldscalc.h:52, stream.h:142-155
+    assert np.all(out["l2d_ws"][keep] <= out["l2_ws"][keep]) and np.all(out["l2d_wse"][keep] <= out["l2d_ws"][keep])
+
+
+def test_cfg2_full_size_oracle_rows():
+    """BASELINE.json configs[1] IN FULL -- the benchmark's workload: N=10,000 x 100,000 SNPs, 2% missing, 1 cM --
+    with the oracle on >= 200 random rows spread over the whole chromosome."""
+    g = _gpu_case(10_000, 100_000, 0.02, seed=2, density=340.0, wind=1.0)
+    out = _run(g)
+    _window_count_property(g, out)
+    assert _check_rows(g, out, n_clusters=30, per_cluster=8, spread=240, max_span=2400) >= 200
+
+
+def test_cfg4_ukb_slice_oracle_rows():
+    """BASELINE.json configs[3] shape (N=315,599, N % 4 == 3, 1 cM): a slice of NLDSC_TEST_UKB_SNPS SNPs (default 4,096;
+    the full genome is scripts/ukb_genome.py), oracle on >= 20 rows."""
+    n_snp = int(os.environ.get("NLDSC_TEST_UKB_SNPS", "4096"))
+    g = _gpu_case(315_599, n_snp, 0.02, seed=7, density=340.0, wind=1.0)
+    out = _run(g)
+    _window_count_property(g, out)
+    assert _check_rows(g, out, n_clusters=2, per_cluster=12, spread=64, max_span=1600, seed=1) >= 20
+
+
+def test_cfg5_wide_window_slice_oracle_rows():
+    """BASELINE.json configs[4] shape (N=100,000, dense map, 10 cM window ~ 20,000 SNPs): a slice of
+    NLDSC_TEST_CFG5_SNPS SNPs (default 12,288), oracle on >= 20 rows with windows thousands of SNPs wide."""
+    n_snp = int(os.environ.get("NLDSC_TEST_CFG5_SNPS", "12288"))
+    g = _gpu_case(100_000, n_snp, 0.02, seed=5, density=1000.0, wind=10.0)
+    out = _run(g)
+    _window_count_property(g, out)
+    assert _check_rows(g, out, n_clusters=2, per_cluster=12, spread=48, max_span=30000, seed=2) >= 20

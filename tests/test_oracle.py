@@ -71,3 +71,23 @@ def test_cross_count_closed_form_matches_restatement(golden):
     r = (sxx - n * xbar[:, None] * xbar[None, :]) / (n * sd[:, None] * sd[None, :])
     want = st["A"][keep] @ st["A"][keep].T / n
     assert np.max(np.abs(r - want)) < 1e-12
+
+
+def test_row_sliced_oracle_equals_whole_file_oracle():
+    """ld_scores_rows (what the full-size GPU tests and bench.py check against) must agree with ld_scores, itself
+    pinned to the compiled reference above -- for any clustering of the rows and any block size."""
+    from nldsc_b200 import synth
+    spec = synth.SynthSpec(n_org=701, n_snp=2000, missing=0.03, seed=14)
+    packed = synth.generate_packed(spec, workers=1)
+    cm, _ = synth.genetic_map(spec)
+    full = ld_oracle.ld_scores(packed, 701, cm, 0.8, 1e-4, 1e-5, 1 / 2000)
+    rows = [0, 3, 700, 701, 702, 1500, 1999] + list(np.nonzero(~full["keep"])[0][:2])
+    for max_span, block in ((1, 64), (900, 257), (4096, 1024)):
+        got = ld_oracle.ld_scores_rows(packed, 701, cm, 0.8, 1e-4, 1e-5, 1 / 2000, rows, max_span=max_span, block=block)
+        r = got["rows"]
+        assert np.array_equal(got["keep"], full["keep"][r])
+        for k in ("l2_ws", "l2d_ws", "l2d_wse"):
+            assert np.array_equal(got[k], full[k][r]), k
+        assert np.array_equal(got["maf"], full["maf"][r], equal_nan=True)
+        for k in ("l2", "l2d", "residuals_std"):
+            assert np.allclose(got[k], full[k][r], rtol=1e-12, atol=1e-12, equal_nan=True), k
