@@ -290,6 +290,7 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 #pragma unroll 1
                 for (int c2 = 0; c2 < 2; ++c2) {      // 16 j-SNPs per pass
                     const int c = 2 * half + c2;
+                    if (args.dump == nullptr && !__any_sync(0xFFFFFFFFu, row_needs(row, tl.j0 + 16 * c, tl.j0 + 16 * c + 15))) continue;
                     // columns: [m h a] of j-SNPs 0-31, then [m h a] of j-SNPs 32-63
                     const uint32_t col = 96 * half + 16 * c2;
                     int32_t vm[16], vh[16], va[16];
@@ -392,7 +393,7 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
-        for (int s = 0; s < kWStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < kWStages; ++s) { mbar_init(&full[s], args.probe == 1 ? 2 : 1); mbar_init(&empty[s], 1); }
         mbar_init(tfull, 1);
         mbar_init(tempty, 16);                 // 8 epilogue warps x 2 CTAs
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -423,7 +424,9 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 for (int k = 0; k < args.k_steps; ++k) {
                     mbar_wait(&empty[stage], phase ^ 1, 5);
                     if (args.probe == 1) {           // tensor-pipe probe: no loads, operands are whatever the stage holds
-                        if (rank == 0) mbar_expect_tx(&full[stage], 0);
+                        // the full barrier must still wait for BOTH producers (as the bytes of both make it do normally):
+                        // a peer that is not part of the handshake falls phases behind its empty barriers and loses them
+                        if (rank == 0) mbar_expect_tx(&full[stage], 0); else mbar_arrive_leader(&full[stage]);
                         if (++stage == kWStages) { stage = 0; phase ^= 1; }
                         continue;
                     }
@@ -465,7 +468,13 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                         for (int kk = 0; kk < kKStep / 32; ++kk)
                             tc_mma_i8(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, kIdesc, (k | kk) != 0);
                     }
-                    tc_commit_pair(&empty[stage]);
+                    if (!args.commit2) {
+                        tc_commit_pair(&empty[stage]);
+                    } else if ((k & 1) || k == args.k_steps - 1) {
+                        // two stages released together: 16 MMAs between commits instead of 8
+                        if (k & 1) tc_commit_pair(&empty[stage == 0 ? kWStages - 1 : stage - 1]);
+                        tc_commit_pair(&empty[stage]);
+                    }
                     if (++stage == kWStages) { stage = 0; phase ^= 1; }
                 }
                 tc_commit_pair(tfull);
@@ -496,6 +505,9 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 #pragma unroll 1
                 for (int c2 = 0; c2 < 2; ++c2) {
                     const int c = 2 * half + c2;
+                    // the 16 j-SNPs of this pass lie outside the window of every row of the warp (the corners of the
+                    // first / last supertiles of an i-pair, a fifth of all pair slots at a 1 cM window): nothing to add
+                    if (!__any_sync(0xFFFFFFFFu, row_needs(row, j0 + 16 * c, j0 + 16 * c + 15))) continue;
                     const uint32_t col = 96 * half + 16 * c2;
                     int32_t vm[16], vh[16], va[16];
                     tmem_ld16(taddr + col, vm);

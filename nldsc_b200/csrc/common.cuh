@@ -54,8 +54,8 @@ __host__ __device__ inline int64_t part_index(int64_t slot, int rank, int half, 
     return ((slot * 2 + rank) * 2 + half) * kBlk + row;
 }
 struct Partials {
-    double* add;     // sum of r2adj(A_i, A_j)
-    double* dom;     // sum of r2adj(A_i, D_j) over dominance-usable j
+    double* add;     // sum over the tile's in-window kept j of q_ij = (n sd_i corr(A_i, A_j))^2 -- see epilogue.cuh
+    double* dom;     // the same for corr(A_i, D_j), over dominance-usable j
     int32_t* wsa;    // in-window kept j
     int32_t* wsd;    // ... that are dominance-usable
     int32_t* wsde;   // ... with r2adj_dom > rsq_thr
@@ -74,8 +74,10 @@ struct BandArgs {
     double inv_n;
     double adj_c;               // (n - 1) / (n - 2)
     double rsq_thr;
+    double thr_num;             // (rsq_thr - k0) / adj_c with k0 = 1 - adj_c: r2adj > rsq_thr  <=>  w_i^2 q_ij > thr_num (epilogue.cuh)
     Partials part;
     int32_t* dump;              // optional raw accumulators [tile][rank][128][192] (parity hook)
+    int32_t commit2;            // experiment: release the operand ring two stages at a time (16 MMAs between commits)
     int32_t probe;              // measurement hook: 0 = normal, 1 = MMAs without TMA loads, 2 = TMA loads without MMAs, 3 = epilogue only
 };
 
@@ -99,7 +101,7 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 // counts / coef / flags / maf / rstd are indexed by shard-local row; rows [row0, row0 + n_rows) are processed
 void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
                   double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
-                  double* rstd_out, cudaStream_t st);
+                  double* rstd_out, cudaStream_t st, const uint8_t* unused = nullptr);   // unused[row] != 0: position < 0
 void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
                    int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
                    int32_t dst_row0, int32_t* counts, cudaStream_t st);   // counts != null: += genotype counts (zeroed by the caller)
@@ -128,6 +130,8 @@ struct FinalizeArgs {
     int32_t own_end;
     Partials part;
     const uint8_t* flags;
+    const SnpCoef* coef;        // [n_load]: the row factor w_i = inv_sd / n
+    double n, inv_n, adj_c;     // organisms, 1 / n, (n - 1) / (n - 2)
     double* l2;                 // outputs, indexed by (local row - own_begin)
     double* l2d;
     int32_t* wsa;

@@ -350,17 +350,51 @@ void require_sm100(int device) {
 
 int device_sm_count(int device) { return dev_info(device).sms; }
 
-void validate_params(const nldsc_ld_params* p) {
+void validate_params(const nldsc_ld_params* p, bool allow_unused = false) {
     if (!p) throw InvalidArgument("params is null");
     if (p->n_snp <= 0) throw InvalidArgument("n_snp must be positive");
     if (p->n_org <= 0) throw InvalidArgument("n_org must be positive");
     if (!p->positions) throw InvalidArgument("positions is null");
     if (!(p->ld_wind >= 0.0)) throw InvalidArgument("ld_wind must be non-negative");
+    double last = -1.0;
     for (int32_t i = 0; i < p->n_snp; ++i) {
-        // negative ("unused") or unsorted positions are undefined behaviour in the reference
-        if (!(p->positions[i] >= 0.0)) throw InvalidArgument("positions must be non-negative");
-        if (i && p->positions[i] < p->positions[i - 1]) throw InvalidArgument("positions must be non-decreasing");
+        const double x = p->positions[i];
+        if (x != x) throw InvalidArgument("positions must not be NaN");
+        if (x < 0.0) {
+            // the reference treats position < 0 as "SNP not used" (tools.h:16-24): never read, in nobody's window
+            if (!allow_unused) throw InvalidArgument("positions must be non-negative");
+            continue;
+        }
+        // unlike the reference, which walks whatever order it is given (undefined results), the band plan
+        // needs the used SNPs in map order
+        if (x < last) throw InvalidArgument("positions of the used SNPs must be non-decreasing (sort the .bim by position; the reference does not check this)");
+        last = x;
     }
+}
+
+// SNPs with a negative position are "unused" (reference tools.h:16-24, stream.h:189-194, ldscalc.h:24,57): skipped in
+// the .bed, members of no window, outputs left at NaN / -1 (MAF too: never decoded).  Here they stay rows of the
+// band plan -- dropped rows, like SNPs that fail the MAF filter -- and get the position of the nearest used SNP before
+// them so that the windows of the others can be found by bisection.  `eff` is empty when no SNP is unused.
+struct UnusedView {
+    std::vector<double> eff;
+    std::vector<uint8_t> unused;
+    bool any() const { return !unused.empty(); }
+};
+UnusedView mark_unused(const nldsc_ld_params* p) {
+    UnusedView v;
+    bool any = false;
+    for (int32_t i = 0; i < p->n_snp && !any; ++i) any = p->positions[i] < 0.0;
+    if (!any) return v;
+    v.eff.assign(p->positions, p->positions + p->n_snp);
+    v.unused.assign(static_cast<size_t>(p->n_snp), 0);
+    double fill = 0.0;
+    for (int32_t i = 0; i < p->n_snp; ++i) if (v.eff[i] >= 0.0) { fill = v.eff[i]; break; }
+    for (int32_t i = 0; i < p->n_snp; ++i) {
+        if (v.eff[i] < 0.0) { v.eff[i] = fill; v.unused[i] = 1; }
+        else fill = v.eff[i];
+    }
+    return v;
 }
 
 template <class T>
@@ -764,6 +798,11 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     s->d_rstd = amalloc<double>(s->arena, n_load_pad);
     s->d_win_lo = amalloc<int32_t>(s->arena, n_load_pad);
     s->d_win_hi = amalloc<int32_t>(s->arena, n_load_pad);
+    if (!s->h_unused.empty()) {
+        s->d_unused = amalloc<uint8_t>(s->arena, n_load_pad);
+        CUDA_CHECK(cudaMemsetAsync(s->d_unused, 0, n_load_pad, st));
+        CUDA_CHECK(cudaMemcpyAsync(s->d_unused, s->h_unused.data(), s->h_unused.size(), cudaMemcpyHostToDevice, st));
+    }
     CUDA_CHECK(cudaMemsetAsync(s->d_flags, 0, n_load_pad, st));
     CUDA_CHECK(cudaMemsetAsync(s->d_coef, 0, sizeof(SnpCoef) * n_load_pad, st));
     const int32_t n_own = s->own_end - s->own_begin;
@@ -1031,6 +1070,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     // N = 10,000 it is the other way round: 4.09 vs 4.62 ms), so there the two kernels take turns.
     const char* wo = getenv("NLDSC_WIDE_OVERLAP");
     const bool turns = overlap && s->wide && (wo ? wo[0] == '0' : s->npad / kKAlign >= 512);
+    const int32_t commit2 = env_size("NLDSC_COMMIT2", 0) != 0 ? 1 : 0;
     const char* bsn = getenv("NLDSC_BAND_STREAMS");
     const bool two_band = overlap && !(bsn && bsn[0] == '1') && s->chunks.size() > 1;
     if (overlap) {
@@ -1088,7 +1128,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         if (r1 > r0) {
             SpanScope sc(s, us, kFamStats);
             launch_stats(s->d_counts, r0, r1 - r0, s->n_org, s->maf_thr, s->std_thr, s->d_coef, s->d_flags,
-                         s->d_maf, s->d_rstd, us);
+                         s->d_maf, s->d_rstd, us, s->d_unused);
             ++s->launches;
         }
         if (overlap) {
@@ -1108,8 +1148,10 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         a.inv_n = 1.0 / n;
         a.adj_c = (n - 1.0) / (n - 2.0);
         a.rsq_thr = s->rsq_thr;
+        a.thr_num = (s->rsq_thr - (1.0 - a.adj_c)) / a.adj_c;
         a.part = odd ? s->part2 : s->part;
         a.dump = nullptr;
+        a.commit2 = commit2;
         {
             SpanScope sc(s, bs, kFamBand);
             if (s->use_simt)
@@ -1127,6 +1169,10 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         f.own_end = s->own_end;
         f.part = odd ? s->part2 : s->part;
         f.flags = s->d_flags;
+        f.coef = s->d_coef;
+        f.n = n;
+        f.inv_n = 1.0 / n;
+        f.adj_c = (n - 1.0) / (n - 2.0);
         f.l2 = s->d_l2;
         f.l2d = s->d_l2d;
         f.wsa = s->d_wsa;
@@ -1264,12 +1310,16 @@ void compute_windows_device(int device, PlanStage* ps, cudaStream_t st, const do
 // `start_upload(session)` begins the asynchronous H2D of the session's packed rows [load_begin, load_end)
 // (from host memory or from the .bed); it must not block on the transfer.
 template <class StartUpload>
-void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& start_upload) {
+void run_sharded(const nldsc_ld_params* p_in, nldsc_ld_result* out, StartUpload&& start_upload) {
     Tracer tr;
-    validate_params(p);
+    validate_params(p_in, /*allow_unused=*/true);
     if (!out || !out->l2 || !out->l2d || !out->maf || !out->residuals_std || !out->l2_ws || !out->l2d_ws ||
         !out->l2d_wse)
         throw InvalidArgument("result arrays must all be non-null");
+    const UnusedView uv = mark_unused(p_in);
+    nldsc_ld_params p_eff = *p_in;
+    if (uv.any()) p_eff.positions = uv.eff.data();
+    const nldsc_ld_params* p = &p_eff;
     const int ndev = usable_devices();
     const int dev0 = first_device_from_env();
     const int ndev_use = gpus_from_env(std::max(1, ndev - dev0));
@@ -1299,6 +1349,7 @@ void run_sharded(const nldsc_ld_params* p, nldsc_ld_result* out, StartUpload&& s
             // PCIe before anything is planned (windows and plan travel by SM copies, not the copy engine)
             if (whole) s = session_open(j.device, p, 0, p->n_snp);
             else s = session_open(j.device, p, floor64(lo[j.row_begin]), hi[j.row_end - 1] + 1);
+            if (uv.any()) s->h_unused.assign(uv.unused.begin() + s->load_begin, uv.unused.begin() + s->load_end);
             t1 = now();
             start_upload(s);
             t2 = now();
@@ -1432,7 +1483,7 @@ int nldsc_ld_calculate_packed(const uint8_t* packed, const nldsc_ld_params* para
                               size_t errlen) {
     return guarded(err, errlen, [&] {
         if (!packed) throw InvalidArgument("packed is null");
-        validate_params(params);
+        validate_params(params, /*allow_unused=*/true);
         const int64_t bps = (static_cast<int64_t>(params->n_org) + 3) / 4;
         run_sharded(params, out, [&](nldsc_ld_session* s) {
             session_upload_mem(s, packed + static_cast<size_t>(s->load_begin) * bps, nullptr);
@@ -1442,7 +1493,7 @@ int nldsc_ld_calculate_packed(const uint8_t* packed, const nldsc_ld_params* para
 
 int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char* err, size_t errlen) {
     return guarded(err, errlen, [&] {
-        validate_params(params);
+        validate_params(params, /*allow_unused=*/true);
         if (!params->bedfile) throw InvalidArgument("bedfile is null");
         const int fd = open(params->bedfile, O_RDONLY);
         if (fd < 0) throw CudaError(std::string("cannot open ") + params->bedfile + ": " + strerror(errno));
@@ -1742,6 +1793,7 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         a.inv_n = 1.0 / n_org;
         a.adj_c = 1.0;
         a.rsq_thr = 0.0;
+        a.thr_num = 0.0;
         a.part.add = d_pd;
         a.part.dom = d_pd + 4 * kBlk;
         a.part.wsa = d_pi;

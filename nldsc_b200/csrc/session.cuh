@@ -108,6 +108,8 @@ struct nldsc_ld_session {
     int32_t* d_counts = nullptr;
     nldsc::SnpCoef* d_coef = nullptr;
     uint8_t* d_flags = nullptr;
+    uint8_t* d_unused = nullptr;               // [n_load] 1 = position < 0 ("unused", tools.h:16-24); null when no SNP is
+    std::vector<uint8_t> h_unused;
     double* d_maf = nullptr;
     double* d_rstd = nullptr;
     int32_t* d_win_lo = nullptr;

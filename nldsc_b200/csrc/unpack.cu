@@ -30,7 +30,7 @@ __device__ __forceinline__ uint32_t tail_pair_mask(int n_org) {
 __global__ void __launch_bounds__(256)
 stats_kernel(const int32_t* __restrict__ counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
              double std_thr, SnpCoef* __restrict__ coef, uint8_t* __restrict__ flags,
-             double* __restrict__ maf_out, double* __restrict__ rstd_out) {
+             double* __restrict__ maf_out, double* __restrict__ rstd_out, const uint8_t* __restrict__ unused) {
     int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_rows) return;
     row += row0;
@@ -44,8 +44,10 @@ stats_kernel(const int32_t* __restrict__ counts, int32_t row0, int32_t n_rows, i
     const float mu_d_f = (float)(nadd_sum / n_obs);
     const float f2 = mu_a_f / 2.0f;
     const float maf_f = ((double)f2 < 0.5) ? f2 : 1.0f - f2;
-    const bool keep = !((double)maf_f <= maf_thr);         // NaN passes
-    maf_out[row] = (double)maf_f;
+    // position < 0: the reference never reads the SNP (stream.h:189-194), its MAF stays NaN (encoder.h:47)
+    const bool is_unused = unused != nullptr && unused[row] != 0;
+    const bool keep = !is_unused && !((double)maf_f <= maf_thr);         // NaN passes
+    maf_out[row] = is_unused ? __longlong_as_double(0x7FF8000000000000LL) : (double)maf_f;
 
     SnpCoef c;
     uint8_t fl = 0;
@@ -171,10 +173,10 @@ zero_rows_kernel(int8_t* __restrict__ planes, int64_t plane_stride, int32_t npad
 
 void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
                   double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
-                  double* rstd_out, cudaStream_t st) {
+                  double* rstd_out, cudaStream_t st, const uint8_t* unused) {
     if (n_rows <= 0) return;
     stats_kernel<<<(n_rows + 255) / 256, 256, 0, st>>>(counts, row0, n_rows, n_org, maf_thr, std_thr,
-                                                       coef, flags, maf_out, rstd_out);
+                                                       coef, flags, maf_out, rstd_out, unused);
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -244,22 +244,24 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     if "NLDSC_READERS" not in os.environ and n_dev > 1:
         os.environ["NLDSC_READERS"] = str(max(1, min(4, cores // n_dev)))
 
-    # ---- 1. parse (processes) beside the device warm-up (threads inside the library)
+    # ---- 1. parse (processes) beside the device warm-up; the GPU threads below start on a chromosome as soon as ITS
+    # parse is done, so only the first parse is on the critical path
     phases = {}
+    t0 = time.perf_counter()
     warm = threading.Thread(target=lambda: lds.warmup(first_device, n_dev) if hasattr(lds, "warmup") else None)
     warm.start()
-    t0 = time.perf_counter()
+    order = sorted(jobs, key=lambda j: -os.path.getsize(j[1] + ".bed"))          # longest first
     n_parse = max(1, min(len(jobs), parse_workers if parse_workers is not None else max(1, cores - n_dev)))
-    if n_parse > 1:
-        with ProcessPoolExecutor(max_workers=n_parse) as ex:
-            metas = list(ex.map(_parse_bfile_meta, [p for _, p in jobs]))
-    else:
-        metas = [_parse_bfile_meta(p) for _, p in jobs]
-    phases["parse_s"] = time.perf_counter() - t0
+    pool = ProcessPoolExecutor(max_workers=n_parse) if n_parse > 1 else ThreadPoolExecutor(max_workers=1)
+    meta_f = {label: pool.submit(_parse_bfile_meta, path) for label, path in order}
+    parse_done = [0.0]
+
+    def _note_parse(_f):
+        parse_done[0] = max(parse_done[0], time.perf_counter() - t0)
+    for f in meta_f.values():
+        f.add_done_callback(_note_parse)
     warm.join()
-    phases["parse_and_warmup_s"] = time.perf_counter() - t0
-    meta = {label: m for (label, _), m in zip(jobs, metas)}
-    order = sorted(jobs, key=lambda j: -meta[j[0]]["bed_bytes"])          # longest first
+    phases["warmup_s"] = time.perf_counter() - t0
     todo: queue.Queue = queue.Queue()
     for j in order:
         todo.put(j)
@@ -289,7 +291,7 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
             except queue.Empty:
                 return
             try:
-                m = meta[label]
+                m = meta_f[label].result()
                 rsq = _unit_interval(1.0 / m["n_snp"] if rsq_thr is None else rsq_thr, 0.1, "r-squared threshold")
                 params = lds.LDScoreParams(bfile=m["bed"], n_snp=m["n_snp"], n_org=m["n_org"], ld_wind=wind, maf=maf,
                                            std_thr=std, rsq_thr=rsq, positions=m["cm"] if metric == "cm" else m["bp_f"])
@@ -310,6 +312,8 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     for t in threads:
         t.join()
     phases["score_s"] = time.perf_counter() - t0
+    phases["parse_s"] = parse_done[0]                # when the last parse finished, from the start (overlaps the scoring)
+    pool.shutdown()
     t0 = time.perf_counter()
     for f in pending:
         try:

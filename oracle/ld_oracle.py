@@ -84,6 +84,33 @@ def snp_stats(codes: np.ndarray, maf_thr: float):
 
 def ld_scores(packed: np.ndarray, n_org: int, positions: np.ndarray, ld_wind: float,
               maf_thr: float, std_thr: float, rsq_thr: float, rows=None) -> dict:
+    """calculate() with the reference's "unused SNP" rule: a SNP with position < 0 is skipped in the .bed
+    (stream.h:189-194 `pass`), is in nobody's window (tools.h:16-24,41-49) and keeps the initial outputs NaN / -1
+    (ldscalc.h:13-21,24,57), MAF included (never decoded: encoder.h:47).  The used SNPs are scored among themselves
+    by _ld_scores_used.  NB: this is the rule as the reference's filter states it; the reference's own sliding cache
+    stops reading ahead at an unused SNP (stream.h:182-197) and indexes past its cache when the file starts with
+    one, so its results with negative positions are not well defined and are not a parity target."""
+    positions = np.asarray(positions, dtype=np.float64)
+    used = positions >= 0
+    if used.all():
+        return _ld_scores_used(packed, n_org, positions, ld_wind, maf_thr, std_thr, rsq_thr, rows)
+    idx = np.nonzero(used)[0]
+    sub_rows = None
+    if rows is not None:
+        where = {int(g): k for k, g in enumerate(idx)}
+        sub_rows = [where[int(r)] for r in rows if int(r) in where]
+    sub = _ld_scores_used(packed[idx], n_org, positions[idx], ld_wind, maf_thr, std_thr, rsq_thr, sub_rows)
+    m = len(positions)
+    out = {"l2": np.full(m, np.nan), "l2d": np.full(m, np.nan), "maf": np.full(m, np.nan),
+           "residuals_std": np.full(m, np.nan), "l2_ws": np.full(m, -1, np.int32), "l2d_ws": np.full(m, -1, np.int32),
+           "l2d_wse": np.full(m, -1, np.int32), "keep": np.zeros(m, bool), "counts": np.zeros((m, 3), np.int64)}
+    for k in out:
+        out[k][idx] = sub[k]
+    return out
+
+
+def _ld_scores_used(packed: np.ndarray, n_org: int, positions: np.ndarray, ld_wind: float,
+                    maf_thr: float, std_thr: float, rsq_thr: float, rows=None) -> dict:
     """calculate(), ldscalc.h:8-65, for sorted non-negative positions (the window
     of SNP i is {j != i : kept_j and |pos_j - pos_i| <= ld_wind}, stream.h:142-155
     with tools.h:41-49).  `rows`: score only these SNPs (spot checks at large sizes)."""

@@ -26,6 +26,27 @@ def _lib(flavour: int) -> ctypes.CDLL:
     return _libs[flavour]
 
 
+def find_openblas() -> str | None:
+    """A real OpenBLAS exporting cblas_sdot, if this image has one (bundled with opencv / scipy wheels)."""
+    import glob
+    import site
+    for sp in site.getsitepackages():
+        for pat in ("opencv_python_headless.libs/libopenblas*.so*", "scipy.libs/libscipy_openblas*.so*"):
+            hits = sorted(glob.glob(os.path.join(sp, pat)))
+            if hits:
+                return hits[0]
+    import ctypes.util
+    return ctypes.util.find_library("openblas")
+
+
+def blas_name(flavour: int = 32) -> str:
+    """Which dot the float build uses: the shim loop, or the BLAS symbol resolved through NLDSC_REF_BLAS (the variable
+    is read once, at the first dot of the process)."""
+    lib = _lib(flavour)
+    lib.ref_shim_blas_name.restype = ctypes.c_char_p
+    return lib.ref_shim_blas_name().decode()
+
+
 def calculate(bedfile: str, n_snp: int, n_org: int, positions, ld_wind: float, maf: float,
               std_thr: float, rsq_thr: float, flavour: int = 64) -> dict:
     lib = _lib(flavour)

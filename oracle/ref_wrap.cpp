@@ -45,3 +45,6 @@ extern "C" int ref_ld_calculate(const char* bedfile, int n_snp, int n_org, doubl
 }
 
 extern "C" int ref_ld_elem_bytes() { return (int)sizeof(ARMA_SHIM_ELEM); }
+
+// which dot the float build is using right now: "shim loop (omp simd)" or the BLAS symbol it resolved (NLDSC_REF_BLAS)
+extern "C" const char* ref_shim_blas_name() { return arma::detail::blas().name; }
