@@ -50,6 +50,22 @@ def ext_path() -> str:
     return os.path.join(HERE, "_ldscore" + sysconfig.get_config_var("EXT_SUFFIX"))
 
 
+def build_variant(tag: str, defines: list[str]) -> str:
+    """An A/B build of the same sources with extra -D flags -> nldsc_b200/libnldsc_ld_<tag>.so (select it with NLDSC_LIB).
+    Measurement only: never loaded unless asked for."""
+    obj = os.path.join(OBJ, tag)
+    os.makedirs(obj, exist_ok=True)
+    nvcc = _nvcc()
+    objs = []
+    for src, extra in SOURCES.items():
+        o = os.path.join(obj, src.replace(".cu", ".o"))
+        objs.append(o)
+        _run([nvcc] + ARCH + COMMON + extra + ["-D" + d for d in defines] + ["-c", os.path.join(CSRC, src), "-o", o])
+    out = os.path.join(HERE, f"libnldsc_ld_{tag}.so")
+    _run([nvcc] + ARCH + ["-shared", "-o", out] + objs)
+    return out
+
+
 def build_native(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     nvcc = _nvcc()

@@ -15,7 +15,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libnldsc_ld.so")
+LIB_PATH = os.environ.get("NLDSC_LIB") or os.path.join(HERE, "libnldsc_ld.so")      # NLDSC_LIB: an A/B build of the same sources
 
 EXPORTS = [
     "nldsc_ld_calculate", "nldsc_ld_calculate_packed", "nldsc_ld_session_create",

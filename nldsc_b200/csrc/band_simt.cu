@@ -141,8 +141,14 @@ finalize_kernel(const FinalizeArgs a) {
     // sums of q_ij -> sums of r2adj (epilogue.cuh): k0 * count + c * w_i^2 * sum q
     const double w = a.coef[row].inv_sd * a.inv_n;
     const double cw2 = a.adj_c * (w * w), k0 = adj_k0(a.n);
+#ifdef NLDSC_EPILOGUE_V1
+    a.l2[o] = 1.0 + add;
+    a.l2d[o] = dom;
+    (void)cw2; (void)k0;
+#else
     a.l2[o] = 1.0 + (k0 * wsa + cw2 * add);                        // ldscalc.h:27-28,38
     a.l2d[o] = k0 * wsd + cw2 * dom;
+#endif
     a.wsa[o] = wsa; a.wsd[o] = wsd; a.wsde[o] = wsde;
 }
 

@@ -111,6 +111,31 @@ __device__ __forceinline__ void mbar_wait_idle(uint64_t* bar, uint32_t parity, u
     }
     mbar_wait_slow(addr, parity, site, 256);
 }
+// Fused launch: block until ring rows [0, need) are unpacked and their statistics final (BandArgs::ready_rows, published
+// by launch_publish_rows after every chunk).  `seen` caches the last value read, so a tile whose rows are already known
+// to be there costs nothing.  A wait can legitimately last as long as the upload of the shard (seconds from a cold disk),
+// so its bound is 10 x the barrier bound; a failed upload publishes 0xFFFFFFFF, which releases every waiter.
+__device__ __noinline__ uint32_t wait_rows_slow(const uint32_t* p, uint32_t need) {
+    const unsigned long long t0 = global_ns();
+    for (uint32_t spins = 0;; ++spins) {
+        uint32_t v;
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+        if (v >= need) return v;
+        __nanosleep(400);
+        if ((spins & 0xFFu) == 0xFFu && global_ns() - t0 > 10 * kHangNs) hang_trap(10);
+    }
+}
+__device__ __forceinline__ void wait_rows(const uint32_t* p, uint32_t need, uint32_t& seen) {
+    if (p == nullptr || seen >= need) return;
+    seen = wait_rows_slow(p, need);
+}
+// rows a supertile reads: its i-blocks and its j-block(s)
+__device__ __forceinline__ uint32_t tile_rows_needed(const Tile& tl, bool two) {
+    int32_t need = tl.i0[0] + kBlk;
+    if (tl.i0[1] != kDeadBlock) need = max(need, tl.i0[1] + kBlk);
+    return static_cast<uint32_t>(max(need, tl.j0 + (two ? 2 : 1) * kBlk));
+}
+
 // remote arrive on the leader (even) CTA's copy of `bar`
 __device__ __forceinline__ void mbar_arrive_leader(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerMask) : "memory");
@@ -413,13 +438,17 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         // ===== TMA producer: own A block, own half of one or two B blocks =====
         if (lane == 0) {
             int stage = 0;
-            uint32_t phase = 0;
+            uint32_t phase = 0, seen = 0;
             for (int t = pair; t < args.n_tiles; t += n_pairs) {
                 const Tile tl = args.tiles[t];
                 const int32_t a_row = tl.a_row[rank];
                 const int32_t b_row = tl.b_row + 32 * static_cast<int32_t>(rank);
                 const bool two = tl.b_row2 >= 0;
                 const int32_t b_row2 = tl.b_row2 + 32 * static_cast<int32_t>(rank);
+                if (args.ready_rows != nullptr && seen < tile_rows_needed(tl, two)) {
+                    wait_rows(args.ready_rows, tile_rows_needed(tl, two), seen);
+                    asm volatile("fence.proxy.async;" ::: "memory");      // the rows were written through the generic proxy
+                }
                 const uint32_t bytes = 2u * (kABytes + (two ? 2 : 1) * kBBytes);          // both CTAs' bytes
                 for (int k = 0; k < args.k_steps; ++k) {
                     mbar_wait(&empty[stage], phase ^ 1, 5);
@@ -490,11 +519,14 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         const bool is_g = lane < 16;
         const int s = 16 * q + (lane & 15);
         int n = 0;
+        uint32_t seen = 0;
         for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
             const Tile tl = args.tiles[t];
             const int32_t i0 = tl.i0[rank];
-            const RowCtx row = load_row_ctx(args, i0 + s);
             const int n_j = tl.b_row2 >= 0 ? 2 : 1;
+            // fused launch: the per-SNP coefficients / flags of the tile's rows are final only once its chunk's stats ran
+            wait_rows(args.ready_rows, tile_rows_needed(tl, n_j == 2), seen);
+            const RowCtx row = load_row_ctx(args, i0 + s);
             mbar_wait_idle(tfull, n & 1, 8);
             tc_fence_after();
 #pragma unroll 1
@@ -507,7 +539,7 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                     const int c = 2 * half + c2;
                     // the 16 j-SNPs of this pass lie outside the window of every row of the warp (the corners of the
                     // first / last supertiles of an i-pair, a fifth of all pair slots at a 1 cM window): nothing to add
-                    if (!__any_sync(0xFFFFFFFFu, row_needs(row, j0 + 16 * c, j0 + 16 * c + 15))) continue;
+                    if (!args.no_skip && !__any_sync(0xFFFFFFFFu, row_needs(row, j0 + 16 * c, j0 + 16 * c + 15))) continue;
                     const uint32_t col = 96 * half + 16 * c2;
                     int32_t vm[16], vh[16], va[16];
                     tmem_ld16(taddr + col, vm);
@@ -619,7 +651,8 @@ namespace {
 uint32_t* g_hang_host[64] = {nullptr};
 std::mutex g_hang_mu;
 const char* const kSiteNames[] = {"?", "narrow/producer:empty", "narrow/mma:tmem-empty", "narrow/mma:full", "narrow/epilogue:tmem-full",
-                                  "wide/producer:empty", "wide/mma:tmem-empty", "wide/mma:full", "wide/epilogue:tmem-full", "i8-peak"};
+                                  "wide/producer:empty", "wide/mma:tmem-empty", "wide/mma:full", "wide/epilogue:tmem-full", "i8-peak",
+                                  "rows-ready (the chunk's unpack never published)"};
 void install_hang_word() {
     int dev = 0;
     CUDA_CHECK(cudaGetDevice(&dev));

@@ -77,6 +77,9 @@ struct BandArgs {
     double thr_num;             // (rsq_thr - k0) / adj_c with k0 = 1 - adj_c: r2adj > rsq_thr  <=>  w_i^2 q_ij > thr_num (epilogue.cuh)
     Partials part;
     int32_t* dump;              // optional raw accumulators [tile][rank][128][192] (parity hook)
+    const uint32_t* ready_rows; // fused launch (one band launch per shard): ring rows [0, *ready_rows) are unpacked and their
+                                // per-SNP statistics final; published after every chunk's unpack + stats.  null = everything is ready
+    int32_t no_skip;            // A/B: score the out-of-window column groups too (NLDSC_NOSKIP=1)
     int32_t commit2;            // experiment: release the operand ring two stages at a time (16 MMAs between commits)
     int32_t probe;              // measurement hook: 0 = normal, 1 = MMAs without TMA loads, 2 = TMA loads without MMAs, 3 = epilogue only
 };
@@ -108,6 +111,7 @@ void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_r
 void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st,
                     int32_t n_pad = 0, unsigned long long* total = nullptr);   // rows n..n_pad-1 get the empty window (1, 0)
 void launch_copy16(const void* src, void* dst, size_t bytes, cudaStream_t st);   // SM copy, either side may be pinned host memory
+void launch_publish_rows(uint32_t* ready_rows, uint32_t value, cudaStream_t st);   // release-store for BandArgs::ready_rows
 void launch_zero_rows(int8_t* planes, int64_t plane_stride, int32_t npad, int32_t row0,
                       int32_t n_rows, cudaStream_t st);
 

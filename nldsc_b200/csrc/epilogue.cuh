@@ -23,6 +23,9 @@ struct RowCtx {
     double mu;      // mu_i
     double nxbar;   // n * xbar_i
     double thr;     // q_ij > thr  <=>  r2adj(dom) > rsq_thr   (+inf for a dropped row)
+#ifdef NLDSC_EPILOGUE_V1
+    double w;
+#endif
     int32_t lo, hi; // inclusive window (shard-local SNP indices)
     int32_t gi;     // this row's SNP index
     bool keep;
@@ -45,11 +48,17 @@ __device__ __forceinline__ RowCtx load_row_ctx(const BandArgs& a, int32_t gi) {
         r.nxbar = a.n * c.xbar;
         const double w = c.inv_sd * a.inv_n;
         r.thr = a.thr_num / (w * w);
+#ifdef NLDSC_EPILOGUE_V1
+        r.w = w;
+#endif
         r.lo = a.win_lo[gi];
         r.hi = a.win_hi[gi];
         r.keep = (a.flags[gi] & kFlagKeep) != 0;
     } else {
         r.mu = r.nxbar = r.thr = 0.0;
+#ifdef NLDSC_EPILOGUE_V1
+        r.w = 0.0;
+#endif
         r.lo = 1; r.hi = 0;
         r.keep = false;
     }
@@ -93,6 +102,25 @@ __device__ __forceinline__ void pair_eval(const BandArgs& a, const RowCtx& r, in
 
     // additive: ldscalc.h:38
     const double sa = (dGgg + mu_j * dGgm) + r.mu * (dGmg + mu_j * dGmm) - r.nxbar * xbar_j;
+#ifdef NLDSC_EPILOGUE_V1      // A/B build only: r2adj evaluated pair by pair (round-1 arithmetic)
+    {
+        const double ra = sa * r.w * inv_sd_j;
+        const double r2a = ra * ra;
+        const double adj_a = 1.0 - (1.0 - r2a) * a.adj_c;
+        acc.add += use ? adj_a : 0.0;
+        acc.wsa += use ? 1 : 0;
+        const double u0 = ch * dGgh + ca * dGga + cm * dGgm;
+        const double u1 = ch * dGmh + ca * dGma + cm * dGmm;
+        const double sd = (u0 + r.mu * u1) - r.nxbar * rbar_j;
+        const double rd = sd * r.w * inv_rsd_j;
+        const double r2d = rd * rd;
+        const double adj = 1.0 - (1.0 - r2d) * a.adj_c;
+        acc.dom += use_d ? adj : 0.0;
+        acc.wsd += use_d ? 1 : 0;
+        acc.wsde += (use_d && adj > a.rsq_thr) ? 1 : 0;
+        return;
+    }
+#endif
     const double ta = sa * inv_sd_j;
     acc.add += use ? ta * ta : 0.0;
     acc.wsa += use ? 1 : 0;

@@ -74,4 +74,16 @@ void launch_copy16(const void* src, void* dst, size_t bytes, cudaStream_t st) {
     CUDA_CHECK(cudaGetLastError());
 }
 
+// One thread: *ready_rows = value with release semantics at GPU scope -- everything the stream ran before this kernel
+// (unpack, stats) is visible to a band-kernel thread that reads the value with an acquire load (band_tc.cu wait_rows).
+__global__ void publish_rows_kernel(uint32_t* ready_rows, uint32_t value) {
+    __threadfence();
+    asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(ready_rows), "r"(value) : "memory");
+}
+
+void launch_publish_rows(uint32_t* ready_rows, uint32_t value, cudaStream_t st) {
+    publish_rows_kernel<<<1, 1, 0, st>>>(ready_rows, value);
+    CUDA_CHECK(cudaGetLastError());
+}
+
 }  // namespace nldsc

@@ -861,6 +861,16 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     s->plane_rows = cap;
     s->d_planes = amalloc<int8_t>(s->arena, static_cast<size_t>(cap) * row_bytes);
     tr.lap("plane ring");
+    // Fused launch (ONE band launch per shard, fed by a device-side "rows ready" counter instead of one launch per
+    // chunk): needs the ring to hold the whole shard (nothing is ever overwritten), the per-tile partial sums of ALL
+    // chunks at once (7 KB per 64 x 64 SNP-pair block: bounded to 1.5 GB), and the wide kernel with short rows
+    // (long rows: unpack and band take turns, and the per-chunk ramps are negligible beside 30 ms band launches).
+    {
+        const char* fu = getenv("NLDSC_FUSED");
+        const size_t part_bytes = static_cast<size_t>(tiles_bound) * 4 * kBlk * 28;
+        s->fused_ok = s->wide && !(fu && fu[0] == '0') && cap == n_load_pad && part_bytes <= (size_t(3) << 29) &&
+                      s->npad / kKAlign < 512;
+    }
 
     // ---- chunks: greedy runs of i-blocks whose column span fits the ring
     // Chunk size: 8,192 rows measured best on configs[1] once consecutive band launches overlap (two streams): 3.65 ms
@@ -899,6 +909,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     tiles.clear();
     tile_begin.clear();
     int32_t unpacked_to = jb_lo[0] * kBlk;   // rows below the first needed column never enter the ring
+    int32_t slot_base = 0;
     // supertiles of the i-block pair starting at block k when the chunk ends at e
     auto pair_tiles = [&](int32_t k, int32_t e) { return (k + 1 < e ? jb_hi[k + 1] : jb_hi[k]) - jb_lo[k] + 1; };
     for (int32_t b = 0; b < n_ib;) {
@@ -936,7 +947,10 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         }
         ramp_rows = std::min(chunk_rows, ramp_rows * 2);
         // e > b is guaranteed by cap >= max_span
-        const int32_t col1 = (jb_hi[e - 1] + 1) * kBlk;
+        int32_t col1 = (jb_hi[e - 1] + 1) * kBlk;
+        // fused launch: a band CTA reads per-SNP flags (1 byte each) of rows that are final while later rows are still
+        // being written; with chunk ends on 128-row boundaries no 128-byte line ever holds both kinds
+        if (s->fused_ok) col1 = std::min(n_load_pad, (col1 + 127) / 128 * 128);
         c.n_iblocks = e - b;
         c.new_row0 = std::max(unpacked_to, col0);
         c.new_row1 = std::max(col1, c.new_row0);
@@ -974,13 +988,15 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
                     t.a_row[1] = two ? static_cast<int32_t>(t.i0[1] % cap) : t.a_row[0];
                     t.j0 = ja * kBlk;
                     t.b_row = static_cast<int32_t>(t.j0 % cap);
-                    t.slot = slot0[(k - b) / 2] + (ja - lo_k);
+                    t.slot = (s->fused_ok ? slot_base : 0) + slot0[(k - b) / 2] + (ja - lo_k);
                     t.b_row2 = jz > ja ? static_cast<int32_t>((static_cast<int64_t>(ja + 1) * kBlk) % cap) : -1;
                     tiles.push_back(t);
                 }
             }
         }
         s->max_chunk_slots = std::max(s->max_chunk_slots, nslots_chunk);
+        c.slot_base = slot_base;                         // fused plans: where the chunk's partials start
+        slot_base += nslots_chunk;
         tile_begin.push_back(nslots_chunk);
         c.n_tiles = static_cast<int32_t>(tiles.size() - c.tile0);
         s->max_chunk_tiles = std::max(s->max_chunk_tiles, c.n_tiles);
@@ -1011,17 +1027,26 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         launch_copy16(h + 2 * b_win, s->d_tiles, b_tiles, st);
         launch_copy16(h + 2 * b_win + b_tiles, s->d_tile_begin, b_tb, st);
     }
-    const size_t np = static_cast<size_t>(s->max_chunk_slots) * 4 * kBlk;      // [slot][rank][half][row]
+    // [slot][rank][half][row]; fused plans keep every chunk's partials (chunk c at slot_base[c]), the others two chunks' worth
+    const size_t np = static_cast<size_t>(s->fused_ok ? slot_base : s->max_chunk_slots) * 4 * kBlk;
+    if (s->fused_ok) {
+        s->d_ready = amalloc<uint32_t>(s->arena, 4);
+        CUDA_CHECK(cudaMemsetAsync(s->d_ready, 0, 16, st));
+    }
     s->part.add = amalloc<double>(s->arena, np);
     s->part.dom = amalloc<double>(s->arena, np);
     s->part.wsa = amalloc<int32_t>(s->arena, np);
     s->part.wsd = amalloc<int32_t>(s->arena, np);
     s->part.wsde = amalloc<int32_t>(s->arena, np);
-    s->part2.add = amalloc<double>(s->arena, np);
-    s->part2.dom = amalloc<double>(s->arena, np);
-    s->part2.wsa = amalloc<int32_t>(s->arena, np);
-    s->part2.wsd = amalloc<int32_t>(s->arena, np);
-    s->part2.wsde = amalloc<int32_t>(s->arena, np);
+    if (s->fused_ok) {
+        s->part2 = s->part;                           // every chunk has its own region: no double buffer
+    } else {
+        s->part2.add = amalloc<double>(s->arena, np);
+        s->part2.dom = amalloc<double>(s->arena, np);
+        s->part2.wsa = amalloc<int32_t>(s->arena, np);
+        s->part2.wsd = amalloc<int32_t>(s->arena, np);
+        s->part2.wsde = amalloc<int32_t>(s->arena, np);
+    }
     if (!s->use_simt) s->maps = band_maps_create(s->d_planes, s->plane_rows, s->npad);
     // the plan is consumed by kernels on the session's own stream or on a caller's stream
     s->ev_planned = ev_get(s->device, false);
@@ -1072,7 +1097,56 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     const bool turns = overlap && s->wide && (wo ? wo[0] == '0' : s->npad / kKAlign >= 512);
     const int32_t commit2 = env_size("NLDSC_COMMIT2", 0) != 0 ? 1 : 0;
     const char* bsn = getenv("NLDSC_BAND_STREAMS");
-    const bool two_band = overlap && !(bsn && bsn[0] == '1') && s->chunks.size() > 1;
+    // ONE band launch for the whole shard (plan permitting): the persistent kernel starts now and every CTA pair waits,
+    // tile by tile, for the rows it needs to be published by the unpack stream -- no per-chunk launch ramp, one
+    // partial last wave per shard instead of one per chunk, and with a concurrent upload the tensor work follows
+    // the bytes as they land.  Needs the second stream (the kernel would wait for work queued behind itself).
+    const bool fused = s->fused_ok && overlap && !turns && !s->use_simt && s->wide;
+    const bool two_band = !fused && overlap && !(bsn && bsn[0] == '1') && s->chunks.size() > 1;
+    auto band_args = [&](const Tile* tiles, int32_t n_tiles, const Partials& part) {
+        BandArgs a{};
+        a.tiles = tiles;
+        a.n_tiles = n_tiles;
+        a.k_steps = s->npad / kKAlign;
+        a.coef = s->d_coef;
+        a.flags = s->d_flags;
+        a.win_lo = s->d_win_lo;
+        a.win_hi = s->d_win_hi;
+        a.n_load = s->n_load;
+        a.n = n;
+        a.inv_n = 1.0 / n;
+        a.adj_c = (n - 1.0) / (n - 2.0);
+        a.rsq_thr = s->rsq_thr;
+        a.thr_num = (s->rsq_thr - (1.0 - a.adj_c)) / a.adj_c;
+        a.part = part;
+        a.dump = nullptr;
+        a.commit2 = commit2;
+        a.no_skip = env_size("NLDSC_NOSKIP", 0) != 0 ? 1 : 0;
+        return a;
+    };
+    auto finalize_chunk = [&](const Chunk& c, const Partials& part, cudaStream_t fs) {
+        FinalizeArgs f{};
+        f.tile_begin = s->d_tile_begin + c.tb0;
+        f.iblock0 = c.iblock0;
+        f.n_iblocks = c.n_iblocks;
+        f.own_begin = s->own_begin;
+        f.own_end = s->own_end;
+        f.part = part;
+        f.flags = s->d_flags;
+        f.coef = s->d_coef;
+        f.n = n;
+        f.inv_n = 1.0 / n;
+        f.adj_c = (n - 1.0) / (n - 2.0);
+        f.l2 = s->d_l2;
+        f.l2d = s->d_l2d;
+        f.wsa = s->d_wsa;
+        f.wsd = s->d_wsd;
+        f.wsde = s->d_wsde;
+        SpanScope sc(s, fs, kFamFinalize);
+        launch_finalize(f, fs);
+        ++s->launches;
+    };
+    if (fused) CUDA_CHECK(cudaMemsetAsync(s->d_ready, 0, sizeof(uint32_t), st));    // before the fork: publishes come after it
     if (overlap) {
         CUDA_CHECK(cudaEventRecord(s->ev_fork, st));
         CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_fork, 0));
@@ -1082,7 +1156,15 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             s->ev_band.push_back(ev_get(s->device, false));
         }
     }
+    if (fused) {
+        BandArgs a = band_args(s->d_tiles, static_cast<int32_t>(s->h_tiles.size()), s->part);
+        a.ready_rows = s->d_ready;
+        SpanScope sc(s, st, kFamBand);
+        launch_band_tc_wide(s->maps, a, s->sm_count, st);
+        ++s->launches;
+    }
     int32_t next_piece = 0;                 // pieces below this one have been waited for on the unpack stream
+    try {
     for (size_t ci = 0; ci < s->chunks.size(); ++ci) {
         const Chunk& c = s->chunks[ci];
         const bool odd = two_band && (ci & 1);
@@ -1131,27 +1213,18 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
                          s->d_maf, s->d_rstd, us, s->d_unused);
             ++s->launches;
         }
+        if (fused) {
+            // the chunk's rows (planes, coefficients, flags) are final: let the waiting CTA pairs at them
+            launch_publish_rows(s->d_ready, static_cast<uint32_t>(c.new_row1), us);
+            ++s->launches;
+            continue;
+        }
         if (overlap) {
             CUDA_CHECK(cudaEventRecord(s->ev_unpacked[ci], us));
             CUDA_CHECK(cudaStreamWaitEvent(bs, s->ev_unpacked[ci], 0));
         }
-        BandArgs a{};
-        a.tiles = s->d_tiles + c.tile0;
-        a.n_tiles = c.n_tiles;
-        a.k_steps = s->npad / kKAlign;
-        a.coef = s->d_coef;
-        a.flags = s->d_flags;
-        a.win_lo = s->d_win_lo;
-        a.win_hi = s->d_win_hi;
-        a.n_load = s->n_load;
-        a.n = n;
-        a.inv_n = 1.0 / n;
-        a.adj_c = (n - 1.0) / (n - 2.0);
-        a.rsq_thr = s->rsq_thr;
-        a.thr_num = (s->rsq_thr - (1.0 - a.adj_c)) / a.adj_c;
-        a.part = odd ? s->part2 : s->part;
-        a.dump = nullptr;
-        a.commit2 = commit2;
+        const Partials& part = (odd && !s->fused_ok) ? s->part2 : s->part;
+        const BandArgs a = band_args(s->d_tiles + c.tile0, c.n_tiles, part);
         {
             SpanScope sc(s, bs, kFamBand);
             if (s->use_simt)
@@ -1161,27 +1234,25 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             ++s->launches;
         }
         if (overlap) CUDA_CHECK(cudaEventRecord(s->ev_band[ci], bs));
-        FinalizeArgs f{};
-        f.tile_begin = s->d_tile_begin + c.tb0;
-        f.iblock0 = c.iblock0;
-        f.n_iblocks = c.n_iblocks;
-        f.own_begin = s->own_begin;
-        f.own_end = s->own_end;
-        f.part = odd ? s->part2 : s->part;
-        f.flags = s->d_flags;
-        f.coef = s->d_coef;
-        f.n = n;
-        f.inv_n = 1.0 / n;
-        f.adj_c = (n - 1.0) / (n - 2.0);
-        f.l2 = s->d_l2;
-        f.l2d = s->d_l2d;
-        f.wsa = s->d_wsa;
-        f.wsd = s->d_wsd;
-        f.wsde = s->d_wsde;
-        {
-            SpanScope sc(s, bs, kFamFinalize);
-            launch_finalize(f, bs);
-            ++s->launches;
+        // fused-capable plans number their slots shard-wide: the chunk's partials start at its slot_base
+        Partials fp = part;
+        if (s->fused_ok) {
+            const size_t o = static_cast<size_t>(c.slot_base) * 4 * kBlk;
+            fp.add += o; fp.dom += o; fp.wsa += o; fp.wsd += o; fp.wsde += o;
+        }
+        finalize_chunk(c, fp, bs);
+    }
+    } catch (...) {
+        // a failed upload: the fused band kernel is already waiting for rows that will never be published
+        if (fused) launch_publish_rows(s->d_ready, 0xFFFFFFFFu, s->band2_stream);
+        throw;
+    }
+    if (fused) {
+        for (const Chunk& c : s->chunks) {
+            Partials fp = s->part;
+            const size_t o = static_cast<size_t>(c.slot_base) * 4 * kBlk;
+            fp.add += o; fp.dom += o; fp.wsa += o; fp.wsd += o; fp.wsde += o;
+            finalize_chunk(c, fp, st);
         }
     }
     if (two_band) {

@@ -31,6 +31,7 @@ struct Chunk {
     int64_t tile0;        // offset into the tile list
     int32_t n_tiles;
     int32_t tb0;          // offset into tile_begin (n_iblocks + 1 entries, relative to tile0)
+    int32_t slot_base;    // fused plans: first partial slot of the chunk (its tiles' slots already include it)
 };
 
 // Device workspace of one session: a bump allocator over a few large cudaMalloc blocks that are
@@ -92,6 +93,8 @@ struct nldsc_ld_session {
     double maf_thr = 0, std_thr = 0, rsq_thr = 0;
     bool use_simt = false;
     bool wide = false;                        // band_tc_wide_kernel: two j-blocks per supertile (N >= 65,536, or NLDSC_WIDE=1)
+    bool fused_ok = false;                    // the plan allows ONE band launch per shard (session_plan); run() decides
+    uint32_t* d_ready = nullptr;              // fused launch: ring rows [0, *d_ready) are unpacked, their statistics final
     bool upload_started = false;
     bool planned = false;
 

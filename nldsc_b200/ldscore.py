@@ -241,7 +241,8 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     maf = _unit_interval(maf_thr, 1.0, "Minor allele frequency")
     std = _unit_interval(std_thr, 1.0, "standard deviation threshold")
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-    if "NLDSC_READERS" not in os.environ and n_dev > 1:
+    own_readers = "NLDSC_READERS" not in os.environ and n_dev > 1
+    if own_readers:
         os.environ["NLDSC_READERS"] = str(max(1, min(4, cores // n_dev)))
 
     # ---- 1. parse (processes) beside the device warm-up; the GPU threads below start on a chromosome as soon as ITS
@@ -312,6 +313,8 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     for t in threads:
         t.join()
     phases["score_s"] = time.perf_counter() - t0
+    if own_readers:
+        os.environ.pop("NLDSC_READERS", None)
     phases["parse_s"] = parse_done[0]                # when the last parse finished, from the start (overlaps the scoring)
     pool.shutdown()
     t0 = time.perf_counter()

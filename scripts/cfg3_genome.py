@@ -1,6 +1,7 @@
 """BASELINE.json configs[2]: N=50,000 x 5 chromosome bfiles of 100,000 SNPs, 2% missing, 1 cM window, scored by the
 genome driver (one process, one host thread per GPU, .bed files read from disk) on the GPUs of this box.
-Writes gpurun_out/cfg3_genome.json.   usage: cfg3_genome.py [gpus] [n_snp_per_chromosome]
+Writes gpurun_out/cfg3_genome_<gpus>gpu.json.   usage: cfg3_genome.py [gpus[,gpus...]] [n_snp_per_chromosome]
+(several GPU counts: the bfiles are generated once and scored with each count in turn)
 With NLDSC_GENOME=ukb: configs[3] shape instead -- N=315,599, 22 chromosomes with SNP counts proportional to their genetic
 lengths, `n_snp_per_chromosome` x 22 SNPs in total (the full 1.2M-SNP genome is 94.7 GB; this is a cut that fits a scratch disk)."""
 import dataclasses, json, os, shutil, sys, tempfile, time
@@ -10,7 +11,7 @@ import pandas as pd
 import torch
 from nldsc_b200 import ldscore, synth
 
-gpus = int(sys.argv[1]) if len(sys.argv) > 1 else torch.cuda.device_count()
+gpu_counts = [int(x) for x in sys.argv[1].split(",")] if len(sys.argv) > 1 else [torch.cuda.device_count()]
 n_snp = int(sys.argv[2]) if len(sys.argv) > 2 else 100_000
 N = 50_000
 CHROMS = list(range(1, 6))
@@ -39,26 +40,28 @@ for c in CHROMS:
 torch.cuda.empty_cache()
 gen_s = time.perf_counter() - t0
 import hashlib
-runs, digests = [], []
-for rep in range(2):
-    shutil.rmtree(f"{d}/out", ignore_errors=True)
-    t0 = time.perf_counter()
-    summ = ldscore.estimate_lds_genome(f"{d}/g.@", 1.0, "cm", 1e-4, 1e-5, out_dir=f"{d}/out", gpus=gpus)
-    runs.append(time.perf_counter() - t0)
-    digests.append(hashlib.sha256(b"".join(open(f"{d}/out/{c}.L2", "rb").read() for c in range(1, 6))).hexdigest())
-pairs = 0
-for c in CHROMS:
-    df = pd.read_csv(f"{d}/out/{c}.L2", sep="\t")
-    pairs += int(df["WSA"][df["WSA"] >= 0].sum())
-total_snps = sum(SIZES.values())
-phases = dict(summ.attrs.get("phases", {}))
-busy = {str(k): v for k, v in summ.attrs.get("per_gpu_busy_s", {}).items()}
-rec = {"phases_last_run": phases, "per_gpu_busy_s_last_run": busy, "config": "%s: N=%d x %d chromosomes, %d SNPs in total, 2%% missing, 1 cM" % (TAG, N, len(CHROMS), total_snps), "gpus": gpus,
-       "bed_bytes": total_snps * ((N + 3) // 4),
-       "pairs": pairs, "wall_s": runs, "outputs_identical_across_runs": digests[0] == digests[1], "l2_sha256": digests[0], "pairs_per_s_wall": pairs / min(runs), "generate_s": gen_s,
-       "per_chromosome": summ.drop(columns=["file"]).to_dict(orient="records"),
-       "note": "wall time of estimate_lds_genome: .bim/.fam parsing, .bed read from the page cache, GPU scoring, %.5f .L2 + .M files written"}
-print(json.dumps(rec))
-os.makedirs("gpurun_out", exist_ok=True)
-json.dump(rec, open("gpurun_out/%s_%dgpu.json" % (TAG, gpus), "w"), indent=1)
+for gpus in gpu_counts:
+    runs, digests = [], []
+    for rep in range(2):
+        shutil.rmtree(f"{d}/out", ignore_errors=True)
+        t0 = time.perf_counter()
+        summ = ldscore.estimate_lds_genome(f"{d}/g.@", 1.0, "cm", 1e-4, 1e-5, out_dir=f"{d}/out", gpus=gpus)
+        runs.append(time.perf_counter() - t0)
+        digests.append(hashlib.sha256(b"".join(open(f"{d}/out/{c}.L2", "rb").read() for c in range(1, 6))).hexdigest())
+    pairs = 0
+    for c in CHROMS:
+        df = pd.read_csv(f"{d}/out/{c}.L2", sep="\t")
+        pairs += int(df["WSA"][df["WSA"] >= 0].sum())
+    total_snps = sum(SIZES.values())
+    phases = dict(summ.attrs.get("phases", {}))
+    busy = {str(k): v for k, v in summ.attrs.get("per_gpu_busy_s", {}).items()}
+    rec = {"phases_last_run": phases, "per_gpu_busy_s_last_run": busy, "config": "%s: N=%d x %d chromosomes, %d SNPs in total, 2%% missing, 1 cM" % (TAG, N, len(CHROMS), total_snps), "gpus": gpus,
+           "bed_bytes": total_snps * ((N + 3) // 4),
+           "pairs": pairs, "wall_s": runs, "outputs_identical_across_runs": digests[0] == digests[1], "l2_sha256": digests[0], "pairs_per_s_wall": pairs / min(runs), "generate_s": gen_s,
+           "per_chromosome": summ.drop(columns=["file"]).to_dict(orient="records"),
+           "note": "wall time of estimate_lds_genome: .bim/.fam parsing, .bed read from the page cache, GPU scoring, %.5f .L2 + .M files written"}
+    print(json.dumps(rec))
+    os.makedirs("gpurun_out", exist_ok=True)
+    json.dump(rec, open("gpurun_out/%s_%dgpu.json" % (TAG, gpus), "w"), indent=1)
+
 shutil.rmtree(d, ignore_errors=True)

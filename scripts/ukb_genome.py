@@ -73,7 +73,7 @@ print(f"[ukb] {gpus} GPUs, {sum(SIZES.values())} SNPs, {total_bytes / 1e9:.1f} G
 capi.warmup(0, n_threads)
 order = sorted(CHROMS, key=lambda c: -SIZES[c])
 lock = threading.Lock()
-oracle_gate = threading.Semaphore(2)
+oracle_gate = threading.Semaphore(6)
 records, checks, errors = {}, [], []
 hosts = {}
 
@@ -159,8 +159,6 @@ if mode == "resident":
     # ---- phase 2: THE timed region -- all 22 chromosomes, host memory -> GPUs -> host arrays
     results = {}
     q = queue.Queue()
-    for c in order:
-        q.put(c)
     busy = {d: 0.0 for d in range(gpus)}
 
     def score_worker(device):
@@ -196,7 +194,7 @@ if mode == "resident":
     score_wall = walls[-1]
     t0 = time.perf_counter()
     th = [threading.Thread(target=lambda cs=cs: [oracle_check(c, hosts[c][0], hosts[c][1], results[c]) for c in cs])
-          for cs in (order[k::4] for k in range(4))]
+          for cs in (order[k::6] for k in range(6))]
     [t.start() for t in th]
     [t.join() for t in th]
     oracle_s = time.perf_counter() - t0
