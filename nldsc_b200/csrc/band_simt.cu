@@ -159,4 +159,9 @@ void launch_finalize(const FinalizeArgs& a, cudaStream_t st) {
     CUDA_CHECK(cudaGetLastError());
 }
 
+void preload_finalize_kernels() {
+    cudaFuncAttributes fa;
+    CUDA_CHECK(cudaFuncGetAttributes(&fa, finalize_kernel));
+}
+
 }  // namespace nldsc

@@ -122,6 +122,9 @@ void band_maps_destroy(BandMaps*);
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);
 void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);   // tiles carry b_row2
 void install_band_kernels();   // per device: function attributes + module load of the band kernels (warm-up)
+void preload_unpack_kernels(); // per device: force the (lazily loaded) images of the unpack.cu / plan.cu / band_simt.cu kernels in
+void preload_plan_kernels();
+void preload_finalize_kernels();
 void launch_i8_peak(int iters, int n_cols, int per_commit, int depth, int sm_count, cudaStream_t st);   // measurement only
 void launch_band_simt(const int8_t* planes, int64_t plane_stride, int32_t npad,
                       const BandArgs& args, cudaStream_t st);

@@ -86,4 +86,10 @@ void launch_publish_rows(uint32_t* ready_rows, uint32_t value, cudaStream_t st) 
     CUDA_CHECK(cudaGetLastError());
 }
 
+void preload_plan_kernels() {
+    cudaFuncAttributes fa;
+    CUDA_CHECK(cudaFuncGetAttributes(&fa, publish_rows_kernel));
+    CUDA_CHECK(cudaFuncGetAttributes(&fa, copy16_kernel));
+}
+
 }  // namespace nldsc

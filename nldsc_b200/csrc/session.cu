@@ -350,6 +350,21 @@ void require_sm100(int device) {
 
 int device_sm_count(int device) { return dev_info(device).sms; }
 
+// CUDA loads kernel images lazily, at a kernel's first launch, and that load can wait for the device to go idle.  The
+// fused band launch keeps the device busy until the unpack stream has run -- so every kernel that stream launches must
+// be resident BEFORE the first fused launch, or its first launch deadlocks against the kernel that is waiting for it.
+void preload_kernels(int device) {
+    static std::mutex mu;
+    static bool done[64] = {false};
+    std::lock_guard<std::mutex> g(mu);
+    if (done[device & 63]) return;
+    install_band_kernels();
+    preload_unpack_kernels();
+    preload_plan_kernels();
+    preload_finalize_kernels();
+    done[device & 63] = true;
+}
+
 void validate_params(const nldsc_ld_params* p, bool allow_unused = false) {
     if (!p) throw InvalidArgument("params is null");
     if (p->n_snp <= 0) throw InvalidArgument("n_snp must be positive");
@@ -412,6 +427,7 @@ T* amalloc(Arena* a, size_t n) {
 int32_t floor64(int32_t x) { return x & ~63; }
 
 cudaEvent_t ev_get(int device, bool timing);     // per-device pools, defined below
+void preload_kernels(int device);
 
 struct SpanScope {
     nldsc_ld_session* s;
@@ -544,6 +560,7 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     if (device < 0 || device >= ndev) throw CudaError("CUDA device index out of range");
     CUDA_CHECK(cudaSetDevice(device));
     require_sm100(device);
+    preload_kernels(device);
 
     std::unique_ptr<nldsc_ld_session, void (*)(nldsc_ld_session*)> sp(new nldsc_ld_session, session_free);
     nldsc_ld_session* s = sp.get();
@@ -1156,13 +1173,15 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             s->ev_band.push_back(ev_get(s->device, false));
         }
     }
-    if (fused) {
+    bool band_launched = false;
+    auto launch_fused_band = [&] {
         BandArgs a = band_args(s->d_tiles, static_cast<int32_t>(s->h_tiles.size()), s->part);
         a.ready_rows = s->d_ready;
         SpanScope sc(s, st, kFamBand);
         launch_band_tc_wide(s->maps, a, s->sm_count, st);
         ++s->launches;
-    }
+        band_launched = true;
+    };
     int32_t next_piece = 0;                 // pieces below this one have been waited for on the unpack stream
     try {
     for (size_t ci = 0; ci < s->chunks.size(); ++ci) {
@@ -1217,6 +1236,9 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             // the chunk's rows (planes, coefficients, flags) are final: let the waiting CTA pairs at them
             launch_publish_rows(s->d_ready, static_cast<uint32_t>(c.new_row1), us);
             ++s->launches;
+            // the band kernel goes in once the first chunk's work is queued (it then never waits for anything that
+            // is not already on its way to the device)
+            if (!band_launched) launch_fused_band();
             continue;
         }
         if (overlap) {
@@ -1244,9 +1266,10 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     }
     } catch (...) {
         // a failed upload: the fused band kernel is already waiting for rows that will never be published
-        if (fused) launch_publish_rows(s->d_ready, 0xFFFFFFFFu, s->band2_stream);
+        if (fused && band_launched) launch_publish_rows(s->d_ready, 0xFFFFFFFFu, s->band2_stream);
         throw;
     }
+    if (fused && !band_launched) launch_fused_band();
     if (fused) {
         for (const Chunk& c : s->chunks) {
             Partials fp = s->part;

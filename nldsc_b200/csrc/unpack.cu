@@ -199,4 +199,11 @@ void launch_zero_rows(int8_t* planes, int64_t plane_stride, int32_t npad, int32_
     CUDA_CHECK(cudaGetLastError());
 }
 
+void preload_unpack_kernels() {
+    cudaFuncAttributes fa;
+    CUDA_CHECK(cudaFuncGetAttributes(&fa, stats_kernel));
+    CUDA_CHECK(cudaFuncGetAttributes(&fa, unpack_kernel));
+    CUDA_CHECK(cudaFuncGetAttributes(&fa, zero_rows_kernel));
+}
+
 }  // namespace nldsc
