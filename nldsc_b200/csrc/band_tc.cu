@@ -394,7 +394,9 @@ band_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 namespace {
 constexpr int kWStages = 5;
 constexpr int kWStageBytes = kABytes + 2 * kBBytes;          // 40 KB per CTA per stage
-constexpr int kWSmemBytes = kWStages * kWStageBytes + 1024 + 256;
+constexpr int kWCols = 2 * kBlk;                             // j-SNPs of a wide supertile
+constexpr int kWColBytes = kWCols * static_cast<int>(sizeof(SnpCoef)) + kWCols;   // their SnpCoef + flags, staged for the epilogue
+constexpr int kWSmemBytes = kWStages * kWStageBytes + 1024 + 256 + kWColBytes;
 constexpr int kWThreads = 320;                               // TMA warp, MMA warp, 8 epilogue warps
 }  // namespace
 
@@ -410,6 +412,9 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     uint64_t* tfull = empty + kWStages;        // one per CTA
     uint64_t* tempty = tfull + 1;              // leader CTA only
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
+    // the j-SNPs' constants of the supertile being scored: staged by the epilogue warps while they wait for its MMAs
+    double2* col_coef = reinterpret_cast<double2*>(smem + kWStages * kWStageBytes + 256);
+    uint8_t* col_flags = reinterpret_cast<uint8_t*>(col_coef) + kWCols * sizeof(SnpCoef);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
@@ -527,6 +532,26 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             // fused launch: the per-SNP coefficients / flags of the tile's rows are final only once its chunk's stats ran
             wait_rows(args.ready_rows, tile_rows_needed(tl, n_j == 2), seen);
             const RowCtx row = load_row_ctx(args, i0 + s);
+            // Stage the constants of the supertile's 64 or 128 j-SNPs (64 bytes + 1 flag byte each) in shared memory
+            // NOW, while the MMAs run: in the epilogue every pair needs them, and fetched pair by pair from L2 their
+            // latency was what the (exposed) epilogue spent most of its time on.  Named barrier 1 = the 8 epilogue
+            // warps: nobody overwrites the staging area while a slower warp still scores the previous supertile.
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            {
+                const int te = threadIdx.x - 64;                       // 0..255 among the epilogue threads
+                const int n_cols = n_j * kBlk;
+                for (int e = te; e < n_cols * 4; e += 256) {           // 4 double2 per SNP
+                    const int32_t gj = tl.j0 + (e >> 2);
+                    double2 v = make_double2(0.0, 0.0);
+                    if (gj < args.n_load) v = __ldg(reinterpret_cast<const double2*>(args.coef + gj) + (e & 3));
+                    col_coef[e] = v;
+                }
+                if (te < n_cols) {
+                    const int32_t gj = tl.j0 + te;
+                    col_flags[te] = gj < args.n_load ? __ldg(args.flags + gj) : uint8_t(0);
+                }
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
             mbar_wait_idle(tfull, n & 1, 8);
             tc_fence_after();
 #pragma unroll 1
@@ -558,7 +583,13 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                         const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
                         const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
                         const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
+#ifndef NLDSC_NO_COL_STAGE
+                        const double2* cj = col_coef + 4 * (kBlk * jj + jl);
+                        pair_eval_core(args, row, j0 + jl, col_flags[kBlk * jj + jl], cj[0], cj[1], cj[2], cj[3],
+                                       Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
+#else       // A/B build: the constants pair by pair from global memory, as the narrow kernel does
                         pair_eval(args, row, j0 + jl, Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
+#endif
                     }
                 }
                 if (jj == n_j - 1) {

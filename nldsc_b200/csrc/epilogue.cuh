@@ -82,17 +82,16 @@ __device__ __forceinline__ double i2d(int32_t x) {
 // Branch-free: every pair is evaluated and its terms are SELECTED in or out, so the compiler can interleave the
 // FP64 chains of the unrolled j loop (with early returns each pair cost ~1,000 cycles of exposed latency).
 // A rejected pair may compute inf / NaN (a dropped SNP has 1/sd = 0 or inf); selects never propagate them.
-__device__ __forceinline__ void pair_eval(const BandArgs& a, const RowCtx& r, int32_t gj,
-                                          int32_t Ggm, int32_t Ggh, int32_t Gga,
-                                          int32_t Gmm, int32_t Gmh, int32_t Gma, RowAcc& acc) {
+// `fj` / `c0..c3` are SNP j's flags and its 64-byte SnpCoef as four double2 (from global memory, or from the copy
+// the wide kernel stages in shared memory while its epilogue warps wait for the MMAs).
+__device__ __forceinline__ void pair_eval_core(const BandArgs& a, const RowCtx& r, int32_t gj, uint8_t fj, const double2 c0,
+                                               const double2 c1, const double2 c2, const double2 c3,
+                                               int32_t Ggm, int32_t Ggh, int32_t Gga,
+                                               int32_t Gmm, int32_t Gmh, int32_t Gma, RowAcc& acc) {
     // stream.h:145-147, tools.h:41-49: in the window, not the SNP itself; cache_[j] is false for dropped SNPs
     const bool in_win = gj >= r.lo && gj <= r.hi && gj != r.gi;
-    const int32_t gjc = in_win ? gj : 0;                        // a valid index: the loads below are unconditional
-    const uint8_t fj = __ldg(a.flags + gjc);
     const bool use = in_win && (fj & kFlagKeep);
     const bool use_d = use && (fj & kFlagDom);
-    const double2* cp = reinterpret_cast<const double2*>(a.coef + gjc);
-    const double2 c0 = __ldg(cp), c1 = __ldg(cp + 1), c2 = __ldg(cp + 2), c3 = __ldg(cp + 3);
     const double mu_j = c0.x, xbar_j = c0.y, inv_sd_j = c1.x, ch = c1.y;
     const double ca = c2.x, cm = c2.y, rbar_j = c3.x, inv_rsd_j = c3.y;
 
@@ -134,6 +133,17 @@ __device__ __forceinline__ void pair_eval(const BandArgs& a, const RowCtx& r, in
     acc.dom += use_d ? qd : 0.0;
     acc.wsd += use_d ? 1 : 0;
     acc.wsde += (use_d && qd > r.thr) ? 1 : 0;                  // tools.h:36-38 (strict)
+}
+
+// SNP j's constants straight from global memory (narrow kernel, SIMT yardstick)
+__device__ __forceinline__ void pair_eval(const BandArgs& a, const RowCtx& r, int32_t gj,
+                                          int32_t Ggm, int32_t Ggh, int32_t Gga,
+                                          int32_t Gmm, int32_t Gmh, int32_t Gma, RowAcc& acc) {
+    const bool in_win = gj >= r.lo && gj <= r.hi && gj != r.gi;
+    const int32_t gjc = in_win ? gj : 0;                        // a valid index: the loads below are unconditional
+    const uint8_t fj = __ldg(a.flags + gjc);
+    const double2* cp = reinterpret_cast<const double2*>(a.coef + gjc);
+    pair_eval_core(a, r, gj, fj, __ldg(cp), __ldg(cp + 1), __ldg(cp + 2), __ldg(cp + 3), Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
 }
 
 }  // namespace nldsc

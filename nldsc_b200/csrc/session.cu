@@ -883,9 +883,12 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // chunks at once (7 KB per 64 x 64 SNP-pair block: bounded to 1.5 GB), and the wide kernel with short rows
     // (long rows: unpack and band take turns, and the per-chunk ramps are negligible beside 30 ms band launches).
     {
+        // Measured (profiles/r02f_ab_step*.json, same box): the fused launch is SLOWER -- configs[1] 4.31 vs 3.82 ms per
+        // step, N = 2,504: 1.91 vs 1.48 -- because the CTA pairs drift apart over 70 supertiles each and stop sharing
+        // operand slices in L2, which the per-chunk launches re-align every 8,192 rows.  Opt-in (NLDSC_FUSED=1) only.
         const char* fu = getenv("NLDSC_FUSED");
         const size_t part_bytes = static_cast<size_t>(tiles_bound) * 4 * kBlk * 28;
-        s->fused_ok = s->wide && !(fu && fu[0] == '0') && cap == n_load_pad && part_bytes <= (size_t(3) << 29) &&
+        s->fused_ok = s->wide && (fu && fu[0] == '1') && cap == n_load_pad && part_bytes <= (size_t(3) << 29) &&
                       s->npad / kKAlign < 512;
     }
 

@@ -29,6 +29,8 @@ VARIANTS = [
     {"NLDSC_WIDE": "0", "NLDSC_CHUNK_ROWS": "128", "NLDSC_PLANE_BYTES": "ring"},
     {"NLDSC_CHUNK_ROWS": "128", "NLDSC_PLANE_BYTES": "ring", "NLDSC_GPUS": "2"},
     {"NLDSC_TEST_SHARDS": "3"},
+    {"NLDSC_FUSED": "1"},
+    {"NLDSC_FUSED": "1", "NLDSC_CHUNK_ROWS": "64"},
 ]
 
 
@@ -96,6 +98,7 @@ MID_VARIANTS = [
     {"NLDSC_BAND_STREAMS": "1", "NLDSC_WIDE_OVERLAP": "0"},
     {"NLDSC_FIRST_BYTES": "1000000", "NLDSC_CHUNK_BYTES": "3000000"},
     {"NLDSC_TEST_SHARDS": "4", "NLDSC_CHUNK_ROWS": "1024"},
+    {"NLDSC_FUSED": "1", "NLDSC_CHUNK_ROWS": "1024"},
 ]
 
 
