@@ -169,6 +169,10 @@ __device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {
         ::"r"(smem_u32(bar)), "h"(static_cast<uint16_t>(3))
         : "memory");
 }
+// the same commit arriving on the executing (leader) CTA's barrier only
+__device__ __forceinline__ void tc_commit_leader(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 // D[tmem, both CTAs] (+)= A[smem, 128 rows per CTA] * B[smem, 96 rows per CTA]^T, int8 x int8 -> int32
 __device__ __forceinline__ void tc_mma_i8(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                           uint32_t accumulate) {
@@ -749,7 +753,8 @@ void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_coun
 // alternating between two accumulators; at most 4 commits are in flight.
 template <int kPerCommit>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
-i8_peak_kernel(int iters, int n_cols, int depth) {
+i8_peak_kernel(int iters, int n_cols, int depth_flags) {
+    const int depth = depth_flags & 0xFF;          // bit 8: commit to the leader's barrier only (no multicast)
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     constexpr int kMaxDepth = 8;
@@ -793,7 +798,7 @@ i8_peak_kernel(int iters, int n_cols, int depth) {
 #pragma unroll
             for (int m = 0; m < kPerCommit; ++m)       // 4 K-slices into accumulator 0, then 4 into accumulator 1, ...
                 tc_mma_i8(tmem_base + ((m >> 2) & 1) * 256, a_desc + 2 * (m & 3), b_desc + 2 * (m & 3), idesc, 1u);
-            tc_commit_pair(&bar[d]);
+            if (depth_flags & 0x100) tc_commit_leader(&bar[d]); else tc_commit_pair(&bar[d]);
         }
         for (int it = iters > depth ? iters - depth : 0; it < iters; ++it) mbar_wait(&bar[it % depth], (it / depth) & 1, 9);
     }

@@ -2017,8 +2017,8 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
 int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t depth, int32_t iters, int32_t reps, float* ms_out,
                            double* tops_out, char* err, size_t errlen) {
     return guarded(err, errlen, [&] {
-        if (n_cols < 16 || n_cols > 256 || (n_cols % 16) != 0 || (per_commit != 4 && per_commit != 8 && per_commit != 16) || depth < 1 ||
-            depth > 8 || iters < 1 || reps < 1 || !ms_out)
+        if (n_cols < 16 || n_cols > 256 || (n_cols % 16) != 0 || (per_commit != 4 && per_commit != 8 && per_commit != 16) || (depth & 0xFF) < 1 ||
+            (depth & 0xFF) > 8 || iters < 1 || reps < 1 || !ms_out)
             throw InvalidArgument("bad arguments");
         usable_devices();
         const int dev = first_device_from_env();
