@@ -124,7 +124,7 @@ finalize_kernel(const FinalizeArgs a) {
         a.wsa[o] = -1; a.wsd[o] = -1; a.wsde[o] = -1;
         return;
     }
-    double add = 0.0, dom = 0.0;
+    double add = 1.0, dom = 0.0;                                     // ldscalc.h:27-28
     int wsa = 0, wsd = 0, wsde = 0;
     // i-block b of the chunk is rank b % 2 of supertile row b / 2
     for (int t = a.tile_begin[b >> 1]; t < a.tile_begin[(b >> 1) + 1]; ++t) {
@@ -138,17 +138,7 @@ finalize_kernel(const FinalizeArgs a) {
             wsde += a.part.wsde[p];
         }
     }
-    // sums of q_ij -> sums of r2adj (epilogue.cuh): k0 * count + c * w_i^2 * sum q
-    const double w = a.coef[row].inv_sd * a.inv_n;
-    const double cw2 = a.adj_c * (w * w), k0 = adj_k0(a.n);
-#ifdef NLDSC_EPILOGUE_V1
-    a.l2[o] = 1.0 + add;
-    a.l2d[o] = dom;
-    (void)cw2; (void)k0;
-#else
-    a.l2[o] = 1.0 + (k0 * wsa + cw2 * add);                        // ldscalc.h:27-28,38
-    a.l2d[o] = k0 * wsd + cw2 * dom;
-#endif
+    a.l2[o] = add; a.l2d[o] = dom;
     a.wsa[o] = wsa; a.wsd[o] = wsd; a.wsde[o] = wsde;
 }
 

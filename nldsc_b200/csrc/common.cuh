@@ -54,8 +54,8 @@ __host__ __device__ inline int64_t part_index(int64_t slot, int rank, int half, 
     return ((slot * 2 + rank) * 2 + half) * kBlk + row;
 }
 struct Partials {
-    double* add;     // sum over the tile's in-window kept j of q_ij = (n sd_i corr(A_i, A_j))^2 -- see epilogue.cuh
-    double* dom;     // the same for corr(A_i, D_j), over dominance-usable j
+    double* add;     // sum of r2adj(A_i, A_j)
+    double* dom;     // sum of r2adj(A_i, D_j) over dominance-usable j
     int32_t* wsa;    // in-window kept j
     int32_t* wsd;    // ... that are dominance-usable
     int32_t* wsde;   // ... with r2adj_dom > rsq_thr
@@ -74,7 +74,6 @@ struct BandArgs {
     double inv_n;
     double adj_c;               // (n - 1) / (n - 2)
     double rsq_thr;
-    double thr_num;             // (rsq_thr - k0) / adj_c with k0 = 1 - adj_c: r2adj > rsq_thr  <=>  w_i^2 q_ij > thr_num (epilogue.cuh)
     Partials part;
     int32_t* dump;              // optional raw accumulators [tile][rank][128][192] (parity hook)
     const uint32_t* ready_rows; // fused launch (one band launch per shard): ring rows [0, *ready_rows) are unpacked and their
@@ -137,8 +136,6 @@ struct FinalizeArgs {
     int32_t own_end;
     Partials part;
     const uint8_t* flags;
-    const SnpCoef* coef;        // [n_load]: the row factor w_i = inv_sd / n
-    double n, inv_n, adj_c;     // organisms, 1 / n, (n - 1) / (n - 2)
     double* l2;                 // outputs, indexed by (local row - own_begin)
     double* l2d;
     int32_t* wsa;

@@ -1,5 +1,5 @@
 // FP64 epilogue shared by the tcgen05 band kernels and the SIMT yardstick:
-// exact integer cross-counts -> correlations -> squared, row-summed; finalize applies the bias correction.
+// exact integer cross-counts -> correlations -> bias-corrected r^2 -> row sums.
 //
 // Replaces Math::r2_adjusted (reference tools.h:87-92) and the body of the OpenMP loop
 // in calculate() (ldscalc.h:34-47).  With x = g + mu*m the imputed additive vector and
@@ -7,13 +7,9 @@
 //   sum x_i x_j   = G_gg + mu_j G_gm + mu_i (G_mg + mu_j G_mm)
 //   sum x_i res_j = ch G_gh + ca G_ga + cm G_gm + mu_i (ch G_mh + ca G_ma + cm G_mm)
 //   corr = (sum - n xbar_i ybar_j) / (n sd_i sd_j);  r2adj = 1 - (1 - corr^2)(n-1)/(n-2)
-// r2adj is affine in corr^2:  r2adj = k0 + c corr^2  with c = (n-1)/(n-2), k0 = 1 - c = -1/(n-2), and
-// corr = w_i * (sum - ...) / sd_j with the per-ROW factor w_i = 1 / (n sd_i).  So a row's score is
-//   sum_j r2adj = k0 * count + c * w_i^2 * sum_j ((sum - ...) / sd_j)^2
-// and the band kernels only accumulate  q_ij = ((sum - ...) / sd_j)^2  (sums of non-negative terms); the count, k0, c
-// and w_i^2 are applied once per row by finalize_kernel.  The dominance threshold test r2adj > rsq_thr (tools.h:36-38)
-// becomes  q_ij > thr_i  with  thr_i = (rsq_thr - k0) / (c w_i^2).  Six FP64 operations per pair fewer than
-// evaluating r2adj pair by pair, and the band kernel's exposed epilogue is latency-bound FP64 work.
+// Measured and rejected (profiles/r02g_ab_step*.json, same box): accumulating only (sum - ...)^2 / sd_j^2 per pair and
+// applying the affine bias correction once per row in finalize_kernel -- six FP64 operations per pair fewer -- was 1.4 %
+// SLOWER on configs[1] (3.586 vs 3.537 ms per step): the exposed epilogue waits on memory, not on the FP64 pipe.
 #pragma once
 #include "common.cuh"
 
@@ -22,22 +18,16 @@ namespace nldsc {
 struct RowCtx {
     double mu;      // mu_i
     double nxbar;   // n * xbar_i
-    double thr;     // q_ij > thr  <=>  r2adj(dom) > rsq_thr   (+inf for a dropped row)
-#ifdef NLDSC_EPILOGUE_V1
-    double w;
-#endif
+    double w;       // inv_sd_i / n
     int32_t lo, hi; // inclusive window (shard-local SNP indices)
     int32_t gi;     // this row's SNP index
     bool keep;
 };
 
 struct RowAcc {
-    double add = 0.0, dom = 0.0;     // sums of q_ij (see the header)
+    double add = 0.0, dom = 0.0;
     int32_t wsa = 0, wsd = 0, wsde = 0;
 };
-
-// k0, c of the header for n organisms
-__host__ __device__ inline double adj_k0(double n) { return 1.0 - (n - 1.0) / (n - 2.0); }
 
 __device__ __forceinline__ RowCtx load_row_ctx(const BandArgs& a, int32_t gi) {
     RowCtx r;
@@ -46,19 +36,12 @@ __device__ __forceinline__ RowCtx load_row_ctx(const BandArgs& a, int32_t gi) {
         const SnpCoef c = a.coef[gi];
         r.mu = c.mu;
         r.nxbar = a.n * c.xbar;
-        const double w = c.inv_sd * a.inv_n;
-        r.thr = a.thr_num / (w * w);
-#ifdef NLDSC_EPILOGUE_V1
-        r.w = w;
-#endif
+        r.w = c.inv_sd * a.inv_n;
         r.lo = a.win_lo[gi];
         r.hi = a.win_hi[gi];
         r.keep = (a.flags[gi] & kFlagKeep) != 0;
     } else {
-        r.mu = r.nxbar = r.thr = 0.0;
-#ifdef NLDSC_EPILOGUE_V1
-        r.w = 0.0;
-#endif
+        r.mu = r.nxbar = r.w = 0.0;
         r.lo = 1; r.hi = 0;
         r.keep = false;
     }
@@ -101,38 +84,22 @@ __device__ __forceinline__ void pair_eval_core(const BandArgs& a, const RowCtx& 
 
     // additive: ldscalc.h:38
     const double sa = (dGgg + mu_j * dGgm) + r.mu * (dGmg + mu_j * dGmm) - r.nxbar * xbar_j;
-#ifdef NLDSC_EPILOGUE_V1      // A/B build only: r2adj evaluated pair by pair (round-1 arithmetic)
-    {
-        const double ra = sa * r.w * inv_sd_j;
-        const double r2a = ra * ra;
-        const double adj_a = 1.0 - (1.0 - r2a) * a.adj_c;
-        acc.add += use ? adj_a : 0.0;
-        acc.wsa += use ? 1 : 0;
-        const double u0 = ch * dGgh + ca * dGga + cm * dGgm;
-        const double u1 = ch * dGmh + ca * dGma + cm * dGmm;
-        const double sd = (u0 + r.mu * u1) - r.nxbar * rbar_j;
-        const double rd = sd * r.w * inv_rsd_j;
-        const double r2d = rd * rd;
-        const double adj = 1.0 - (1.0 - r2d) * a.adj_c;
-        acc.dom += use_d ? adj : 0.0;
-        acc.wsd += use_d ? 1 : 0;
-        acc.wsde += (use_d && adj > a.rsq_thr) ? 1 : 0;
-        return;
-    }
-#endif
-    const double ta = sa * inv_sd_j;
-    acc.add += use ? ta * ta : 0.0;
+    const double ra = sa * r.w * inv_sd_j;
+    const double r2a = ra * ra;
+    const double adj_a = 1.0 - (1.0 - r2a) * a.adj_c;           // tools.h:91
+    acc.add += use ? adj_a : 0.0;
     acc.wsa += use ? 1 : 0;
 
     // dominance: ldscalc.h:40-46
     const double u0 = ch * dGgh + ca * dGga + cm * dGgm;
     const double u1 = ch * dGmh + ca * dGma + cm * dGmm;
     const double sd = (u0 + r.mu * u1) - r.nxbar * rbar_j;
-    const double td = sd * inv_rsd_j;
-    const double qd = td * td;
-    acc.dom += use_d ? qd : 0.0;
+    const double rd = sd * r.w * inv_rsd_j;
+    const double r2d = rd * rd;
+    const double adj = 1.0 - (1.0 - r2d) * a.adj_c;
+    acc.dom += use_d ? adj : 0.0;
     acc.wsd += use_d ? 1 : 0;
-    acc.wsde += (use_d && qd > r.thr) ? 1 : 0;                  // tools.h:36-38 (strict)
+    acc.wsde += (use_d && adj > a.rsq_thr) ? 1 : 0;             // tools.h:36-38 (strict)
 }
 
 // SNP j's constants straight from global memory (narrow kernel, SIMT yardstick)

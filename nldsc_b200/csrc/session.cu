@@ -1137,7 +1137,6 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         a.inv_n = 1.0 / n;
         a.adj_c = (n - 1.0) / (n - 2.0);
         a.rsq_thr = s->rsq_thr;
-        a.thr_num = (s->rsq_thr - (1.0 - a.adj_c)) / a.adj_c;
         a.part = part;
         a.dump = nullptr;
         a.commit2 = commit2;
@@ -1153,10 +1152,6 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         f.own_end = s->own_end;
         f.part = part;
         f.flags = s->d_flags;
-        f.coef = s->d_coef;
-        f.n = n;
-        f.inv_n = 1.0 / n;
-        f.adj_c = (n - 1.0) / (n - 2.0);
         f.l2 = s->d_l2;
         f.l2d = s->d_l2d;
         f.wsa = s->d_wsa;
@@ -1890,7 +1885,6 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         a.inv_n = 1.0 / n_org;
         a.adj_c = 1.0;
         a.rsq_thr = 0.0;
-        a.thr_num = 0.0;
         a.part.add = d_pd;
         a.part.dom = d_pd + 4 * kBlk;
         a.part.wsa = d_pi;
