@@ -115,6 +115,12 @@ typedef struct nldsc_ld_stats {
     float ms_band;
     float ms_finalize;
     float ms_total;
+    /* missing-free path (band_tc_mfree_kernel: the two cross-counts g x {h, a} instead of six): */
+    int32_t mfree_chunks;     /* chunks of the last run() whose columns held no missing genotype and took it */
+    int32_t pad_;
+    int64_t qtiles;           /* missing-free supertiles planned (4 i-blocks x 2 j-blocks each), all chunks */
+    int64_t mfree_qtiles;     /* ... of the chunks that took the path in the last run() */
+    int64_t mfree_tiles_skipped;   /* 6-plane supertiles (wide: 2 i-blocks x <= 2 j-blocks) those chunks did NOT run */
 } nldsc_ld_stats;
 
 /* Shard = SNP rows [row_begin,row_end) of the bfile described by `params`

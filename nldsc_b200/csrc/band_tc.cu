@@ -409,6 +409,8 @@ constexpr int kWThreads = 320;                               // TMA warp, MMA wa
 __global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
 band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const BandArgs args) {
+    // the chunk is missing-free: band_tc_mfree_kernel scores it (every thread of the grid reads the same word)
+    if (args.mfree_flag != nullptr && *reinterpret_cast<const volatile uint32_t*>(args.mfree_flag) != 0) return;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWStages * kWStageBytes);   // leader CTA only
@@ -627,10 +629,198 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                      : "memory");
     }
 }
+// ---- missing-free supertiles: g x {h, a} only -----------------------------------------------------
+// When no kept SNP of a chunk's column range has a missing genotype, the four cross-counts with a missing-indicator
+// factor are identically zero and each ordered pair needs only G_gh and G_ga -- the reference's own two dot products
+// (tools.h:87-92; SURVEY.md section 8d: 4*N int8 ops per pair instead of 12*N).  Same roles and pipeline as the kernels
+// above, other shapes: a CTA's 128 MMA rows hold the dosage plane g of 128 i-SNPs (two i-blocks = one i-pair of the slot
+// scheme), the pair's B operand is [h ; a] of 128 j-SNPs (each CTA stages the j-block of its rank: 64 SNPs x 2 planes),
+// one tcgen05.mma M = 256, N = 256, K = 32 per 32 organisms -- the instruction shape that reaches the pipe's measured
+// ceiling -- and the 256-column accumulator is double-buffered in TMEM, so the epilogue of supertile t runs under the
+// MMAs of t+1.  A third of the MMA work and 2/5 of the operand bytes per SNP pair.  Partials go to the slots the
+// 6-plane kernels use, summed in the same order from the same expressions (pair_eval_mfree): bitwise identical scores.
+namespace {
+constexpr int kMStages = 6;
+constexpr int kMABytes = 2 * kBlk * kKStep;                  // 16 KB: g of 128 i-SNPs
+constexpr int kMBBytes = 2 * kBlk * kKStep;                  // 16 KB: [h ; a] of 64 j-SNPs
+constexpr int kMStageBytes = kMABytes + kMBBytes;            // 32 KB per CTA per stage
+constexpr int kMCols = 2 * kBlk;                             // j-SNPs of a supertile
+constexpr int kMColBytes = kMCols * static_cast<int>(sizeof(SnpCoef)) + kMCols;
+constexpr int kMSmemBytes = kMStages * kMStageBytes + 1024 + 256 + kMColBytes;
+constexpr int kMThreads = 320;                               // TMA warp, MMA warp, 8 epilogue warps
+constexpr uint32_t kIdescM = (2u << 4) | ((256u >> 3) << 17) | ((256u >> 4) << 24);   // s32 += u8 x u8, M = 256, N = 256
+}  // namespace
+
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
+band_tc_mfree_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ha,
+                     const BandArgs args) {
+    // the chunk has missing genotypes: the 6-plane kernel scores it (every thread of the grid reads the same word)
+    if (args.mfree_flag != nullptr && *reinterpret_cast<const volatile uint32_t*>(args.mfree_flag) == 0) return;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + kMStages * kMStageBytes);   // leader CTA only
+    uint64_t* empty = full + kMStages;         // one per CTA
+    uint64_t* tfull = empty + kMStages;        // one per CTA, two accumulator buffers
+    uint64_t* tempty = tfull + 2;              // leader CTA only
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+    double2* col_coef = reinterpret_cast<double2*>(smem + kMStages * kMStageBytes + 256);
+    uint8_t* col_flags = reinterpret_cast<uint8_t*>(col_coef) + kMCols * sizeof(SnpCoef);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_g)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_ha)) : "memory");
+        for (int s = 0; s < kMStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 16); }   // 8 epilogue warps x 2 CTAs
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer: g of this CTA's two i-blocks, [h ; a] of the j-block of its rank =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = pair; t < args.n_qtiles; t += n_pairs) {
+                const QTile tl = args.qtiles[t];
+                const int32_t a_row0 = tl.a_row[2 * rank], a_row1 = tl.a_row[2 * rank + 1];
+                const int32_t b_row = tl.b_row[rank];
+                for (int k = 0; k < args.k_steps; ++k) {
+                    mbar_wait(&empty[stage], phase ^ 1, 11);
+                    if (rank == 0) mbar_expect_tx(&full[stage], 2 * kMStageBytes);    // both CTAs' bytes
+                    uint8_t* sa = smem + stage * kMStageBytes;
+                    tma_load_3d(sa, &map_g, &full[stage], k * kKStep, a_row0, kPlaneG);
+                    tma_load_3d(sa + kBlk * kKStep, &map_g, &full[stage], k * kKStep, a_row1, kPlaneG);
+                    tma_load_3d(sa + kMABytes, &map_ha, &full[stage], k * kKStep, b_row, kPlaneH);
+                    if (++stage == kMStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (rank == 0 && lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int n = 0;
+            for (int t = pair; t < args.n_qtiles; t += n_pairs, ++n) {
+                const int buf = n & 1;
+                mbar_wait(&tempty[buf], ((n >> 1) & 1) ^ 1, 12);   // both CTAs' epilogues drained this accumulator
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * 256;
+                for (int k = 0; k < args.k_steps; ++k) {
+                    mbar_wait(&full[stage], phase, 13);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * kMStageBytes);
+                    const uint64_t a_desc = make_smem_desc(sa);
+                    const uint64_t b_desc = make_smem_desc(sa + kMABytes);
+#pragma unroll
+                    for (int kk = 0; kk < kKStep / 32; ++kk)
+                        tc_mma_i8(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdescM, (k | kk) != 0);
+                    tc_commit_pair(&empty[stage]);
+                    if (++stage == kMStages) { stage = 0; phase ^= 1; }
+                }
+                tc_commit_pair(&tfull[buf]);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue: 8 warps.  TMEM lane = i-SNP (128 per CTA); warps 2-5 score j-block 0 (columns 0..127 =
+        // [h | a] of its 64 SNPs), warps 6-9 j-block 1; warp w reads lanes 32 (w % 4) .. +31 =====
+        const int q = warp & 3;
+        const int jj = (warp - 2) >> 2;
+        const int rho = 32 * q + lane;               // row of this CTA's A tile
+        const int blk = rho >> 6;                    // which i-block of the i-pair ("rank" of the slot scheme)
+        int n = 0;
+        for (int t = pair; t < args.n_qtiles; t += n_pairs, ++n) {
+            const int buf = n & 1;
+            const QTile tl = args.qtiles[t];
+            const int32_t i0 = tl.i0[2 * rank + blk];
+            const RowCtx row = load_row_ctx(args, i0 == kDeadBlock ? kDeadBlock : i0 + (rho & 63));
+            asm volatile("bar.sync 1, 256;" ::: "memory");          // nobody still reads the previous supertile's constants
+            {
+                const int te = threadIdx.x - 64;
+                for (int e = te; e < kMCols * 4; e += 256) {
+                    const int32_t gj = tl.j0 + (e >> 2);
+                    double2 v = make_double2(0.0, 0.0);
+                    if (gj < args.n_load) v = __ldg(reinterpret_cast<const double2*>(args.coef + gj) + (e & 3));
+                    col_coef[e] = v;
+                }
+                if (te < kMCols) {
+                    const int32_t gj = tl.j0 + te;
+                    col_flags[te] = gj < args.n_load ? __ldg(args.flags + gj) : uint8_t(0);
+                }
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            mbar_wait_idle(&tfull[buf], (n >> 1) & 1, 14);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + buf * 256 + 128 * jj + (static_cast<uint32_t>(32 * q) << 16);
+            const int32_t jbase = tl.j0 + kBlk * jj;
+            const int32_t slot = tl.slot[rank][jj];
+#pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                RowAcc ev, od;                        // even / odd j: the two chains the 6-plane kernels sum a half in
+#pragma unroll 1
+                for (int c2 = 0; c2 < 2; ++c2) {
+                    const int c = 2 * half + c2;
+                    if (!__any_sync(0xFFFFFFFFu, row_needs(row, jbase + 16 * c, jbase + 16 * c + 15))) continue;
+                    int32_t vh[16], va[16];
+                    tmem_ld16(taddr + 16 * c, vh);
+                    tmem_ld16(taddr + kBlk + 16 * c, va);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) {
+                        const int jl = 16 * c + u;
+                        const double2* cj = col_coef + 4 * (kBlk * jj + jl);
+                        pair_eval_mfree(args, row, jbase + jl, col_flags[kBlk * jj + jl], cj[0], cj[1], cj[2], cj[3], vh[u], va[u],
+                                        (u & 1) ? od : ev);
+                    }
+                }
+                if (half == 1) {
+                    // accumulator fully read: hand it back to the leader's MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_leader(&tempty[buf]);
+                }
+                if (slot >= 0 && i0 != kDeadBlock) {
+                    const int64_t o = part_index(slot, blk, half, rho & 63);
+                    args.part.add[o] = ev.add + od.add;
+                    args.part.dom[o] = ev.dom + od.dom;
+                    args.part.wsa[o] = ev.wsa + od.wsa;
+                    args.part.wsd[o] = ev.wsd + od.wsd;
+                    args.part.wsde[o] = ev.wsde + od.wsde;
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                     : "memory");
+    }
+}
+
 // ---- host side: TMA descriptors + launch ------------------------------------------------
 struct BandMaps {
     CUtensorMap a;   // box {128 B, 16 rows, 2 planes}
     CUtensorMap b;   // box {128 B, 32 rows, 3 planes}
+    CUtensorMap g;   // box {128 B, 64 rows, 1 plane}    missing-free kernel: g of one i-block
+    CUtensorMap ha;  // box {128 B, 64 rows, 2 planes}   missing-free kernel: [h ; a] of one j-block
 };
 
 namespace {
@@ -673,6 +863,8 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
     try {
         encode(&m->a, planes, plane_rows, npad, 16, 2);
         encode(&m->b, planes, plane_rows, npad, 32, 3);
+        encode(&m->g, planes, plane_rows, npad, 64, 1);
+        encode(&m->ha, planes, plane_rows, npad, 64, 2);
     } catch (...) {
         delete m;
         throw;
@@ -687,7 +879,8 @@ uint32_t* g_hang_host[64] = {nullptr};
 std::mutex g_hang_mu;
 const char* const kSiteNames[] = {"?", "narrow/producer:empty", "narrow/mma:tmem-empty", "narrow/mma:full", "narrow/epilogue:tmem-full",
                                   "wide/producer:empty", "wide/mma:tmem-empty", "wide/mma:full", "wide/epilogue:tmem-full", "i8-peak",
-                                  "rows-ready (the chunk's unpack never published)"};
+                                  "rows-ready (the chunk's unpack never published)", "mfree/producer:empty", "mfree/mma:tmem-empty", "mfree/mma:full",
+                                  "mfree/epilogue:tmem-full"};
 void install_hang_word() {
     int dev = 0;
     CUDA_CHECK(cudaGetDevice(&dev));
@@ -723,6 +916,7 @@ void install_band_kernels() {
     install_hang_word();
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_mfree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMSmemBytes));
 }
 
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
@@ -810,6 +1004,15 @@ i8_peak_kernel(int iters, int n_cols, int depth_flags) {
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
                      : "memory");
     }
+}
+
+void launch_band_tc_mfree(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
+    if (args.n_qtiles <= 0) return;
+    install_hang_word();
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_mfree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMSmemBytes));
+    const int pairs = args.n_qtiles < sm_count / 2 ? args.n_qtiles : sm_count / 2;
+    band_tc_mfree_kernel<<<2 * pairs, kMThreads, kMSmemBytes, st>>>(maps->g, maps->ha, args);
+    CUDA_CHECK(cudaGetLastError());
 }
 
 void launch_i8_peak(int iters, int n_cols, int per_commit, int depth, int sm_count, cudaStream_t st) {

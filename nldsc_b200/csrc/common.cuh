@@ -48,6 +48,19 @@ struct Tile {
                        // the same A tiles (its partials go to slot + 1), or -1.  Unused (0) by the narrow kernel.
 };
 
+// Missing-free supertile (band_tc_mfree_kernel): FOUR consecutive 64-SNP i-blocks (cluster rank r owns blocks 2r, 2r+1 =
+// one i-pair of the slot scheme) x the even-aligned PAIR of j-blocks starting at j0.  Without missing genotypes only the
+// two cross-counts g x {h, a} are needed (SURVEY.md section 8d "4*N int8 ops"), so the 128 MMA rows of a CTA hold g of
+// 128 i-SNPs and one N = 256 accumulator holds [h | a] of 128 j-SNPs: a third of the MMA work per SNP pair.
+struct QTile {
+    int32_t a_row[4];    // ring rows of the four i-blocks (a missing block repeats block 0's row)
+    int32_t i0[4];       // first SNP (shard-local) of each i-block, or kDeadBlock
+    int32_t b_row[2];    // ring rows of j-blocks j0 / 64 and j0 / 64 + 1 (a missing second block repeats the first)
+    int32_t j0;          // first SNP of the j-block pair (a multiple of 128)
+    int32_t slot[2][2];  // [i-pair][j-block]: partial-sum slot, or -1 where the j-block lies outside the i-pair's range
+    int32_t pad;
+};
+
 // Per-row partial sums a (64 x 64 SNP) tile contributes, in two halves: j-SNPs 0..31 and 32..63 of the j-block
 // (the wide kernel scores the halves in different warps).  SoA, index = part_index(slot, rank, half, row).
 __host__ __device__ inline int64_t part_index(int64_t slot, int rank, int half, int row) {
@@ -76,6 +89,11 @@ struct BandArgs {
     double rsq_thr;
     Partials part;
     int32_t* dump;              // optional raw accumulators [tile][rank][128][192] (parity hook)
+    const QTile* qtiles;        // missing-free supertiles of the same chunk (band_tc_mfree_kernel), same slots
+    int32_t n_qtiles;
+    const uint32_t* mfree_flag; // per chunk, written on the device after the chunk's stats: 1 = no kept SNP of the chunk's
+                                // column range has a missing genotype.  The wide kernel returns at once when it reads 1, the
+                                // missing-free kernel when it reads 0; null = the missing-free path is off
     const uint32_t* ready_rows; // fused launch (one band launch per shard): ring rows [0, *ready_rows) are unpacked and their
                                 // per-SNP statistics final; published after every chunk's unpack + stats.  null = everything is ready
     int32_t no_skip;            // A/B: score the out-of-window column groups too (NLDSC_NOSKIP=1)
@@ -103,7 +121,8 @@ inline void cuda_check(cudaError_t e, const char* what, const char* file, int li
 // counts / coef / flags / maf / rstd are indexed by shard-local row; rows [row0, row0 + n_rows) are processed
 void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
                   double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
-                  double* rstd_out, cudaStream_t st, const uint8_t* unused = nullptr);   // unused[row] != 0: position < 0
+                  double* rstd_out, cudaStream_t st, const uint8_t* unused = nullptr,   // unused[row] != 0: position < 0
+                  uint8_t* blk_miss = nullptr);   // [row / 64] = 1 where a kept SNP has a missing genotype
 void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
                    int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
                    int32_t dst_row0, int32_t* counts, cudaStream_t st);   // counts != null: += genotype counts (zeroed by the caller)
@@ -120,6 +139,10 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
 void band_maps_destroy(BandMaps*);
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);
 void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);   // tiles carry b_row2
+void launch_band_tc_mfree(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);  // args.qtiles
+// blk_miss[b] != 0: 64-SNP block b holds a kept SNP with a missing genotype (written by stats_kernel).  One block:
+// *flag = 1 if no block in [block0, block1) is marked, else 0.
+void launch_chunk_mfree_flag(const uint8_t* blk_miss, int32_t block0, int32_t block1, uint32_t* flag, cudaStream_t st);
 void install_band_kernels();   // per device: function attributes + module load of the band kernels (warm-up)
 void preload_unpack_kernels(); // per device: force the (lazily loaded) images of the unpack.cu / plan.cu / band_simt.cu kernels in
 void preload_plan_kernels();

@@ -55,6 +55,11 @@ __device__ __forceinline__ bool row_needs(const RowCtx& r, int32_t j_first, int3
     return j_last >= r.lo && j_first <= r.hi;
 }
 
+// 1 - (1 - corr^2) (n-1)/(n-2)   (tools.h:90-91), one fixed sequence of operations for every kernel
+__device__ __forceinline__ double r2adj(double corr, double adj_c) {
+    return __fma_rn(-(1.0 - corr * corr), adj_c, 1.0);
+}
+
 // Exact int32 -> double without the conversion unit (I2F.F64 runs on the quarter-rate XU pipe): build the
 // double 2^52 + 2^31 + x from its bit pattern and subtract the bias.  Exact for every int32.
 __device__ __forceinline__ double i2d(int32_t x) {
@@ -82,24 +87,48 @@ __device__ __forceinline__ void pair_eval_core(const BandArgs& a, const RowCtx& 
     const double dGgg = i2d(Ggh + 2 * Gga);
     const double dGmg = i2d(Gmh + 2 * Gma);
 
+    // Every multiply-add below is contracted EXPLICITLY: pair_eval_mfree evaluates the same expressions with the four
+    // missing-genotype counts and G_gm identically zero, and must give the same bits (fma(x, 0, y) == y).
     // additive: ldscalc.h:38
-    const double sa = (dGgg + mu_j * dGgm) + r.mu * (dGmg + mu_j * dGmm) - r.nxbar * xbar_j;
+    const double sa = __fma_rn(-r.nxbar, xbar_j, __fma_rn(r.mu, __fma_rn(mu_j, dGmm, dGmg), __fma_rn(mu_j, dGgm, dGgg)));
     const double ra = sa * r.w * inv_sd_j;
-    const double r2a = ra * ra;
-    const double adj_a = 1.0 - (1.0 - r2a) * a.adj_c;           // tools.h:91
+    const double adj_a = r2adj(ra, a.adj_c);                    // tools.h:91
     acc.add += use ? adj_a : 0.0;
     acc.wsa += use ? 1 : 0;
 
     // dominance: ldscalc.h:40-46
-    const double u0 = ch * dGgh + ca * dGga + cm * dGgm;
-    const double u1 = ch * dGmh + ca * dGma + cm * dGmm;
-    const double sd = (u0 + r.mu * u1) - r.nxbar * rbar_j;
+    const double u0 = __fma_rn(cm, dGgm, __fma_rn(ca, dGga, ch * dGgh));
+    const double u1 = __fma_rn(cm, dGmm, __fma_rn(ca, dGma, ch * dGmh));
+    const double sd = __fma_rn(-r.nxbar, rbar_j, __fma_rn(r.mu, u1, u0));
     const double rd = sd * r.w * inv_rsd_j;
-    const double r2d = rd * rd;
-    const double adj = 1.0 - (1.0 - r2d) * a.adj_c;
+    const double adj = r2adj(rd, a.adj_c);
     acc.dom += use_d ? adj : 0.0;
     acc.wsd += use_d ? 1 : 0;
     acc.wsde += (use_d && adj > a.rsq_thr) ? 1 : 0;             // tools.h:36-38 (strict)
+}
+
+// The same pair when neither SNP block holds a missing genotype: G_gm = G_mm = G_mh = G_ma = 0 exactly, so only
+// G_gh and G_ga arrive (band_tc_mfree_kernel).  Bitwise equal to pair_eval_core on those counts.
+__device__ __forceinline__ void pair_eval_mfree(const BandArgs& a, const RowCtx& r, int32_t gj, uint8_t fj, const double2 c0,
+                                                const double2 c1, const double2 c2, const double2 c3,
+                                                int32_t Ggh, int32_t Gga, RowAcc& acc) {
+    const bool in_win = gj >= r.lo && gj <= r.hi && gj != r.gi;
+    const bool use = in_win && (fj & kFlagKeep);
+    const bool use_d = use && (fj & kFlagDom);
+    const double xbar_j = c0.y, inv_sd_j = c1.x, ch = c1.y, ca = c2.x, rbar_j = c3.x, inv_rsd_j = c3.y;
+    const double dGgh = i2d(Ggh), dGga = i2d(Gga), dGgg = i2d(Ggh + 2 * Gga);
+    const double sa = __fma_rn(-r.nxbar, xbar_j, dGgg);
+    const double ra = sa * r.w * inv_sd_j;
+    const double adj_a = r2adj(ra, a.adj_c);
+    acc.add += use ? adj_a : 0.0;
+    acc.wsa += use ? 1 : 0;
+    const double u0 = __fma_rn(ca, dGga, ch * dGgh);
+    const double sd = __fma_rn(-r.nxbar, rbar_j, u0);
+    const double rd = sd * r.w * inv_rsd_j;
+    const double adj = r2adj(rd, a.adj_c);
+    acc.dom += use_d ? adj : 0.0;
+    acc.wsd += use_d ? 1 : 0;
+    acc.wsde += (use_d && adj > a.rsq_thr) ? 1 : 0;
 }
 
 // SNP j's constants straight from global memory (narrow kernel, SIMT yardstick)

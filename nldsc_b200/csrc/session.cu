@@ -583,6 +583,9 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     // 10,000: 3.65 vs 4.33; N >= 100,000: 10-35 %), also where the epilogue dominates -- it has twice the epilogue warps.
     // NLDSC_WIDE=0 selects the narrow, double-buffered kernel (kept as the second implementation the tests compare).
     s->wide = !s->use_simt && (wd ? wd[0] == '1' : true);
+    // missing-free chunks take the 2-plane kernel (a third of the MMAs); decided on the device, chunk by chunk
+    const char* mf = getenv("NLDSC_MFREE");
+    s->mfree = s->wide && !(mf && mf[0] == '0');
     s->load_begin = load_begin;
     s->load_end = load_end;
     s->n_load = load_end - load_begin;
@@ -835,7 +838,8 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     if (fast) {
         // positions -> pinned -> device (SM copy), windows straight into d_win_lo / d_win_hi; the pinned buffer is
         // sized once for everything this plan stages, because growing it would free memory the copy kernel reads
-        s->pstage->reserve(b_pos + pad16(sizeof(Tile) * static_cast<size_t>(tiles_bound)) + pad16(sizeof(int32_t) * (2 * static_cast<size_t>(n_ib) + 4)));
+        s->pstage->reserve(b_pos + pad16(sizeof(Tile) * static_cast<size_t>(tiles_bound)) + pad16(sizeof(int32_t) * (2 * static_cast<size_t>(n_ib) + 4)) +
+                           (s->mfree ? pad16(sizeof(QTile) * static_cast<size_t>(tiles_bound)) : 0));
         double* d_pos = amalloc<double>(s->arena, static_cast<size_t>(n_load) + 2);
         s->d_total_pairs = amalloc<unsigned long long>(s->arena, 1);
         CUDA_CHECK(cudaMemsetAsync(s->d_total_pairs, 0, sizeof(unsigned long long), st));
@@ -928,6 +932,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     std::vector<int32_t>& tile_begin = s->h_tile_begin;
     tiles.clear();
     tile_begin.clear();
+    s->h_qtiles.clear();
     int32_t unpacked_to = jb_lo[0] * kBlk;   // rows below the first needed column never enter the ring
     int32_t slot_base = 0;
     // supertiles of the i-block pair starting at block k when the chunk ends at e
@@ -1014,6 +1019,48 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
                 }
             }
         }
+        // missing-free supertiles of the same chunk: four i-blocks (two i-pairs) x an even-aligned pair of j-blocks,
+        // writing the same slots; rastered like the 6-plane tiles.  A j-block of the pair that lies outside an i-pair's
+        // range has no slot (-1): all its pairs are out of window, the kernel scores them to nothing.
+        c.blk0 = jb_lo[b];
+        c.blk1 = jb_hi[e - 1] + 1;
+        c.qtile0 = static_cast<int64_t>(s->h_qtiles.size());
+        if (s->mfree) {
+            const int32_t base = s->fused_ok ? slot_base : 0;
+            const int32_t n_blocks_ring = n_load_pad / kBlk;
+            for (int32_t g0 = b; g0 < e; g0 += 4 * kRaster) {
+                const int32_t g1 = std::min(e, g0 + 4 * kRaster);
+                for (int32_t jp = jb_lo[g0] >> 1; jp <= (jb_hi[g1 - 1] >> 1); ++jp) {
+                    for (int32_t k = g0; k < g1; k += 4) {
+                        const int32_t kend = std::min(e, k + 4);
+                        if (2 * jp + 1 < jb_lo[k] || 2 * jp > jb_hi[kend - 1]) continue;
+                        QTile t{};
+                        for (int32_t m = 0; m < 4; ++m) {
+                            const bool alive = k + m < kend;
+                            t.i0[m] = alive ? (ib0 + k + m) * kBlk : kDeadBlock;
+                            t.a_row[m] = alive ? static_cast<int32_t>(t.i0[m] % cap) : t.a_row[0];
+                        }
+                        t.j0 = 2 * jp * kBlk;
+                        for (int32_t jj = 0; jj < 2; ++jj) {
+                            const int32_t jb = 2 * jp + jj;
+                            t.b_row[jj] = jb < n_blocks_ring ? static_cast<int32_t>((static_cast<int64_t>(jb) * kBlk) % cap) : t.b_row[0];
+                        }
+                        for (int32_t p = 0; p < 2; ++p) {
+                            const int32_t first = k + 2 * p;
+                            for (int32_t jj = 0; jj < 2; ++jj) {
+                                t.slot[p][jj] = -1;
+                                if (first >= kend) continue;
+                                const int32_t lo_p = jb_lo[first], hi_p = first + 1 < kend ? jb_hi[first + 1] : jb_hi[first];
+                                const int32_t jb = 2 * jp + jj;
+                                if (jb >= lo_p && jb <= hi_p) t.slot[p][jj] = base + slot0[(first - b) / 2] + (jb - lo_p);
+                            }
+                        }
+                        s->h_qtiles.push_back(t);
+                    }
+                }
+            }
+        }
+        c.n_qtiles = static_cast<int32_t>(static_cast<int64_t>(s->h_qtiles.size()) - c.qtile0);
         s->max_chunk_slots = std::max(s->max_chunk_slots, nslots_chunk);
         c.slot_base = slot_base;                         // fused plans: where the chunk's partials start
         slot_base += nslots_chunk;
@@ -1027,14 +1074,15 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     s->total_tiles = 0;                            // in 64-wide supertiles (= partial slots), whichever kernel scores them
     for (size_t k = 0; k + 1 < tile_begin.size(); ++k) s->total_tiles += std::max(0, tile_begin[k + 1] - tile_begin[k]);
     s->d_tiles = amalloc<Tile>(s->arena, tiles.size());
+    if (s->mfree) s->d_qtiles = amalloc<QTile>(s->arena, s->h_qtiles.size());
     s->d_tile_begin = amalloc<int32_t>(s->arena, tile_begin.size());
     {
         // plan arrays -> pinned staging -> device by an SM copy: the H2D copy engine is busy with (or about to
         // be queued full of) the shard's packed rows, and these few MB must not wait behind them
         const size_t b_win = fast ? 0 : pad16(sizeof(int32_t) * n_load_pad), b_tiles = pad16(sizeof(Tile) * tiles.size()),
-                     b_tb = pad16(sizeof(int32_t) * tile_begin.size());
-        if (!fast) s->pstage->reserve(2 * b_win + b_tiles + b_tb);
-        else if (b_pos + b_tiles + b_tb > s->pstage->bytes) throw CudaError("plan staging bound exceeded");
+                     b_tb = pad16(sizeof(int32_t) * tile_begin.size()), b_qt = s->mfree ? pad16(sizeof(QTile) * s->h_qtiles.size()) : 0;
+        if (!fast) s->pstage->reserve(2 * b_win + b_tiles + b_tb + b_qt);
+        else if (b_pos + b_tiles + b_tb + b_qt > s->pstage->bytes) throw CudaError("plan staging bound exceeded");
         char* h = s->pstage->base + b_pos;
         if (!fast) {
             memcpy(h, wlo.data(), sizeof(int32_t) * n_load_pad);
@@ -1046,6 +1094,16 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         memcpy(h + 2 * b_win + b_tiles, tile_begin.data(), sizeof(int32_t) * tile_begin.size());
         launch_copy16(h + 2 * b_win, s->d_tiles, b_tiles, st);
         launch_copy16(h + 2 * b_win + b_tiles, s->d_tile_begin, b_tb, st);
+        if (s->mfree && !s->h_qtiles.empty()) {
+            memcpy(h + 2 * b_win + b_tiles + b_tb, s->h_qtiles.data(), sizeof(QTile) * s->h_qtiles.size());
+            launch_copy16(h + 2 * b_win + b_tiles + b_tb, s->d_qtiles, b_qt, st);
+        }
+    }
+    if (s->mfree) {
+        s->d_blk_miss = amalloc<uint8_t>(s->arena, static_cast<size_t>(n_load_pad / kBlk) + 16);
+        s->d_mfree_flags = amalloc<uint32_t>(s->arena, s->chunks.size() + 4);
+        CUDA_CHECK(cudaMemsetAsync(s->d_mfree_flags, 0, sizeof(uint32_t) * (s->chunks.size() + 4), st));
+        s->total_qtiles = static_cast<int64_t>(s->h_qtiles.size());
     }
     // [slot][rank][half][row]; fused plans keep every chunk's partials (chunk c at slot_base[c]), the others two chunks' worth
     const size_t np = static_cast<size_t>(s->fused_ok ? slot_base : s->max_chunk_slots) * 4 * kBlk;
@@ -1162,6 +1220,10 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         ++s->launches;
     };
     if (fused) CUDA_CHECK(cudaMemsetAsync(s->d_ready, 0, sizeof(uint32_t), st));    // before the fork: publishes come after it
+    // missing-free path: per chunk, decided on the device after the chunk's stats (not with the fused launch, whose
+    // single kernel cannot hand chunks to another kernel)
+    const bool mfree = s->mfree && !fused && !s->use_simt && s->wide && s->d_blk_miss != nullptr;
+    if (mfree) CUDA_CHECK(cudaMemsetAsync(s->d_blk_miss, 0, static_cast<size_t>((s->n_load + kBlk - 1) / kBlk), st));
     if (overlap) {
         CUDA_CHECK(cudaEventRecord(s->ev_fork, st));
         CUDA_CHECK(cudaStreamWaitEvent(us, s->ev_fork, 0));
@@ -1227,7 +1289,12 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         if (r1 > r0) {
             SpanScope sc(s, us, kFamStats);
             launch_stats(s->d_counts, r0, r1 - r0, s->n_org, s->maf_thr, s->std_thr, s->d_coef, s->d_flags,
-                         s->d_maf, s->d_rstd, us, s->d_unused);
+                         s->d_maf, s->d_rstd, us, s->d_unused, mfree ? s->d_blk_miss : nullptr);
+            ++s->launches;
+        }
+        if (mfree) {
+            // 1 = no kept SNP among the columns this chunk reads has a missing genotype
+            launch_chunk_mfree_flag(s->d_blk_miss, c.blk0, std::min(c.blk1, (s->n_load + kBlk - 1) / kBlk), s->d_mfree_flags + ci, us);
             ++s->launches;
         }
         if (fused) {
@@ -1244,7 +1311,12 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             CUDA_CHECK(cudaStreamWaitEvent(bs, s->ev_unpacked[ci], 0));
         }
         const Partials& part = (odd && !s->fused_ok) ? s->part2 : s->part;
-        const BandArgs a = band_args(s->d_tiles + c.tile0, c.n_tiles, part);
+        BandArgs a = band_args(s->d_tiles + c.tile0, c.n_tiles, part);
+        if (mfree) {
+            a.qtiles = s->d_qtiles + c.qtile0;
+            a.n_qtiles = c.n_qtiles;
+            a.mfree_flag = s->d_mfree_flags + ci;
+        }
         {
             SpanScope sc(s, bs, kFamBand);
             if (s->use_simt)
@@ -1252,6 +1324,11 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             else
                 (s->wide ? launch_band_tc_wide : launch_band_tc)(s->maps, a, s->sm_count, bs);
             ++s->launches;
+            // both kernels are launched; the one the chunk's flag does not select returns at once
+            if (mfree && c.n_qtiles > 0) {
+                launch_band_tc_mfree(s->maps, a, s->sm_count, bs);
+                ++s->launches;
+            }
         }
         if (overlap) CUDA_CHECK(cudaEventRecord(s->ev_band[ci], bs));
         // fused-capable plans number their slots shard-wide: the chunk's partials start at its slot_base
@@ -1752,6 +1829,20 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* o) {
     o->load_end = s->load_end;
     o->npad = s->npad;
     o->band_impl = s->use_simt ? 0 : (s->wide ? 2 : 1);
+    o->qtiles = s->total_qtiles;
+    if (s->ran && s->mfree && s->d_mfree_flags) {
+        std::vector<uint32_t> fl(s->chunks.size());
+        cudaSetDevice(s->device);
+        if (cudaEventSynchronize(s->ev_run1) == cudaSuccess &&
+            cudaMemcpy(fl.data(), s->d_mfree_flags, sizeof(uint32_t) * fl.size(), cudaMemcpyDeviceToHost) == cudaSuccess) {
+            for (size_t k = 0; k < fl.size(); ++k) {
+                if (!fl[k]) continue;
+                ++o->mfree_chunks;
+                o->mfree_qtiles += s->chunks[k].n_qtiles;
+                o->mfree_tiles_skipped += s->chunks[k].n_tiles;
+            }
+        }
+    }
     if (s->ran) {
         cudaSetDevice(s->device);
         if (cudaEventSynchronize(s->ev_run1) != cudaSuccess) return NLDSC_ERR_RUNTIME;

@@ -31,6 +31,9 @@ struct Chunk {
     int64_t tile0;        // offset into the tile list
     int32_t n_tiles;
     int32_t tb0;          // offset into tile_begin (n_iblocks + 1 entries, relative to tile0)
+    int64_t qtile0;       // missing-free supertiles of the same chunk (session::d_qtiles)
+    int32_t n_qtiles;
+    int32_t blk0, blk1;   // 64-SNP blocks [blk0, blk1) the chunk's tiles read: the range its missing-free flag covers
     int32_t slot_base;    // fused plans: first partial slot of the chunk (its tiles' slots already include it)
 };
 
@@ -93,6 +96,12 @@ struct nldsc_ld_session {
     double maf_thr = 0, std_thr = 0, rsq_thr = 0;
     bool use_simt = false;
     bool wide = false;                        // band_tc_wide_kernel: two j-blocks per supertile (N >= 65,536, or NLDSC_WIDE=1)
+    bool mfree = false;                       // plan carries missing-free supertiles; chunks without a missing genotype take band_tc_mfree_kernel
+    nldsc::QTile* d_qtiles = nullptr;
+    uint8_t* d_blk_miss = nullptr;            // [n_load_pad / 64] written by stats_kernel
+    uint32_t* d_mfree_flags = nullptr;        // [chunks] 1 = the chunk is missing-free (launch_chunk_mfree_flag)
+    std::vector<nldsc::QTile> h_qtiles;
+    int64_t total_qtiles = 0;
     bool fused_ok = false;                    // the plan allows ONE band launch per shard (session_plan); run() decides
     uint32_t* d_ready = nullptr;              // fused launch: ring rows [0, *d_ready) are unpacked, their statistics final
     bool upload_started = false;

@@ -30,7 +30,8 @@ __device__ __forceinline__ uint32_t tail_pair_mask(int n_org) {
 __global__ void __launch_bounds__(256)
 stats_kernel(const int32_t* __restrict__ counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
              double std_thr, SnpCoef* __restrict__ coef, uint8_t* __restrict__ flags,
-             double* __restrict__ maf_out, double* __restrict__ rstd_out, const uint8_t* __restrict__ unused) {
+             double* __restrict__ maf_out, double* __restrict__ rstd_out, const uint8_t* __restrict__ unused,
+             uint8_t* __restrict__ blk_miss) {
     int row = blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= n_rows) return;
     row += row0;
@@ -73,6 +74,9 @@ stats_kernel(const int32_t* __restrict__ counts, int32_t row0, int32_t n_rows, i
         c.ch = ch; c.ca = ca; c.cm = cm; c.rbar = rbar; c.inv_rsd = 1.0 / rsd;
         fl = kFlagKeep | ((rsd > std_thr) ? kFlagDom : 0);
         rsd_out = rsd;
+        // the block can take the missing-free band kernel only if none of its KEPT SNPs has a missing genotype
+        // (a dropped SNP's counts never reach a score); benign race: every writer stores the same 1
+        if (blk_miss != nullptr && nm > 0.0) blk_miss[row / kBlk] = 1;
     } else {
         c.mu = c.xbar = c.inv_sd = c.ch = c.ca = c.cm = c.rbar = c.inv_rsd = 0.0;
     }
@@ -173,10 +177,10 @@ zero_rows_kernel(int8_t* __restrict__ planes, int64_t plane_stride, int32_t npad
 
 void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n_org, double maf_thr,
                   double std_thr, SnpCoef* coef, uint8_t* flags, double* maf_out,
-                  double* rstd_out, cudaStream_t st, const uint8_t* unused) {
+                  double* rstd_out, cudaStream_t st, const uint8_t* unused, uint8_t* blk_miss) {
     if (n_rows <= 0) return;
     stats_kernel<<<(n_rows + 255) / 256, 256, 0, st>>>(counts, row0, n_rows, n_org, maf_thr, std_thr,
-                                                       coef, flags, maf_out, rstd_out, unused);
+                                                       coef, flags, maf_out, rstd_out, unused, blk_miss);
     CUDA_CHECK(cudaGetLastError());
 }
 
@@ -199,11 +203,26 @@ void launch_zero_rows(int8_t* planes, int64_t plane_stride, int32_t npad, int32_
     CUDA_CHECK(cudaGetLastError());
 }
 
+// *flag = 1 when no 64-SNP block in [block0, block1) holds a kept SNP with a missing genotype (one block of 256 threads)
+__global__ void __launch_bounds__(256)
+chunk_mfree_flag_kernel(const uint8_t* __restrict__ blk_miss, int32_t block0, int32_t block1, uint32_t* __restrict__ flag) {
+    int any = 0;
+    for (int32_t b = block0 + threadIdx.x; b < block1; b += blockDim.x) any |= blk_miss[b];
+    any = __syncthreads_or(any);
+    if (threadIdx.x == 0) *flag = any ? 0u : 1u;
+}
+
+void launch_chunk_mfree_flag(const uint8_t* blk_miss, int32_t block0, int32_t block1, uint32_t* flag, cudaStream_t st) {
+    chunk_mfree_flag_kernel<<<1, 256, 0, st>>>(blk_miss, block0, block1, flag);
+    CUDA_CHECK(cudaGetLastError());
+}
+
 void preload_unpack_kernels() {
     cudaFuncAttributes fa;
     CUDA_CHECK(cudaFuncGetAttributes(&fa, stats_kernel));
     CUDA_CHECK(cudaFuncGetAttributes(&fa, unpack_kernel));
     CUDA_CHECK(cudaFuncGetAttributes(&fa, zero_rows_kernel));
+    CUDA_CHECK(cudaFuncGetAttributes(&fa, chunk_mfree_flag_kernel));
 }
 
 }  // namespace nldsc

@@ -103,16 +103,17 @@ def make_output(bim: pd.DataFrame, ld, *, extra: bool = False) -> pd.DataFrame:
     return out
 
 
-def m_counts(arrays: dict, snp_ids=None, maf_min: float | None = None) -> tuple[int, int]:
+def m_counts(arrays: dict, snp_ids=None, maf_min: float | None = None, first=None) -> tuple[int, int]:
     """(M, MD) as h2 computes them when no side file exists (h2/common.py:126-130): M = rows of the .L2
     file that survive `dropna().drop_duplicates('SNP')`, MD = int(M * mean(WSDE / WSA)) over those rows.
     `maf_min` = 0.05 gives the `.M_5_50` flavour (common SNPs only).  Rows with WSA = 0 (a retained SNP
     with an empty window) are left out of the mean, where the reference would divide by zero."""
     l2 = np.asarray(arrays["l2"], dtype=np.float64)
     keep = ~np.isnan(l2) & ~np.isnan(np.asarray(arrays["l2d"], dtype=np.float64))
-    if snp_ids is not None:
+    if first is None and snp_ids is not None:
         first = ~pd.Series(np.asarray(snp_ids)).duplicated().to_numpy()
-        keep &= first
+    if first is not None:                       # rows that survive drop_duplicates('SNP')
+        keep &= np.asarray(first, dtype=bool)
     if maf_min is not None:
         keep &= np.asarray(arrays["maf"], dtype=np.float64) > maf_min
     m = int(keep.sum())
@@ -123,13 +124,13 @@ def m_counts(arrays: dict, snp_ids=None, maf_min: float | None = None) -> tuple[
     return m, md
 
 
-def write_m_files(l2_path: str, arrays: dict, snp_ids=None) -> dict:
+def write_m_files(l2_path: str, arrays: dict, snp_ids=None, first=None) -> dict:
     """`<stem>.M` and `<stem>.M_5_50` next to an .L2 file, in the tab-separated `M MD` layout that
     LDScoreReader._read_m parses (h2/common.py:141-144)."""
     stem = os.path.splitext(l2_path)[0]
     out = {}
     for suffix, maf_min in ((".M", None), (".M_5_50", 0.05)):
-        m, md = m_counts(arrays, snp_ids, maf_min)
+        m, md = m_counts(arrays, snp_ids, maf_min, first)
         with open(stem + suffix, "w") as f:
             f.write(f"M\tMD\n{m}\t{md}\n")
         out[suffix] = (m, md)
@@ -195,21 +196,35 @@ def _genome_bfiles(bfile: str) -> list[tuple[str, str]]:
 
 
 def _parse_bfile_meta(path: str) -> dict:
-    """Everything the scoring call needs from the .bim / .fam of one chromosome (runs in a worker process, so that
-    22 pandas parses neither run one after the other nor hold the GIL of the process that feeds the GPUs)."""
+    """Everything the scoring call needs from the .bim / .fam of one chromosome (runs in a pool thread beside the
+    others).  With this repo's `_ldscore` the .bim is parsed natively (`read_bim`: GIL released, the CHR / SNP strings
+    stay on the C++ side for the .L2 writer); otherwise by pandas, as the reference does (ldscore/common.py:86-89)."""
     import time
     t0 = time.perf_counter()
+    lds = _module()
     bed, bim_path, fam_path = _bfile_paths(path)
-    bim = pd.read_csv(bim_path, sep="\t", names=BIM_COLUMNS)
-    if len(bim["CHR"].unique()) != 1:
-        raise NLDSCParameterError("The current version of the program can only work with one chromosome in one file.")
     with open(fam_path, "rb") as f:
         fam = f.read()
     n_org = fam.count(b"\n") + (1 if fam and not fam.endswith(b"\n") else 0)
-    return {"bed": bed, "n_org": n_org, "n_snp": len(bim), "chr": bim["CHR"].astype(str).tolist(),
-            "snp": bim["SNP"].astype(str).tolist(), "bp": bim["BP"].to_numpy(np.int64) if bim["BP"].dtype.kind in "iu" else None,
-            "cm": bim["CM"].to_numpy(dtype=np.float64), "bp_f": bim["BP"].to_numpy(dtype=np.float64),
-            "bed_bytes": os.path.getsize(bed), "seconds": time.perf_counter() - t0}
+    m = {"bed": bed, "n_org": n_org, "bed_bytes": os.path.getsize(bed)}
+    if hasattr(lds, "read_bim"):
+        tbl = lds.read_bim(bim_path)
+        if len(tbl.chromosomes()) != 1:
+            raise NLDSCParameterError("The current version of the program can only work with one chromosome in one file.")
+        m.update(table=tbl if tbl.bp_integral else None, n_snp=len(tbl), cm=tbl.cm(), bp_f=tbl.bp_float(),
+                 first=tbl.first_occurrence())
+        if not tbl.bp_integral:
+            m.update(chr=[tbl.chromosomes()[0]] * len(tbl), snp=tbl.snps(), bp=None)
+    else:
+        bim = pd.read_csv(bim_path, sep="\t", names=BIM_COLUMNS)
+        if len(bim["CHR"].unique()) != 1:
+            raise NLDSCParameterError("The current version of the program can only work with one chromosome in one file.")
+        m.update(table=None, n_snp=len(bim), chr=bim["CHR"].astype(str).tolist(), snp=bim["SNP"].astype(str).tolist(),
+                 bp=bim["BP"].to_numpy(np.int64) if bim["BP"].dtype.kind in "iu" else None,
+                 cm=bim["CM"].to_numpy(dtype=np.float64), bp_f=bim["BP"].to_numpy(dtype=np.float64),
+                 first=~bim["SNP"].duplicated().to_numpy())
+    m["seconds"] = time.perf_counter() - t0
+    return m
 
 
 def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: float = 1e-5, std_thr: float = 1e-5,
@@ -219,7 +234,7 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
 
     The reference scores one chromosome per invocation (ldscore/common.py:114-117) and never writes the
     `.M` files `h2` looks for.  Here
-      1. every .bim / .fam is parsed up front by a pool of worker PROCESSES (pandas holds the GIL),
+      1. every .bim / .fam is parsed by a thread pool (pandas' C parser releases the GIL), largest chromosome first,
          while the GPUs are warmed up in parallel (`_ldscore.warmup`: contexts, pinned staging, kernel images);
       2. the chromosomes are dealt, largest .bed first, to one host thread per GPU (`_ldscore.calculate_on`, GIL
          released, no collective: chromosomes are independent); NLDSC_READERS is set to cores / GPUs so that the
@@ -229,7 +244,7 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     Returns one row per chromosome: CHR, file, SNPs, M, MD, seconds (scoring call), device; `.attrs["phases"]` holds
     the wall time of every phase (parse, warmup, score, write) and `.attrs["per_gpu_busy_s"]` the scoring seconds per GPU."""
     import time
-    from concurrent.futures import ProcessPoolExecutor, ThreadPoolExecutor
+    from concurrent.futures import ThreadPoolExecutor
     lds = _module()
     t_start = time.perf_counter()
     jobs = _genome_bfiles(bfile)
@@ -252,8 +267,11 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     warm = threading.Thread(target=lambda: lds.warmup(first_device, n_dev) if hasattr(lds, "warmup") else None)
     warm.start()
     order = sorted(jobs, key=lambda j: -os.path.getsize(j[1] + ".bed"))          # longest first
-    n_parse = max(1, min(len(jobs), parse_workers if parse_workers is not None else max(1, cores - n_dev)))
-    pool = ProcessPoolExecutor(max_workers=n_parse) if n_parse > 1 else ThreadPoolExecutor(max_workers=1)
+    # threads, not processes: pandas' C parser releases the GIL, and a process pool costs more to start (fork of a
+    # process that holds CUDA contexts) and to return 100,000-string lists from (pickle) than the parsing itself --
+    # measured on configs[2]: the last parse landed at 0.15-0.29 s of a 0.55 s job (profiles/r02h_cfg3_genome_*.json)
+    n_parse = max(1, min(len(jobs), parse_workers if parse_workers is not None else max(1, min(8, cores - n_dev))))
+    pool = ThreadPoolExecutor(max_workers=n_parse)
     meta_f = {label: pool.submit(_parse_bfile_meta, path) for label, path in order}
     parse_done = [0.0]
 
@@ -274,13 +292,16 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     def write(label, m, arrays, seconds, device):
         t = time.perf_counter()
         l2_path = os.path.join(out_dir, f"{label}.L2")
-        if hasattr(lds, "write_l2") and m["bp"] is not None:
+        if m.get("table") is not None:
+            lds.write_l2_bim(l2_path, m["table"], arrays["l2"], arrays["l2d"], arrays["maf"], arrays["residuals_std"],
+                             arrays["l2_ws"], arrays["l2d_ws"], arrays["l2d_wse"], extra)
+        elif hasattr(lds, "write_l2") and m["bp"] is not None:
             lds.write_l2(l2_path, m["chr"], m["snp"], m["bp"], arrays["l2"], arrays["l2d"], arrays["maf"],
                          arrays["residuals_std"], arrays["l2_ws"], arrays["l2d_ws"], arrays["l2d_wse"], extra)
         else:
             bim = pd.DataFrame({"CHR": m["chr"], "SNP": m["snp"], "BP": m["bp_f"]})
             make_output(bim, arrays, extra=extra).to_csv(l2_path, sep="\t", index=False, float_format="%.5f")
-        mm = write_m_files(l2_path, arrays, m["snp"])
+        mm = write_m_files(l2_path, arrays, first=m["first"])
         with lock:
             rows.append({"CHR": label, "file": l2_path, "SNPs": m["n_snp"], "M": mm[".M"][0], "MD": mm[".M"][1],
                          "seconds": seconds, "device": device, "write_seconds": time.perf_counter() - t})

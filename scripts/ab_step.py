@@ -10,7 +10,7 @@ import numpy as np
 from nldsc_b200 import capi, synth
 n_org, n_snp = int(os.environ.get("AB_N", 10000)), int(os.environ.get("AB_M", 100000))
 packed = np.load(sys.argv[1], mmap_mode="r")
-spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=0.02, seed=2, density=float(os.environ.get("AB_DENSITY", 340)))
+spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=float(os.environ.get("AB_MISSING", 0.02)), seed=2, density=float(os.environ.get("AB_DENSITY", 340)))
 cm, _ = synth.genetic_map(spec)
 s = capi.Session(0, n_snp, n_org, cm, float(os.environ.get("AB_WIND", 1.0)), 1e-4, 1e-5, 1.0 / n_snp)
 s.upload(np.ascontiguousarray(packed)); s.sync()
@@ -24,14 +24,15 @@ r = s.download()
 import hashlib
 h = hashlib.sha256(b"".join(np.ascontiguousarray(r[k]).tobytes() for k in sorted(r))).hexdigest()[:12]
 print(json.dumps({"ms_step": float(np.median(tot)), "ms_step_min": float(np.min(tot)), "ms_band": float(np.median(band)),
-                  "ms_unpack": float(np.median(unp)), "launches": st["kernel_launches"], "chunks": st["chunks"], "sha": h}))
+                  "ms_unpack": float(np.median(unp)), "launches": st["kernel_launches"], "chunks": st["chunks"],
+                  "mfree_chunks": st["mfree_chunks"], "pairs": int(r["l2_ws"][r["l2_ws"] >= 0].astype(np.int64).sum()), "sha": h}))
 ''' % ROOT
 sys.path.insert(0, ROOT)
 import numpy as np
 import torch
 from nldsc_b200 import synth
 n_org, n_snp = int(os.environ.get("AB_N", 10000)), int(os.environ.get("AB_M", 100000))
-spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=0.02, seed=2, density=float(os.environ.get("AB_DENSITY", 340)))
+spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=float(os.environ.get("AB_MISSING", 0.02)), seed=2, density=float(os.environ.get("AB_DENSITY", 340)))
 path = os.path.join(tempfile.gettempdir(), f"ab_{n_org}_{n_snp}.npy")
 np.save(path, synth.generate_packed_cuda(spec, "cuda:0").cpu().numpy())
 out = {}

@@ -31,6 +31,8 @@ VARIANTS = [
     {"NLDSC_TEST_SHARDS": "3"},
     {"NLDSC_FUSED": "1"},
     {"NLDSC_FUSED": "1", "NLDSC_CHUNK_ROWS": "64"},
+    {"NLDSC_MFREE": "0"},
+    {"NLDSC_MFREE": "0", "NLDSC_CHUNK_ROWS": "128"},
 ]
 
 
@@ -99,6 +101,7 @@ MID_VARIANTS = [
     {"NLDSC_FIRST_BYTES": "1000000", "NLDSC_CHUNK_BYTES": "3000000"},
     {"NLDSC_TEST_SHARDS": "4", "NLDSC_CHUNK_ROWS": "1024"},
     {"NLDSC_FUSED": "1", "NLDSC_CHUNK_ROWS": "1024"},
+    {"NLDSC_MFREE": "0"},
 ]
 
 

@@ -326,6 +326,58 @@ def test_multi_piece_bed_read_equals_host_buffer(tmp_path, monkeypatch):
     assert (mem["l2_ws"] >= 0).sum() > 8000
 
 
+def _session_stats(g, **env):
+    with capi.Session(0, g["packed"].shape[0], g["n_org"], g["positions"], g["ld_wind"], g["maf"], g["std_thr"], g["rsq_thr"]) as s:
+        s.upload(g["packed"])
+        s.run()
+        out = s.download()
+        return out, s.stats()
+
+
+def test_missing_free_kernel_equals_six_plane_bitwise(monkeypatch):
+    """band_tc_mfree_kernel (g x {h, a}: the reference's own two dot products, tools.h:87-92) takes the chunks whose
+    columns hold no missing genotype; it must give the bits the 6-plane kernels give (NLDSC_MFREE=0), meet the oracle
+    bar, and hand chunks WITH missing genotypes back to the 6-plane kernel -- also in one and the same run."""
+    g = _case(1003, 3000, 0.0, seed=23, wind=0.7)
+    out, st = _session_stats(g)
+    assert st["mfree_chunks"] == st["chunks"] >= 1 and st["mfree_qtiles"] > 0
+    assert_ld_close(out, _oracle(g), label="mfree")
+    monkeypatch.setenv("NLDSC_MFREE", "0")
+    six, st6 = _session_stats(g)
+    assert st6["mfree_chunks"] == 0
+    for k in RESULT_KEYS:
+        assert np.array_equal(out[k], six[k], equal_nan=True), k
+    monkeypatch.delenv("NLDSC_MFREE")
+    # missing genotypes in SNPs 1,400-1,500 only: with 256-row chunks some chunks are missing-free, others are not
+    codes = ld_oracle.decode_bed_msb_first(g["packed"], 1003).copy()
+    rng = np.random.default_rng(5)
+    codes[1400:1500][rng.random((100, 1003)) < 0.03] = 1
+    mixed = dict(g, packed=synth.pack_codes(codes))
+    want = _oracle(mixed)
+    for chunk_rows in ("256", "512"):
+        monkeypatch.setenv("NLDSC_CHUNK_ROWS", chunk_rows)
+        monkeypatch.delenv("NLDSC_MFREE", raising=False)
+        a, sta = _session_stats(mixed)
+        assert 0 < sta["mfree_chunks"] < sta["chunks"], sta
+        assert_ld_close(a, want, label="mixed " + chunk_rows)
+        monkeypatch.setenv("NLDSC_MFREE", "0")
+        b, _ = _session_stats(mixed)
+        for k in RESULT_KEYS:
+            assert np.array_equal(a[k], b[k], equal_nan=True), (chunk_rows, k)
+    # ragged ends: odd numbers of i-blocks and j-blocks, tiny shards, a wrapping ring
+    monkeypatch.delenv("NLDSC_MFREE", raising=False)
+    for n_snp, chunk_rows in ((65, "64"), (129, "64"), (333, "128"), (961, "192")):
+        h = _case(517, n_snp, 0.0, seed=40 + n_snp, wind=0.3)
+        monkeypatch.setenv("NLDSC_CHUNK_ROWS", chunk_rows)
+        monkeypatch.delenv("NLDSC_MFREE", raising=False)
+        a = _run(h)
+        assert_ld_close(a, _oracle(h), label=f"mfree ragged {n_snp}")
+        monkeypatch.setenv("NLDSC_MFREE", "0")
+        b = _run(h)
+        for k in RESULT_KEYS:
+            assert np.array_equal(a[k], b[k], equal_nan=True), (n_snp, k)
+
+
 def test_wide_supertiles_equal_narrow_bitwise(monkeypatch):
     """band_tc_wide_kernel (two j-blocks per A tile, eight epilogue warps; the default) and band_tc_kernel (one j-block,
     double-buffered accumulators; NLDSC_WIDE=0) put their partial sums into the same slots: they must agree bit for

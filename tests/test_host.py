@@ -142,11 +142,47 @@ def test_l2_writer_matches_pandas_bytes(tmp_path, extra):
         a[k][drop] = -1
     a["l2d"][:4] = [0.0, -0.0, -4e-6, 0.000005]          # rounding and signed-zero cases
     a["l2"][4:7] = [1e6 + 0.123456, 0.999995, 123.4]
+    # the writer formats %.5f itself and falls back to printf near rounding boundaries and for huge values: all of those
+    a["l2"][10:20] = [0.5e-5, 1.5e-5, 2.5e-5, -2.5e-5, 1e12, -123456789.123455, 1e16, np.inf, -np.inf, 99999.999995]
+    a["l2d"][10:400] = (rng.integers(-10 ** 7, 10 ** 7, 390) + 0.5) * 1e-5      # as close to a tie as doubles get
     bim = pd.DataFrame({"CHR": 22, "SNP": [f"rs{i}" for i in range(n)], "BP": np.arange(n, dtype=np.int64) * 997 + 1})
     ldscore.make_output(bim, a, extra=extra).to_csv(tmp_path / "pandas.L2", sep="\t", index=False, float_format="%.5f")
     m.write_l2(str(tmp_path / "native.L2"), bim["CHR"].astype(str).tolist(), bim["SNP"].tolist(), bim["BP"].to_numpy(),
                a["l2"], a["l2d"], a["maf"], a["residuals_std"], a["l2_ws"], a["l2d_ws"], a["l2d_wse"], extra)
     assert (tmp_path / "native.L2").read_bytes() == (tmp_path / "pandas.L2").read_bytes()
+
+
+def test_native_bim_table(tmp_path):
+    """`_ldscore.read_bim` (the .bim parsed and kept on the C++ side for the genome driver) against pandas, the way the
+    reference reads it (ldscore/common.py:86-89), and `write_l2_bim` against the list-based writer."""
+    import pandas as pd
+    m = importlib.import_module("nldsc_b200._ldscore")
+    rng = np.random.default_rng(8)
+    n = 5000
+    cm = np.round(np.cumsum(rng.exponential(1 / 340, n)), 8)
+    ids = [f"rs{i}" for i in range(n)]
+    ids[77] = ids[3]                                          # a duplicated SNP id
+    with open(tmp_path / "t.bim", "w") as f:
+        for i in range(n):
+            sep = "\t" if i % 3 else " "                       # PLINK allows either
+            f.write(sep.join(["7", ids[i], f"{cm[i]:.8f}", str(1000 + 37 * i), "A", "C"]) + ("\r\n" if i == 5 else "\n"))
+    t = m.read_bim(str(tmp_path / "t.bim"))
+    assert len(t) == n and t.chromosomes() == ["7"] and t.bp_integral and t.snp(77) == ids[3]
+    assert np.array_equal(t.cm(), np.array([float(f"{v:.8f}") for v in cm]))
+    assert np.array_equal(t.bp(), 1000 + 37 * np.arange(n)) and np.array_equal(t.bp_float(), t.bp().astype(float))
+    assert np.array_equal(t.first_occurrence(), ~pd.Series(ids).duplicated().to_numpy())
+    a = {k: rng.normal(size=n) for k in ("l2", "l2d", "maf", "residuals_std")}
+    w = {k: rng.integers(-1, 900, n).astype(np.int32) for k in ("l2_ws", "l2d_ws", "l2d_wse")}
+    for extra in (False, True):
+        m.write_l2_bim(str(tmp_path / "a.L2"), t, a["l2"], a["l2d"], a["maf"], a["residuals_std"], w["l2_ws"], w["l2d_ws"], w["l2d_wse"], extra)
+        m.write_l2(str(tmp_path / "b.L2"), ["7"] * n, ids, t.bp(), a["l2"], a["l2d"], a["maf"], a["residuals_std"], w["l2_ws"],
+                   w["l2d_ws"], w["l2d_wse"], extra)
+        assert (tmp_path / "a.L2").read_bytes() == (tmp_path / "b.L2").read_bytes()
+    (tmp_path / "two.bim").write_text("1\trs1\t0.1\t5\tA\tC\n2\trs2\t0.2\t9\tA\tC\n")
+    assert m.read_bim(str(tmp_path / "two.bim")).chromosomes() == ["1", "2"]
+    (tmp_path / "bad.bim").write_text("1\trs1\n")
+    with pytest.raises(RuntimeError):
+        m.read_bim(str(tmp_path / "bad.bim"))
 
 
 def test_genome_bfile_pattern(tmp_path):
