@@ -406,11 +406,7 @@ constexpr int kWThreads = 320;                               // TMA warp, MMA wa
 
 // 128 registers x 320 threads leave a third of the register file to the unpack blocks that run beside this kernel
 // (at the 162 ptxas would take, only one unpack block fits per SM and the unpack becomes the critical path)
-__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
-band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                    const BandArgs args) {
-    // the chunk is missing-free: band_tc_mfree_kernel scores it (every thread of the grid reads the same word)
-    if (args.mfree_flag != nullptr && *reinterpret_cast<const volatile uint32_t*>(args.mfree_flag) != 0) return;
+__device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const CUtensorMap& map_b, const BandArgs& args) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWStages * kWStageBytes);   // leader CTA only
@@ -651,11 +647,7 @@ constexpr int kMThreads = 320;                               // TMA warp, MMA wa
 constexpr uint32_t kIdescM = (2u << 4) | ((256u >> 3) << 17) | ((256u >> 4) << 24);   // s32 += u8 x u8, M = 256, N = 256
 }  // namespace
 
-__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
-band_tc_mfree_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ha,
-                     const BandArgs args) {
-    // the chunk has missing genotypes: the 6-plane kernel scores it (every thread of the grid reads the same word)
-    if (args.mfree_flag != nullptr && *reinterpret_cast<const volatile uint32_t*>(args.mfree_flag) == 0) return;
+__device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const CUtensorMap& map_ha, const BandArgs& args) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kMStages * kMStageBytes);   // leader CTA only
@@ -815,6 +807,18 @@ band_tc_mfree_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_con
     }
 }
 
+// ONE launch per chunk for both paths: the chunk's flag (written on the device after its stats) picks the body.
+// (Two kernels, one of them returning at once, cost configs[1] 12 %: the idle launch still has to wait for a whole
+// grid's worth of free SMs behind the other stream's persistent band kernel -- profiles/r02i_ab_missing_n10000.json.)
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
+band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ha, const BandArgs args) {
+    // every thread of the grid reads the same word, written before this launch could start
+    const bool mfree = args.mfree_flag != nullptr && *reinterpret_cast<const volatile uint32_t*>(args.mfree_flag) != 0;
+    if (mfree) band_mfree_body(map_g, map_ha, args);
+    else band_wide_body(map_a, map_b, args);
+}
+
 // ---- host side: TMA descriptors + launch ------------------------------------------------
 struct BandMaps {
     CUtensorMap a;   // box {128 B, 16 rows, 2 planes}
@@ -915,8 +919,8 @@ std::string band_hang_note() {
 void install_band_kernels() {
     install_hang_word();
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
-    CUDA_CHECK(cudaFuncSetAttribute(band_tc_mfree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    kWSmemBytes > kMSmemBytes ? kWSmemBytes : kMSmemBytes));
 }
 
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
@@ -930,11 +934,13 @@ void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cu
 }
 
 void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
-    if (args.n_tiles <= 0) return;
+    const int32_t n_max = args.mfree_flag != nullptr ? (args.n_tiles > args.n_qtiles ? args.n_tiles : args.n_qtiles) : args.n_tiles;
+    if (n_max <= 0) return;
     install_hang_word();
-    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWSmemBytes));
-    const int pairs = args.n_tiles < sm_count / 2 ? args.n_tiles : sm_count / 2;
-    band_tc_wide_kernel<<<2 * pairs, kWThreads, kWSmemBytes, st>>>(maps->a, maps->b, args);
+    constexpr int smem = kWSmemBytes > kMSmemBytes ? kWSmemBytes : kMSmemBytes;
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    const int pairs = n_max < sm_count / 2 ? n_max : sm_count / 2;
+    band_tc_wide_kernel<<<2 * pairs, kWThreads, smem, st>>>(maps->a, maps->b, maps->g, maps->ha, args);
     CUDA_CHECK(cudaGetLastError());
 }
 
@@ -1004,15 +1010,6 @@ i8_peak_kernel(int iters, int n_cols, int depth_flags) {
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
                      : "memory");
     }
-}
-
-void launch_band_tc_mfree(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
-    if (args.n_qtiles <= 0) return;
-    install_hang_word();
-    CUDA_CHECK(cudaFuncSetAttribute(band_tc_mfree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMSmemBytes));
-    const int pairs = args.n_qtiles < sm_count / 2 ? args.n_qtiles : sm_count / 2;
-    band_tc_mfree_kernel<<<2 * pairs, kMThreads, kMSmemBytes, st>>>(maps->g, maps->ha, args);
-    CUDA_CHECK(cudaGetLastError());
 }
 
 void launch_i8_peak(int iters, int n_cols, int per_commit, int depth, int sm_count, cudaStream_t st) {

@@ -92,8 +92,8 @@ struct BandArgs {
     const QTile* qtiles;        // missing-free supertiles of the same chunk (band_tc_mfree_kernel), same slots
     int32_t n_qtiles;
     const uint32_t* mfree_flag; // per chunk, written on the device after the chunk's stats: 1 = no kept SNP of the chunk's
-                                // column range has a missing genotype.  The wide kernel returns at once when it reads 1, the
-                                // missing-free kernel when it reads 0; null = the missing-free path is off
+                                // column range has a missing genotype: the launch then scores `qtiles` (2 planes) instead of
+                                // `tiles` (6 planes); null = the missing-free path is off
     const uint32_t* ready_rows; // fused launch (one band launch per shard): ring rows [0, *ready_rows) are unpacked and their
                                 // per-SNP statistics final; published after every chunk's unpack + stats.  null = everything is ready
     int32_t no_skip;            // A/B: score the out-of-window column groups too (NLDSC_NOSKIP=1)
@@ -139,7 +139,6 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
 void band_maps_destroy(BandMaps*);
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);
 void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);   // tiles carry b_row2
-void launch_band_tc_mfree(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st);  // args.qtiles
 // blk_miss[b] != 0: 64-SNP block b holds a kept SNP with a missing genotype (written by stats_kernel).  One block:
 // *flag = 1 if no block in [block0, block1) is marked, else 0.
 void launch_chunk_mfree_flag(const uint8_t* blk_miss, int32_t block0, int32_t block1, uint32_t* flag, cudaStream_t st);

@@ -23,6 +23,8 @@
 #include <thread>
 #include <unistd.h>
 
+#include <nvtx3/nvToolsExt.h>      // header-only NVTX v3: ranges cost nothing unless a profiler is attached
+
 using namespace nldsc;
 
 namespace nldsc {
@@ -428,6 +430,13 @@ int32_t floor64(int32_t x) { return x & ~63; }
 
 cudaEvent_t ev_get(int device, bool timing);     // per-device pools, defined below
 void preload_kernels(int device);
+
+// NVTX range over a host phase of a call: nsys / ncu timelines show open / upload / plan / run /
+// download per shard, and one range per chunk inside run.
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 struct SpanScope {
     nldsc_ld_session* s;
@@ -1246,6 +1255,9 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     try {
     for (size_t ci = 0; ci < s->chunks.size(); ++ci) {
         const Chunk& c = s->chunks[ci];
+        char chunk_tag[48];
+        snprintf(chunk_tag, sizeof(chunk_tag), "nldsc_ld chunk %zu", ci);
+        NvtxRange chunk_range(chunk_tag);
         const bool odd = two_band && (ci & 1);
         cudaStream_t bs = odd ? s->band2_stream : st;
         const int32_t r0 = std::min(c.new_row0, s->n_load), r1 = std::min(c.new_row1, s->n_load);
@@ -1324,11 +1336,6 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             else
                 (s->wide ? launch_band_tc_wide : launch_band_tc)(s->maps, a, s->sm_count, bs);
             ++s->launches;
-            // both kernels are launched; the one the chunk's flag does not select returns at once
-            if (mfree && c.n_qtiles > 0) {
-                launch_band_tc_mfree(s->maps, a, s->sm_count, bs);
-                ++s->launches;
-            }
         }
         if (overlap) CUDA_CHECK(cudaEventRecord(s->ev_band[ci], bs));
         // fused-capable plans number their slots shard-wide: the chunk's partials start at its slot_base
@@ -1516,17 +1523,33 @@ void run_sharded(const nldsc_ld_params* p_in, nldsc_ld_result* out, StartUpload&
         try {
             // one shard = the whole file: its load range needs no windows, so the packed rows start crossing
             // PCIe before anything is planned (windows and plan travel by SM copies, not the copy engine)
-            if (whole) s = session_open(j.device, p, 0, p->n_snp);
-            else s = session_open(j.device, p, floor64(lo[j.row_begin]), hi[j.row_end - 1] + 1);
-            if (uv.any()) s->h_unused.assign(uv.unused.begin() + s->load_begin, uv.unused.begin() + s->load_end);
+            char tag[64];
+            snprintf(tag, sizeof(tag), "nldsc_ld shard gpu%d rows %d-%d", j.device, j.row_begin, j.row_end);
+            NvtxRange shard_range(tag);
+            {
+                NvtxRange r("nldsc_ld open");
+                if (whole) s = session_open(j.device, p, 0, p->n_snp);
+                else s = session_open(j.device, p, floor64(lo[j.row_begin]), hi[j.row_end - 1] + 1);
+                if (uv.any()) s->h_unused.assign(uv.unused.begin() + s->load_begin, uv.unused.begin() + s->load_end);
+            }
             t1 = now();
-            start_upload(s);
+            {
+                NvtxRange r("nldsc_ld upload start");
+                start_upload(s);
+            }
             t2 = now();
-            if (whole) session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true, p->positions, p->ld_wind);
-            else session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true);
+            {
+                NvtxRange r("nldsc_ld plan");
+                if (whole) session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true, p->positions, p->ld_wind);
+                else session_plan(s, j.row_begin, j.row_end, lo, hi, /*ramp=*/true);
+            }
             t3 = now();
-            session_run(s, nullptr);
+            {
+                NvtxRange r("nldsc_ld run (issue)");
+                session_run(s, nullptr);
+            }
             t4 = now();
+            NvtxRange dl_range("nldsc_ld download + sync");
             nldsc_ld_result sub = *out;
             sub.l2 += j.row_begin; sub.l2d += j.row_begin; sub.maf += j.row_begin;
             sub.residuals_std += j.row_begin; sub.l2_ws += j.row_begin; sub.l2d_ws += j.row_begin;
