@@ -916,8 +916,13 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // last byte has landed: cap it in BYTES (NLDSC_CHUNK_BYTES, default 256 MB = ~5 ms of PCIe) so that wait
     // stays short when rows are long (N = 315,599: 16,384 rows would be 1.3 GB = 24 ms).
     const size_t byte_rows = std::max<size_t>(2048, env_size("NLDSC_CHUNK_BYTES", size_t(256) << 20) / static_cast<size_t>(s->bps) / kBlk * kBlk);
+    // Short rows (N < 4,096: reference panels such as 1000 Genomes) make a supertile so cheap that 8,192 rows are only a few
+    // waves of them, and the per-launch ramp and tail dominate -- above all for the missing-free supertiles, which cover four
+    // times the pairs each: 32,768 rows there (N = 2,504 missing-free: 0.72 vs 1.04 ms per 100,000 SNPs; with missing data 1.31
+    // vs 1.33; at N = 10,000 the 6-plane path loses 1 % to 16,384-row chunks: profiles/r02k_ab_chunks_*.json).
+    const size_t base_rows = s->npad < 4096 ? 32768 : 8192;
     const int32_t chunk_rows = static_cast<int32_t>(
-        std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? std::min<size_t>(8192, byte_rows) : 8192),
+        std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? std::min<size_t>(base_rows, byte_rows) : base_rows),
                          static_cast<size_t>(std::numeric_limits<int32_t>::max() / 2)));
     // without a concurrent upload a short first chunk still pays: its unpack is the only one that runs alone
     const char* rp = getenv("NLDSC_RAMP");
@@ -926,7 +931,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // (~0.7 ms of PCIe, ~40 MB), so its kernels neither wait for data nor start needlessly small
     const int64_t landed = static_cast<int64_t>(env_size("NLDSC_FIRST_BYTES", size_t(40) << 20)) / std::max<int64_t>(1, s->bps);
     const int32_t first_rows = static_cast<int32_t>(std::min<int64_t>(chunk_rows, std::max<int64_t>(512, landed / kBlk * kBlk)));
-    int32_t ramp_rows = (ramp0 && !fixed_rows) ? (ramp ? first_rows : 8192) : chunk_rows;
+    int32_t ramp_rows = (ramp0 && !fixed_rows) ? (ramp ? first_rows : static_cast<int32_t>(base_rows)) : chunk_rows;
     const char* tp = getenv("NLDSC_TAPER");
     // taper the chunk size towards the end of the shard only when the upload is clearly the longer pole
     // (narrow windows / few organisms): then the last chunk starts when the last byte lands and its length
