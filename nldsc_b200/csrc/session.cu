@@ -658,9 +658,11 @@ static void session_upload_file(nldsc_ld_session* s, int fd) {
     s->upload_started = true;
     const int32_t n_pieces = static_cast<int32_t>(s->ev_piece.size());
     s->piece_done.assign(n_pieces, 0);
-    // NLDSC_READERS: reader threads of this shard (default and maximum 4).  A driver that keeps several GPUs busy
+    // NLDSC_READERS: reader threads of this shard (default min(8, cores / 2), at most 8).  A driver that keeps several GPUs busy
     // from one host sets it to cores / GPUs, so that the readers of all shards together do not oversubscribe the host.
-    const int want_readers = static_cast<int>(std::min<size_t>(HostStage::kReaders, std::max<size_t>(1, env_size("NLDSC_READERS", HostStage::kReaders))));
+    const size_t hw = std::max<size_t>(1, std::thread::hardware_concurrency());
+    const size_t dflt_readers = std::min<size_t>(HostStage::kReaders, std::max<size_t>(2, hw / 2));
+    const int want_readers = static_cast<int>(std::min<size_t>(HostStage::kReaders, std::max<size_t>(1, env_size("NLDSC_READERS", dflt_readers))));
     const int n_readers = std::max(1, std::min<int>(want_readers, n_pieces));
     // NLDSC_ODIRECT=1: read the .bed past the page cache (O_DIRECT), for files that are read once and are larger than
     // the host's memory can usefully cache (a 94.7 GB UK-Biobank-scale genome).  The byte range of a slot is widened

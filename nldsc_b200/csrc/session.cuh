@@ -57,7 +57,8 @@ void arena_trim(int device);          // frees the cached blocks (device < 0: ev
 // Pinned staging ring for reading a .bed: kSlots slots the reader thread fills by pread and drains by
 // cudaMemcpyAsync; cached per device like the Arena (pinning memory costs tens of ms).
 struct HostStage {
-    static constexpr int kReaders = 4;            // reader threads: one pread stream copies ~10 GB/s, PCIe takes 55
+    static constexpr int kReaders = 8;            // most reader threads a shard may use: one pread stream copies ~10 GB/s out of
+                                                  // the page cache, PCIe takes 55; the default is min(8, max(2, cores / 2))
     static constexpr int kSlots = 2 * kReaders;   // two slots per reader
     int device = -1;
     bool cached = false;

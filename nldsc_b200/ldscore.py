@@ -258,7 +258,7 @@ def estimate_lds_genome(bfile: str, ld_wind: float, wind_metric: str, maf_thr: f
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     own_readers = "NLDSC_READERS" not in os.environ and n_dev > 1
     if own_readers:
-        os.environ["NLDSC_READERS"] = str(max(1, min(4, cores // n_dev)))
+        os.environ["NLDSC_READERS"] = str(max(1, min(8, cores // n_dev)))
 
     # ---- 1. parse (processes) beside the device warm-up; the GPU threads below start on a chromosome as soon as ITS
     # parse is done, so only the first parse is on the critical path

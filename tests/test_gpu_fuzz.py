@@ -146,3 +146,30 @@ def test_midsize_case_variants_bitwise(seed, monkeypatch):
             got = capi.calculate_packed(packed, *args)
         for key in RESULT_KEYS:
             assert np.array_equal(got[key], base[key], equal_nan=True), f"{label} {variant}: {key} differs from the default run"
+
+
+# The oracle the cases above are graded against is the NumPy restatement; these go to the COMPILED reference itself
+# (oracle/_ref/libref_ld64.so: the reference's own sources, float storage promoted to double -- built by oracle/Makefile in the
+# build container and shipped to the GPU box with the tree), through a real .bed file.
+@pytest.mark.parametrize("seed", range(6))
+def test_random_case_matches_compiled_reference(seed, tmp_path):
+    from oracle import ref
+    if not ref.available(64):
+        pytest.skip("oracle/_ref/libref_ld64.so is not built on this box")
+    rng = np.random.default_rng(4000 + seed)
+    n_org = int(rng.choice([127, 300, 513, 1001, 1500]))
+    n_snp = int(rng.choice([129, 333, 640, 900]))
+    missing = float(rng.choice([0.0, 0.02, 0.1]))
+    wind = float(rng.choice([0.1, 0.5, 1.0]))
+    spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=missing, seed=4500 + seed, density=float(rng.choice([100.0, 340.0])))
+    packed = synth.generate_packed(spec, workers=1)
+    cm, _ = synth.genetic_map(spec)
+    bed = tmp_path / "c.bed"
+    with open(bed, "wb") as f:
+        f.write(synth.BED_MAGIC)
+        f.write(packed.tobytes())
+    a = (n_snp, n_org, cm, wind, 1e-4, 1e-5, 1.0 / n_snp)
+    want = ref.calculate(str(bed), *a, flavour=64)
+    label = f"compiled reference, seed {seed}: N={n_org} M={n_snp} miss={missing} wind={wind}"
+    assert_ld_close(capi.calculate(str(bed), *a), want, label=label + " (.bed)")
+    assert_ld_close(capi.calculate_packed(packed, *a), want, label=label + " (packed)")
