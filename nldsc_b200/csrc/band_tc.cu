@@ -1,5 +1,11 @@
 // Banded int8 cross-count GEMM on the 5th-gen tensor cores + fused FP64 epilogue.
 //
+// Three bodies, one pipeline (TMA producer warp, one MMA-issuing thread per CTA pair, epilogue warps, mbarrier hand-offs):
+//   band_tc_kernel        narrow: 2 i-blocks x 1 j-block, accumulator double-buffered        (NLDSC_WIDE=0; second implementation)
+//   band_wide_body        wide:   2 i-blocks x 2 j-blocks, 6 cross-counts per pair            (the default)
+//   band_mfree_body       4 i-blocks x 2 j-blocks, 2 cross-counts per pair, for chunks without a missing genotype
+// The last two share the launch band_tc_wide_kernel; a per-chunk flag written on the device picks the body.
+//
 // Replaces the pair loop of calculate() (reference ldscalc.h:34-47) and the two
 // arma::dot calls per ordered pair in Math::r2_adjusted (tools.h:87-92).
 //
@@ -721,7 +727,15 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
 #pragma unroll
                     for (int kk = 0; kk < kKStep / 32; ++kk)
                         tc_mma_i8(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdescM, (k | kk) != 0);
-                    tc_commit_pair(&empty[stage]);
+                    // A commit costs the tensor pipe ~220 clk (i8 peak probe: N = 256 reaches 3,400 TOP/s at 4 MMAs per commit,
+                    // 4,580 at 8).  commit2: release the operand ring two stages at a time -- 8 MMAs per commit; the 6 x 32 KB
+                    // ring is then three 64 KB granules deep.
+                    if (!args.commit2) {
+                        tc_commit_pair(&empty[stage]);
+                    } else if ((k & 1) || k == args.k_steps - 1) {
+                        if (k & 1) tc_commit_pair(&empty[stage == 0 ? kMStages - 1 : stage - 1]);
+                        tc_commit_pair(&empty[stage]);
+                    }
                     if (++stage == kMStages) { stage = 0; phase ^= 1; }
                 }
                 tc_commit_pair(&tfull[buf]);

@@ -44,11 +44,11 @@ struct Tile {
     int32_t slot;      // where its partial row sums go: position in i-pair-major order (what finalize walks), which is
                        // NOT the execution order -- tiles of 8 i-pairs are interleaved by j-block so that concurrent
                        // CTA pairs share B operands in L2 as well as A (wide windows would otherwise stream B from HBM)
-    int32_t b_row2;    // wide supertiles (band_tc_wide_kernel, large N): ring row of a SECOND j-block j0 + 64 scored from
+    int32_t b_row2;    // wide supertiles (band_tc_wide_kernel, the default): ring row of a SECOND j-block j0 + 64 scored from
                        // the same A tiles (its partials go to slot + 1), or -1.  Unused (0) by the narrow kernel.
 };
 
-// Missing-free supertile (band_tc_mfree_kernel): FOUR consecutive 64-SNP i-blocks (cluster rank r owns blocks 2r, 2r+1 =
+// Missing-free supertile (band_mfree_body of band_tc_wide_kernel): FOUR consecutive 64-SNP i-blocks (cluster rank r owns blocks 2r, 2r+1 =
 // one i-pair of the slot scheme) x the even-aligned PAIR of j-blocks starting at j0.  Without missing genotypes only the
 // two cross-counts g x {h, a} are needed (SURVEY.md section 8d "4*N int8 ops"), so the 128 MMA rows of a CTA hold g of
 // 128 i-SNPs and one N = 256 accumulator holds [h | a] of 128 j-SNPs: a third of the MMA work per SNP pair.
@@ -89,7 +89,7 @@ struct BandArgs {
     double rsq_thr;
     Partials part;
     int32_t* dump;              // optional raw accumulators [tile][rank][128][192] (parity hook)
-    const QTile* qtiles;        // missing-free supertiles of the same chunk (band_tc_mfree_kernel), same slots
+    const QTile* qtiles;        // missing-free supertiles of the same chunk (band_mfree_body), same slots
     int32_t n_qtiles;
     const uint32_t* mfree_flag; // per chunk, written on the device after the chunk's stats: 1 = no kept SNP of the chunk's
                                 // column range has a missing genotype: the launch then scores `qtiles` (2 planes) instead of

@@ -108,7 +108,7 @@ __device__ __forceinline__ void pair_eval_core(const BandArgs& a, const RowCtx& 
 }
 
 // The same pair when neither SNP block holds a missing genotype: G_gm = G_mm = G_mh = G_ma = 0 exactly, so only
-// G_gh and G_ga arrive (band_tc_mfree_kernel).  Bitwise equal to pair_eval_core on those counts.
+// G_gh and G_ga arrive (band_mfree_body).  Bitwise equal to pair_eval_core on those counts.
 __device__ __forceinline__ void pair_eval_mfree(const BandArgs& a, const RowCtx& r, int32_t gj, uint8_t fj, const double2 c0,
                                                 const double2 c1, const double2 c2, const double2 c3,
                                                 int32_t Ggh, int32_t Gga, RowAcc& acc) {

@@ -96,8 +96,8 @@ struct nldsc_ld_session {
     int32_t npad = 0;
     double maf_thr = 0, std_thr = 0, rsq_thr = 0;
     bool use_simt = false;
-    bool wide = false;                        // band_tc_wide_kernel: two j-blocks per supertile (N >= 65,536, or NLDSC_WIDE=1)
-    bool mfree = false;                       // plan carries missing-free supertiles; chunks without a missing genotype take band_tc_mfree_kernel
+    bool wide = false;                        // band_tc_wide_kernel: two j-blocks per supertile (the default; NLDSC_WIDE=0 = narrow kernel)
+    bool mfree = false;                       // plan carries missing-free supertiles; chunks without a missing genotype take the 2-plane body of the band kernel
     nldsc::QTile* d_qtiles = nullptr;
     uint8_t* d_blk_miss = nullptr;            // [n_load_pad / 64] written by stats_kernel
     uint32_t* d_mfree_flags = nullptr;        // [chunks] 1 = the chunk is missing-free (launch_chunk_mfree_flag)

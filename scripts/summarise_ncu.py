@@ -66,7 +66,8 @@ def main():
              "--no-cpu-baseline` (cold-cache, serialised: compare SHARES)", f"{'kernel':60s} {'launches':>8s} {'ms':>10s} {'share':>7s}"]
         for k, v in tot.most_common():
             o.append(f"{k[:60]:60s} {cnt[k]:8d} {v:10.3f} {100 * v / s:6.1f}%")
-        ours = [k for k in tot if any(t in k for t in ("band_", "unpack_", "count_", "stats_", "finalize_", "zero_rows"))]
+        # the step's kernels (the int8 peak probe and the plan-time kernels are the engine's too, but not part of a step)
+        ours = [k for k in tot if any(t in k for t in ("band_", "unpack_", "count_", "stats_", "finalize_", "zero_rows", "chunk_mfree", "publish_rows"))]
         so = sum(tot[k] for k in ours)
         o.append("")
         o.append("# shares among the engine's own kernels (the synthetic-data generator's torch kernels excluded)")
