@@ -191,6 +191,12 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
  * ("the int8 peak must be measured on the box"). */
 int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t depth, int32_t iters, int32_t reps,
                            float* ms_out, double* tops_out, char* err, size_t errlen);
+/* Measurement hook: the host's H2D ceiling with n_devices GPUs uploading at once.  Every device (own host thread) copies a
+ * pinned host buffer of `bytes` (cudaHostAllocDefault, or cudaHostAllocWriteCombined when write_combined != 0) to its HBM
+ * `reps` times, all starting together; gbs_out[k] = GB/s of device first_device + k.  (what bounds the
+ * end-to-end call when 4 or 8 GPUs upload at the same time.) */
+int nldsc_ld_debug_h2d_probe(int64_t bytes, int32_t write_combined, int32_t first_device, int32_t n_devices, int32_t reps,
+                             double* gbs_out, char* err, size_t errlen);
 /* Number of usable CUDA devices (0 and an error message when none). */
 int nldsc_ld_device_count(int32_t* count, char* err, size_t errlen);
 

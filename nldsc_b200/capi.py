@@ -24,7 +24,7 @@ EXPORTS = [
     "nldsc_ld_debug_unpack", "nldsc_ld_debug_cross_counts", "nldsc_ld_device_count",
     "nldsc_ld_plan_windows", "nldsc_ld_plan_shards", "nldsc_ld_debug_band_probe", "nldsc_ld_debug_plan_windows_device",
     "nldsc_ld_calculate_on", "nldsc_ld_debug_i8_peak", "nldsc_ld_last_call_report", "nldsc_ld_arena_trim",
-    "nldsc_ld_calculate_packed_on", "nldsc_ld_warmup",
+    "nldsc_ld_calculate_packed_on", "nldsc_ld_warmup", "nldsc_ld_debug_h2d_probe",
 ]
 
 
@@ -336,3 +336,12 @@ def last_call_report() -> list[dict]:
 def arena_trim(device: int = -1) -> None:
     """Give the device memory cached between calls back to the driver (all devices when device < 0)."""
     lib().nldsc_ld_arena_trim(C.c_int32(device))
+
+
+def debug_h2d_probe(nbytes: int, n_devices: int, write_combined: bool = False, first_device: int = 0, reps: int = 4) -> list[float]:
+    """GB/s per device of n_devices simultaneous pinned-host -> HBM copies (default or write-combined pinned memory)."""
+    out = (C.c_double * n_devices)()
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_h2d_probe(C.c_int64(nbytes), C.c_int32(1 if write_combined else 0), C.c_int32(first_device),
+                                          C.c_int32(n_devices), C.c_int32(reps), out, err, C.c_size_t(512)), err)
+    return [float(x) for x in out]

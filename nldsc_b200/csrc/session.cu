@@ -2129,6 +2129,63 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
     });
 }
 
+int nldsc_ld_debug_h2d_probe(int64_t bytes, int32_t write_combined, int32_t first_device, int32_t n_devices, int32_t reps,
+                             double* gbs_out, char* err, size_t errlen) {
+    return guarded(err, errlen, [&] {
+        const int ndev = usable_devices();
+        if (bytes <= 0 || n_devices < 1 || first_device < 0 || first_device + n_devices > ndev || reps < 1 || !gbs_out)
+            throw InvalidArgument("bad arguments");
+        std::vector<std::thread> th;
+        std::vector<std::string> errs(static_cast<size_t>(n_devices));
+        std::mutex mu;
+        std::condition_variable cv;
+        int ready = 0;
+        for (int k = 0; k < n_devices; ++k) {
+            th.emplace_back([&, k] {
+                void* h = nullptr;
+                void* d = nullptr;
+                cudaStream_t st = nullptr;
+                cudaEvent_t e0 = nullptr, e1 = nullptr;
+                try {
+                    CUDA_CHECK(cudaSetDevice(first_device + k));
+                    CUDA_CHECK(cudaHostAlloc(&h, static_cast<size_t>(bytes), write_combined ? cudaHostAllocWriteCombined : cudaHostAllocDefault));
+                    memset(h, 0x5A, static_cast<size_t>(bytes));
+                    CUDA_CHECK(cudaMalloc(&d, static_cast<size_t>(bytes)));
+                    CUDA_CHECK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+                    CUDA_CHECK(cudaEventCreate(&e0));
+                    CUDA_CHECK(cudaEventCreate(&e1));
+                    CUDA_CHECK(cudaMemcpyAsync(d, h, static_cast<size_t>(bytes), cudaMemcpyHostToDevice, st));
+                    CUDA_CHECK(cudaStreamSynchronize(st));
+                    {   // all devices start their timed copies together
+                        std::unique_lock<std::mutex> g(mu);
+                        if (++ready == n_devices) cv.notify_all();
+                        else cv.wait(g, [&] { return ready >= n_devices; });
+                    }
+                    CUDA_CHECK(cudaEventRecord(e0, st));
+                    for (int r = 0; r < reps; ++r) CUDA_CHECK(cudaMemcpyAsync(d, h, static_cast<size_t>(bytes), cudaMemcpyHostToDevice, st));
+                    CUDA_CHECK(cudaEventRecord(e1, st));
+                    CUDA_CHECK(cudaEventSynchronize(e1));
+                    float ms = 0;
+                    CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+                    gbs_out[k] = static_cast<double>(bytes) * reps / (ms * 1e-3) / 1e9;
+                } catch (const std::exception& e) {
+                    errs[static_cast<size_t>(k)] = e.what();
+                    std::lock_guard<std::mutex> g(mu);
+                    ++ready;
+                    cv.notify_all();
+                }
+                if (e0) cudaEventDestroy(e0);
+                if (e1) cudaEventDestroy(e1);
+                if (st) cudaStreamDestroy(st);
+                if (d) cudaFree(d);
+                if (h) cudaFreeHost(h);
+            });
+        }
+        for (auto& t : th) t.join();
+        for (const auto& e : errs) if (!e.empty()) throw CudaError(e);
+    });
+}
+
 int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t depth, int32_t iters, int32_t reps, float* ms_out,
                            double* tops_out, char* err, size_t errlen) {
     return guarded(err, errlen, [&] {

@@ -47,7 +47,7 @@ for gpus in gpu_counts:
         t0 = time.perf_counter()
         summ = ldscore.estimate_lds_genome(f"{d}/g.@", 1.0, "cm", 1e-4, 1e-5, out_dir=f"{d}/out", gpus=gpus)
         runs.append(time.perf_counter() - t0)
-        digests.append(hashlib.sha256(b"".join(open(f"{d}/out/{c}.L2", "rb").read() for c in range(1, 6))).hexdigest())
+        digests.append(hashlib.sha256(b"".join(open(f"{d}/out/{c}.L2", "rb").read() for c in CHROMS)).hexdigest())
     pairs = 0
     for c in CHROMS:
         df = pd.read_csv(f"{d}/out/{c}.L2", sep="\t")
