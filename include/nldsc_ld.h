@@ -106,7 +106,7 @@ typedef struct nldsc_ld_stats {
     int32_t kernel_launches;  /* kernels launched by the last run() */
     int32_t load_begin;       /* first SNP row the shard needs (owned range minus halo, 64-aligned) */
     int32_t load_end;         /* one past the last SNP row needed */
-    int32_t npad;             /* padded organisms per plane row (bytes) */
+    int32_t npad;             /* bytes per plane row: padded organisms with int8 planes, half of them with fp4 planes */
     int32_t band_impl;        /* 1 = tcgen05 kernel, 2 = its wide variant (two j-blocks per supertile; the default at every N), 0 = SIMT yardstick (NLDSC_BAND=simt) */
     float ms_count;           /* CUDA-event times of the last run(), per kernel family; counting is fused
                                  into the unpack kernel, so this one stays 0 */
@@ -117,7 +117,7 @@ typedef struct nldsc_ld_stats {
     float ms_total;
     /* missing-free path (band_tc_mfree_kernel: the two cross-counts g x {h, a} instead of six): */
     int32_t mfree_chunks;     /* chunks of the last run() whose columns held no missing genotype and took it */
-    int32_t pad_;
+    int32_t fp4;              /* 1 = the planes hold e2m1 (fp4) nibbles and the band kernel multiplies them with kind::mxf4 */
     int64_t qtiles;           /* missing-free supertiles planned (4 i-blocks x 2 j-blocks each), all chunks */
     int64_t mfree_qtiles;     /* ... of the chunks that took the path in the last run() */
     int64_t mfree_tiles_skipped;   /* 6-plane supertiles (wide: 2 i-blocks x <= 2 j-blocks) those chunks did NOT run */
@@ -169,6 +169,10 @@ int nldsc_ld_arena_trim(int32_t device);
  * g,m,h,a (npad returned), counts_out = int32 [n_snp][3] = n_het, n_hom2, n_missing. */
 int nldsc_ld_debug_unpack(const uint8_t* packed, int32_t n_snp, int32_t n_org, int8_t* planes_out,
                           int32_t* counts_out, int32_t* npad_out, char* err, size_t errlen);
+/* The same through the fp4 unpack kernel: planes_out = bytes [4][n_snp][npad] with npad = plane row bytes (returned), two
+ * organisms per byte (organism 2i in the low nibble), every value an e2m1 nibble: 0 -> 0x0, 1 -> 0x2, 2 -> 0x4. */
+int nldsc_ld_debug_unpack_fp4(const uint8_t* packed, int32_t n_snp, int32_t n_org, int8_t* planes_out,
+                              int32_t* counts_out, int32_t* npad_out, char* err, size_t errlen);
 /* Raw band-kernel accumulators for SNP block pair (i_block, j_block) (64 SNPs each):
  * acc_out = int32 [128][192]; row 32*(s/16) + 16*p + s%16 is SNP s of the i block,
  * left plane p (0 = g, 1 = m); column 64*q + t is SNP t of the j block, right plane q
@@ -191,6 +195,12 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
  * ("the int8 peak must be measured on the box"). */
 int nldsc_ld_debug_i8_peak(int32_t n_cols, int32_t per_commit, int32_t depth, int32_t iters, int32_t reps,
                            float* ms_out, double* tops_out, char* err, size_t errlen);
+/* Feasibility probe (measurement only): n_mma accumulating tcgen05.mma.kind::mxf4 (fp4 e2m1 operands holding 0 / 1 / 2, all
+ * scale factors 1.0; M = 256, N = n_cols, K = 64) on known operand patterns; out = float [2][128][16]: the first 16
+ * accumulator columns of every row of the first CTA pair; ms_out = kernel time (all_pairs != 0: on every CTA pair, for the rate).
+ * Asks whether the fp4 pipe sums small integers exactly -- the precondition for running the cross-count GEMM on it. */
+int nldsc_ld_debug_fp4_probe(int32_t n_mma, int32_t n_cols, int32_t per_commit, int32_t all_pairs, float* out, float* ms_out,
+                             char* err, size_t errlen);
 /* Measurement hook: the host's H2D ceiling with n_devices GPUs uploading at once.  Every device (own host thread) copies a
  * pinned host buffer of `bytes` (cudaHostAllocDefault, or cudaHostAllocWriteCombined when write_combined != 0) to its HBM
  * `reps` times, all starting together; gbs_out[k] = GB/s of device first_device + k.  (what bounds the

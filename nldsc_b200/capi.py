@@ -24,7 +24,8 @@ EXPORTS = [
     "nldsc_ld_debug_unpack", "nldsc_ld_debug_cross_counts", "nldsc_ld_device_count",
     "nldsc_ld_plan_windows", "nldsc_ld_plan_shards", "nldsc_ld_debug_band_probe", "nldsc_ld_debug_plan_windows_device",
     "nldsc_ld_calculate_on", "nldsc_ld_debug_i8_peak", "nldsc_ld_last_call_report", "nldsc_ld_arena_trim",
-    "nldsc_ld_calculate_packed_on", "nldsc_ld_warmup", "nldsc_ld_debug_h2d_probe",
+    "nldsc_ld_calculate_packed_on", "nldsc_ld_warmup", "nldsc_ld_debug_h2d_probe", "nldsc_ld_debug_fp4_probe",
+    "nldsc_ld_debug_unpack_fp4",
 ]
 
 
@@ -46,7 +47,7 @@ class Stats(C.Structure):
                 ("kernel_launches", C.c_int32), ("load_begin", C.c_int32), ("load_end", C.c_int32),
                 ("npad", C.c_int32), ("band_impl", C.c_int32), ("ms_count", C.c_float),
                 ("ms_stats", C.c_float), ("ms_unpack", C.c_float), ("ms_band", C.c_float),
-                ("ms_finalize", C.c_float), ("ms_total", C.c_float), ("mfree_chunks", C.c_int32), ("pad_", C.c_int32),
+                ("ms_finalize", C.c_float), ("ms_total", C.c_float), ("mfree_chunks", C.c_int32), ("fp4", C.c_int32),
                 ("qtiles", C.c_int64), ("mfree_qtiles", C.c_int64), ("mfree_tiles_skipped", C.c_int64)]
 
 
@@ -345,3 +346,33 @@ def debug_h2d_probe(nbytes: int, n_devices: int, write_combined: bool = False, f
     _raise(lib().nldsc_ld_debug_h2d_probe(C.c_int64(nbytes), C.c_int32(1 if write_combined else 0), C.c_int32(first_device),
                                           C.c_int32(n_devices), C.c_int32(reps), out, err, C.c_size_t(512)), err)
     return [float(x) for x in out]
+
+
+def debug_fp4_probe(n_mma: int, n_cols: int = 256, per_commit: int = 8, all_pairs: bool = False) -> dict:
+    """Accumulating fp4 (mxf4, scale 1.0) MMAs on known integer patterns -> accumulator columns 0..15 of the first CTA pair."""
+    out = np.zeros((2, 128, 16), np.float32)
+    ms = C.c_float(0)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_fp4_probe(C.c_int32(n_mma), C.c_int32(n_cols), C.c_int32(per_commit), C.c_int32(1 if all_pairs else 0),
+                                          out.ctypes.data_as(C.POINTER(C.c_float)), C.byref(ms), err, C.c_size_t(512)), err)
+    pairs = 74 if all_pairs else 1
+    return {"acc": out, "ms": ms.value, "tops_equiv": pairs * n_mma * 2.0 * 256 * n_cols * 64 / (ms.value * 1e-3) / 1e12}
+
+
+def debug_unpack_fp4(packed, n_org):
+    """-> planes int8-valued [4, n_snp, 2 * npad_bytes] (g, m, h, a) decoded from the fp4 planes' nibbles, counts [n_snp, 3]."""
+    a = np.ascontiguousarray(packed, dtype=np.uint8)
+    n_snp = a.shape[0]
+    npad = C.c_int32(0)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_unpack_fp4(C.c_void_p(a.ctypes.data), C.c_int32(n_snp), C.c_int32(n_org),
+                                           None, None, C.byref(npad), err, C.c_size_t(512)), err)
+    raw = np.empty((4, n_snp, npad.value), np.uint8)
+    counts = np.empty((n_snp, 3), np.int32)
+    _raise(lib().nldsc_ld_debug_unpack_fp4(C.c_void_p(a.ctypes.data), C.c_int32(n_snp), C.c_int32(n_org),
+                                           C.c_void_p(raw.ctypes.data), C.c_void_p(counts.ctypes.data),
+                                           C.byref(npad), err, C.c_size_t(512)), err)
+    nib = np.stack([raw & 0xF, raw >> 4], -1).reshape(4, n_snp, 2 * npad.value)      # organism 2i = low nibble of byte i
+    value = np.full(16, -1, np.int8)
+    value[[0x0, 0x2, 0x4]] = [0, 1, 2]                                               # e2m1: 0.0, 1.0, 2.0
+    return value[nib], counts

@@ -211,6 +211,49 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, int32_t (&v)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- fp4 (mxf4) operands: the same cross-counts at twice the int8 rate -------------------------------------------
+// Genotype planes hold 0 / 1 / 2, exact in e2m1; with every scale factor 2^0 tcgen05.mma.kind::mxf4 multiplies 64
+// organisms per instruction (32 operand bytes per row, as kind::i8 does for 32) and accumulates the small integer block
+// sums exactly in FP32 as long as a count stays below 2^24 (measured: nldsc_ld_debug_fp4_probe, 150,000 accumulating MMAs
+// to 14,400,000 exact).  The scale factors live in TMEM; the kernels store 1.0 everywhere in columns 448..479 once.
+__device__ __forceinline__ void tc_mma_mxf4(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t sfa,
+                                            uint32_t sfb, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::mxf4.block_scale.block32 [%0], %1, %2, %3, [%5], [%6], p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(sfa), "r"(sfb)
+        : "memory");
+}
+constexpr uint32_t kSfCols = 448;   // TMEM columns 448..479 hold scale factors 1.0 for every lane: any SF layout reads ones
+
+__device__ __forceinline__ void tmem_fill_sf_ones(uint32_t tmem_base, int warp_in_quarter_order) {
+    // 32 lanes of this warp's quarter x 32 columns of 0x7F7F7F7F (four E8M0 exponents of 2^0 per 32-bit column)
+    const uint32_t taddr = tmem_base + kSfCols + (static_cast<uint32_t>(32 * (warp_in_quarter_order & 3)) << 16);
+    const uint32_t v = 0x7F7F7F7Fu;
+#pragma unroll
+    for (int c = 0; c < 32; c += 16)
+        asm volatile(
+            "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};"
+            ::"r"(taddr + c), "r"(v)
+            : "memory");
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// FP32 accumulator (an exact integer below 2^22) -> int32 without the conversion pipe: add 1.5 * 2^23, read the mantissa
+__device__ __forceinline__ int32_t acc_f2i(int32_t bits) {
+    return __float_as_int(__int_as_float(bits) + 12582912.0f) - 0x4B400000;
+}
+__device__ __forceinline__ void acc_to_int(int32_t (&v)[16]) {
+#pragma unroll
+    for (int e = 0; e < 16; ++e) v[e] = acc_f2i(v[e]);
+}
+// instruction descriptor, block-scaled (cute/arch/mma_sm100_desc.hpp InstrDescriptorBlockScaled): A / B = e2m1 (1 at bits
+// 7 and 10), both K-major, N >> 3 at bit 17, scale format E8M0 (bit 23), M >> 4 at bit 24, K = 64 (bit 31 = 0)
+__device__ __forceinline__ constexpr uint32_t idesc_mxf4(uint32_t n_cols) {
+    return (1u << 7) | (1u << 10) | ((n_cols >> 3) << 17) | (1u << 23) | ((256u >> 4) << 24);
+}
+
 }  // namespace
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
@@ -446,6 +489,12 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (args.fp4) {                            // scale factors 1.0 for every lane of both CTAs, before the first MMA
+        if (warp >= 2 && warp < 6) tmem_fill_sf_ones(tmem_base, warp);
+        tc_fence_before();
+        cluster_sync_all();
+        tc_fence_after();
+    }
 
     if (warp == 0) {
         // ===== TMA producer: own A block, own half of one or two B blocks =====
@@ -502,13 +551,25 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
                     const uint64_t a_desc = make_smem_desc(sa);
                     const uint64_t b_desc = make_smem_desc(sa + kABytes);
                     const uint64_t b2_desc = make_smem_desc(sa + kABytes + kBBytes);
-#pragma unroll
-                    for (int kk = 0; kk < kKStep / 32; ++kk)
-                        tc_mma_i8(tmem_base, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (k | kk) != 0);
-                    if (two) {
+                    if (args.fp4) {            // 128 operand bytes per row = 256 organisms per stage, 64 per MMA
+                        const uint32_t sf = tmem_base + kSfCols;
 #pragma unroll
                         for (int kk = 0; kk < kKStep / 32; ++kk)
-                            tc_mma_i8(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, kIdesc, (k | kk) != 0);
+                            tc_mma_mxf4(tmem_base, a_desc + 2 * kk, b_desc + 2 * kk, idesc_mxf4(kBRows), sf, sf + 16, (k | kk) != 0);
+                        if (two) {
+#pragma unroll
+                            for (int kk = 0; kk < kKStep / 32; ++kk)
+                                tc_mma_mxf4(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, idesc_mxf4(kBRows), sf, sf + 16, (k | kk) != 0);
+                        }
+                    } else {
+#pragma unroll
+                        for (int kk = 0; kk < kKStep / 32; ++kk)
+                            tc_mma_i8(tmem_base, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (k | kk) != 0);
+                        if (two) {
+#pragma unroll
+                            for (int kk = 0; kk < kKStep / 32; ++kk)
+                                tc_mma_i8(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, kIdesc, (k | kk) != 0);
+                        }
                     }
                     if (!args.commit2) {
                         tc_commit_pair(&empty[stage]);
@@ -579,6 +640,7 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
                     tmem_ld16(taddr + col + 32, vh);
                     tmem_ld16(taddr + col + 64, va);
                     tmem_ld_wait();
+                    if (args.fp4) { acc_to_int(vm); acc_to_int(vh); acc_to_int(va); }    // FP32 accumulators holding exact counts
 #pragma unroll
                     for (int u = 0; u < 8; ++u) {
                         const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
@@ -685,6 +747,14 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
     cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // fp4: the scale factors take TMEM columns 448..479, so there is room for ONE 256-column accumulator: single-buffered
+    const bool one_buf = args.fp4 != 0;
+    if (args.fp4) {
+        if (warp >= 2 && warp < 6) tmem_fill_sf_ones(tmem_base, warp);
+        tc_fence_before();
+        cluster_sync_all();
+        tc_fence_after();
+    }
 
     if (warp == 0) {
         // ===== TMA producer: g of this CTA's two i-blocks, [h ; a] of the j-block of its rank =====
@@ -714,8 +784,8 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
             uint32_t phase = 0;
             int n = 0;
             for (int t = pair; t < args.n_qtiles; t += n_pairs, ++n) {
-                const int buf = n & 1;
-                mbar_wait(&tempty[buf], ((n >> 1) & 1) ^ 1, 12);   // both CTAs' epilogues drained this accumulator
+                const int buf = one_buf ? 0 : (n & 1);
+                mbar_wait(&tempty[buf], ((one_buf ? n : (n >> 1)) & 1) ^ 1, 12);   // both CTAs' epilogues drained this accumulator
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * 256;
                 for (int k = 0; k < args.k_steps; ++k) {
@@ -724,9 +794,16 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
                     const uint32_t sa = smem_u32(smem + stage * kMStageBytes);
                     const uint64_t a_desc = make_smem_desc(sa);
                     const uint64_t b_desc = make_smem_desc(sa + kMABytes);
+                    if (args.fp4) {
+                        const uint32_t sf = tmem_base + kSfCols;
 #pragma unroll
-                    for (int kk = 0; kk < kKStep / 32; ++kk)
-                        tc_mma_i8(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdescM, (k | kk) != 0);
+                        for (int kk = 0; kk < kKStep / 32; ++kk)
+                            tc_mma_mxf4(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, idesc_mxf4(256), sf, sf + 16, (k | kk) != 0);
+                    } else {
+#pragma unroll
+                        for (int kk = 0; kk < kKStep / 32; ++kk)
+                            tc_mma_i8(d_tmem, a_desc + 2 * kk, b_desc + 2 * kk, kIdescM, (k | kk) != 0);
+                    }
                     // A commit costs the tensor pipe ~220 clk (i8 peak probe: N = 256 reaches 3,400 TOP/s at 4 MMAs per commit,
                     // 4,580 at 8).  commit2: release the operand ring two stages at a time -- 8 MMAs per commit; the 6 x 32 KB
                     // ring is then three 64 KB granules deep.
@@ -751,7 +828,7 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
         const int blk = rho >> 6;                    // which i-block of the i-pair ("rank" of the slot scheme)
         int n = 0;
         for (int t = pair; t < args.n_qtiles; t += n_pairs, ++n) {
-            const int buf = n & 1;
+            const int buf = one_buf ? 0 : (n & 1);
             const QTile tl = args.qtiles[t];
             const int32_t i0 = tl.i0[2 * rank + blk];
             const RowCtx row = load_row_ctx(args, i0 == kDeadBlock ? kDeadBlock : i0 + (rho & 63));
@@ -770,7 +847,7 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
                 }
             }
             asm volatile("bar.sync 1, 256;" ::: "memory");
-            mbar_wait_idle(&tfull[buf], (n >> 1) & 1, 14);
+            mbar_wait_idle(&tfull[buf], (one_buf ? n : (n >> 1)) & 1, 14);
             tc_fence_after();
             const uint32_t taddr = tmem_base + buf * 256 + 128 * jj + (static_cast<uint32_t>(32 * q) << 16);
             const int32_t jbase = tl.j0 + kBlk * jj;
@@ -786,6 +863,7 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
                     tmem_ld16(taddr + 16 * c, vh);
                     tmem_ld16(taddr + kBlk + 16 * c, va);
                     tmem_ld_wait();
+                    if (args.fp4) { acc_to_int(vh); acc_to_int(va); }
 #pragma unroll
                     for (int u = 0; u < 16; ++u) {
                         const int jl = 16 * c + u;
@@ -1037,6 +1115,115 @@ void launch_i8_peak(int iters, int n_cols, int per_commit, int depth, int sm_cou
     else if (per_commit == 8) go(i8_peak_kernel<8>);
     else if (per_commit == 16) go(i8_peak_kernel<16>);
     else throw CudaError("i8 peak probe: per_commit must be 4, 8 or 16");
+}
+
+// ---- fp4 feasibility probe (measurement only) -----------------------------------------------------
+// Genotype planes hold 0 / 1 / 2, all exactly representable in e2m1 (fp4), and every cross-count is below 2^24: if
+// tcgen05.mma.kind::mxf4 (K = 64 per instruction, 2 x the int8 rate, half the operand bytes) accumulates small integers
+// EXACTLY in its FP32 accumulator, the band kernels can run on the fp4 pipe with all scale factors 1.0 and stay
+// bit-exact.  This kernel answers that on the box: one CTA pair, operands resident in shared memory with known nibble
+// patterns, `n_mma` accumulating MMAs (M = 256, N = n_cols), scale factors 2^0 (E8M0 127) stored once to TMEM with
+// tcgen05.st, then the first 16 accumulator columns of every row are written out as floats.
+// Expected with A = [1, 2, 1, 2, ...] along K in every row, B row 0 = e_0, B row 8 = e_0 + e_1 + e_2, other B rows all ones:
+//   column 0 = n_mma, column 8 = 4 n_mma, every other column = 96 n_mma  (if element 2i sits in the LOW nibble of byte i).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128, 1)
+fp4_probe_kernel(int n_mma, int n_cols, int per_commit, float* out) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 2 * kABytes);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 8);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    // A: 128 rows x 128 bytes, every byte 0x42 (element 2i = 0x2 = 1.0, element 2i+1 = 0x4 = 2.0); B: 128 rows, bytes 0x22 (ones)
+    for (int i = threadIdx.x; i < 2 * kABytes / 4; i += blockDim.x)
+        reinterpret_cast<uint32_t*>(smem)[i] = i < kABytes / 4 ? 0x42424242u : 0x22222222u;
+    __syncthreads();
+    if (rank == 0 && threadIdx.x == 0) {
+        // rows 0 and 8 of the leader's half of B: row r of a 128B-swizzled tile starts at r * 128 and rows with r % 8 == 0 are
+        // stored unpermuted.  Only K elements 0..63 (bytes 0..31) are ever multiplied.
+        uint8_t* b0 = smem + kABytes;
+        for (int k = 0; k < 32; ++k) { b0[k] = 0; b0[8 * 128 + k] = 0; }
+        b0[0] = 0x02;                    // e_0
+        b0[8 * 128 + 0] = 0x22;          // e_0 + e_1
+        b0[8 * 128 + 1] = 0x02;          // + e_2
+    }
+    if (warp == 0 && lane == 0) {
+        for (int d = 0; d < 8; ++d) mbar_init(&bar[d], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    tmem_fill_sf_ones(tmem_base, warp);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    if (warp == 1 && lane == 0 && rank == 0) {
+        // block-scaled descriptor (cute/arch/mma_sm100_desc.hpp InstrDescriptorBlockScaled): a/b format E2M1 = 1 (bits 7, 10),
+        // N >> 3 at bit 17, scale format E8M0 = 1 at bit 23, M >> 4 at bit 24, K = 64 (bit 31 = 0), both K-major
+        const uint32_t idesc = (1u << 7) | (1u << 10) | ((static_cast<uint32_t>(n_cols) >> 3) << 17) | (1u << 23) | ((256u >> 4) << 24);
+        const uint64_t a_desc = make_smem_desc(smem_u32(smem));
+        const uint64_t b_desc = make_smem_desc(smem_u32(smem) + kABytes);
+        const uint32_t sfa = tmem_base + kSfCols, sfb = tmem_base + kSfCols + 16;
+        int issued = 0, it = 0;
+        while (issued < n_mma) {
+            const int d = it & 3;
+            if (it >= 4) mbar_wait(&bar[d], ((it >> 2) - 1) & 1, 9);
+            tc_fence_after();
+            for (int m = 0; m < per_commit && issued < n_mma; ++m, ++issued)
+                tc_mma_mxf4(tmem_base, a_desc, b_desc, idesc, sfa, sfb, issued != 0);
+            tc_commit_pair(&bar[d]);
+            ++it;
+        }
+        for (int k = it > 4 ? it - 4 : 0; k < it; ++k) mbar_wait(&bar[k & 3], (k >> 2) & 1, 9);
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    {
+        int32_t v[16];
+        tmem_ld16(tmem_base + (static_cast<uint32_t>(32 * warp) << 16), v);
+        tmem_ld_wait();
+        float* o = out + (static_cast<size_t>(rank) * 128 + 32 * warp + lane) * 16;
+#pragma unroll
+        for (int e = 0; e < 16; ++e) o[e] = __int_as_float(v[e]);
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                     : "memory");
+    }
+}
+
+float launch_fp4_probe(int n_mma, int n_cols, int per_commit, int n_pairs, float* d_out, cudaStream_t st) {
+    const int smem = 2 * kABytes + 1024 + 256;
+    CUDA_CHECK(cudaFuncSetAttribute(fp4_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    cudaEvent_t e0, e1;
+    CUDA_CHECK(cudaEventCreate(&e0));
+    CUDA_CHECK(cudaEventCreate(&e1));
+    CUDA_CHECK(cudaEventRecord(e0, st));
+    fp4_probe_kernel<<<2 * n_pairs, 128, smem, st>>>(n_mma, n_cols, per_commit, d_out);
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaEventRecord(e1, st));
+    CUDA_CHECK(cudaEventSynchronize(e1));
+    float ms = 0;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return ms;
 }
 
 }  // namespace nldsc

@@ -96,6 +96,8 @@ struct BandArgs {
                                 // `tiles` (6 planes); null = the missing-free path is off
     const uint32_t* ready_rows; // fused launch (one band launch per shard): ring rows [0, *ready_rows) are unpacked and their
                                 // per-SNP statistics final; published after every chunk's unpack + stats.  null = everything is ready
+    int32_t fp4;                // the planes hold e2m1 nibbles (launch_unpack_fp4): the wide / missing-free bodies multiply them with
+                                // tcgen05.mma.kind::mxf4 (scale factors 1.0, K = 64 per MMA, k_steps = plane row bytes / 128)
     int32_t no_skip;            // A/B: score the out-of-window column groups too (NLDSC_NOSKIP=1)
     int32_t commit2;            // experiment: release the operand ring two stages at a time (16 MMAs between commits)
     int32_t probe;              // measurement hook: 0 = normal, 1 = MMAs without TMA loads, 2 = TMA loads without MMAs, 3 = epilogue only
@@ -126,6 +128,10 @@ void launch_stats(const int32_t* counts, int32_t row0, int32_t n_rows, int32_t n
 void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
                    int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
                    int32_t dst_row0, int32_t* counts, cudaStream_t st);   // counts != null: += genotype counts (zeroed by the caller)
+// the same planes as e2m1 (fp4) nibbles, two organisms per byte; npad = plane row BYTES (a multiple of 128 = 256 organisms)
+void launch_unpack_fp4(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
+                       int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
+                       int32_t dst_row0, int32_t* counts, cudaStream_t st);
 void launch_windows(const double* pos, int32_t n, double wind, int32_t* lo, int32_t* hi, cudaStream_t st,
                     int32_t n_pad = 0, unsigned long long* total = nullptr);   // rows n..n_pad-1 get the empty window (1, 0)
 void launch_copy16(const void* src, void* dst, size_t bytes, cudaStream_t st);   // SM copy, either side may be pinned host memory
@@ -147,6 +153,7 @@ void preload_unpack_kernels(); // per device: force the (lazily loaded) images o
 void preload_plan_kernels();
 void preload_finalize_kernels();
 void launch_i8_peak(int iters, int n_cols, int per_commit, int depth, int sm_count, cudaStream_t st);   // measurement only
+float launch_fp4_probe(int n_mma, int n_cols, int per_commit, int n_pairs, float* d_out, cudaStream_t st);   // feasibility probe, ms
 void launch_band_simt(const int8_t* planes, int64_t plane_stride, int32_t npad,
                       const BandArgs& args, cudaStream_t st);
 

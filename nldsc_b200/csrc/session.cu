@@ -583,7 +583,7 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     s->std_thr = p->std_thr;
     s->rsq_thr = p->rsq_thr;
     s->bps = (static_cast<int64_t>(p->n_org) + 3) / 4;
-    s->npad = static_cast<int32_t>(((static_cast<int64_t>(p->n_org) + kKAlign - 1) / kKAlign) * kKAlign);
+    s->npad = static_cast<int32_t>(((static_cast<int64_t>(p->n_org) + kKAlign - 1) / kKAlign) * kKAlign);    // int8 planes; fp4: below
     const char* band = getenv("NLDSC_BAND");
     s->use_simt = band && strcmp(band, "simt") == 0;
     // two j-blocks per supertile pay once the MMA time of a supertile outweighs the (then exposed) epilogue
@@ -595,6 +595,13 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     // missing-free chunks take the 2-plane kernel (a third of the MMAs); decided on the device, chunk by chunk
     const char* mf = getenv("NLDSC_MFREE");
     s->mfree = s->wide && !(mf && mf[0] == '0');
+    // fp4 planes (e2m1 nibbles, two organisms per byte) for the wide / missing-free bodies: tcgen05.mma.kind::mxf4 multiplies
+    // 64 organisms per instruction at twice the int8 rate from half the operand bytes and sums these 0 / 1 / 2 values exactly
+    // (counts stay below 2 N < 2^22).  The narrow kernel and the SIMT yardstick keep int8 planes (NLDSC_FP4=0: so does the wide one).
+    const char* f4 = getenv("NLDSC_FP4");
+    s->fp4 = s->wide && !(f4 && f4[0] == '0') && p->n_org <= 2000000;
+    if (s->fp4)      // plane row BYTES: a whole number of 128-byte pipeline stages = 256 organisms each
+        s->npad = static_cast<int32_t>(((static_cast<int64_t>(p->n_org) + 2 * kKAlign - 1) / (2 * kKAlign)) * kKAlign);
     s->load_begin = load_begin;
     s->load_end = load_end;
     s->n_load = load_end - load_begin;
@@ -904,7 +911,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         const char* fu = getenv("NLDSC_FUSED");
         const size_t part_bytes = static_cast<size_t>(tiles_bound) * 4 * kBlk * 28;
         s->fused_ok = s->wide && (fu && fu[0] == '1') && cap == n_load_pad && part_bytes <= (size_t(3) << 29) &&
-                      s->npad / kKAlign < 512;
+                      s->n_org < 65536;
     }
 
     // ---- chunks: greedy runs of i-blocks whose column span fits the ring
@@ -922,7 +929,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     // waves of them, and the per-launch ramp and tail dominate -- above all for the missing-free supertiles, which cover four
     // times the pairs each: 32,768 rows there (N = 2,504 missing-free: 0.72 vs 1.04 ms per 100,000 SNPs; with missing data 1.31
     // vs 1.33; at N = 10,000 the 6-plane path loses 1 % to 16,384-row chunks: profiles/r02k_ab_chunks_*.json).
-    const size_t base_rows = s->npad < 4096 ? 32768 : 8192;
+    const size_t base_rows = s->n_org < 4096 ? 32768 : 8192;
     const int32_t chunk_rows = static_cast<int32_t>(
         std::min<size_t>(env_size("NLDSC_CHUNK_ROWS", ramp ? std::min<size_t>(base_rows, byte_rows) : base_rows),
                          static_cast<size_t>(std::numeric_limits<int32_t>::max() / 2)));
@@ -1157,7 +1164,8 @@ static void unpack_rows(nldsc_ld_session* s, int32_t r0, int32_t r1, cudaStream_
         int32_t n = static_cast<int32_t>(std::min<int64_t>(r1 - r0, s->plane_rows - slot));
         if (r0 < s->n_load) {
             n = std::min(n, s->n_load - r0);
-            launch_unpack(s->d_packed, s->bps, r0, n, s->n_org, s->npad, s->d_planes, plane_stride, slot, s->d_counts, st);
+            (s->fp4 ? launch_unpack_fp4 : launch_unpack)(s->d_packed, s->bps, r0, n, s->n_org, s->npad, s->d_planes, plane_stride, slot,
+                                                         s->d_counts, st);
         } else {
             launch_zero_rows(s->d_planes, plane_stride, s->npad, slot, n, st);
         }
@@ -1188,7 +1196,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     // (N = 315,599: 46.7 ms side by side, 45.6 ms in turn; 10 cM band at N = 100,000: 65.9 vs 60.2 ms; at
     // N = 10,000 it is the other way round: 4.09 vs 4.62 ms), so there the two kernels take turns.
     const char* wo = getenv("NLDSC_WIDE_OVERLAP");
-    const bool turns = overlap && s->wide && (wo ? wo[0] == '0' : s->npad / kKAlign >= 512);
+    const bool turns = overlap && s->wide && (wo ? wo[0] == '0' : s->n_org >= 65536);
     const int32_t commit2 = env_size("NLDSC_COMMIT2", 0) != 0 ? 1 : 0;
     const char* bsn = getenv("NLDSC_BAND_STREAMS");
     // ONE band launch for the whole shard (plan permitting): the persistent kernel starts now and every CTA pair waits,
@@ -1214,6 +1222,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         a.part = part;
         a.dump = nullptr;
         a.commit2 = commit2;
+        a.fp4 = s->fp4 ? 1 : 0;
         a.no_skip = env_size("NLDSC_NOSKIP", 0) != 0 ? 1 : 0;
         return a;
     };
@@ -1682,7 +1691,7 @@ int nldsc_ld_calculate_packed(const uint8_t* packed, const nldsc_ld_params* para
                               size_t errlen) {
     return guarded(err, errlen, [&] {
         if (!packed) throw InvalidArgument("packed is null");
-        validate_params(params, /*allow_unused=*/true);
+        if (!params || params->n_snp <= 0 || params->n_org <= 0) validate_params(params, true);   // throws; the positions are checked once, in run_sharded
         const int64_t bps = (static_cast<int64_t>(params->n_org) + 3) / 4;
         run_sharded(params, out, [&](nldsc_ld_session* s) {
             session_upload_mem(s, packed + static_cast<size_t>(s->load_begin) * bps, nullptr);
@@ -1692,7 +1701,7 @@ int nldsc_ld_calculate_packed(const uint8_t* packed, const nldsc_ld_params* para
 
 int nldsc_ld_calculate(const nldsc_ld_params* params, nldsc_ld_result* out, char* err, size_t errlen) {
     return guarded(err, errlen, [&] {
-        validate_params(params, /*allow_unused=*/true);
+        if (!params || params->n_snp <= 0 || params->n_org <= 0 || !params->positions) validate_params(params, true);   // throws; full check in run_sharded
         if (!params->bedfile) throw InvalidArgument("bedfile is null");
         const int fd = open(params->bedfile, O_RDONLY);
         if (fd < 0) throw CudaError(std::string("cannot open ") + params->bedfile + ": " + strerror(errno));
@@ -1860,6 +1869,7 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* o) {
     o->npad = s->npad;
     o->band_impl = s->use_simt ? 0 : (s->wide ? 2 : 1);
     o->qtiles = s->total_qtiles;
+    o->fp4 = s->fp4 ? 1 : 0;
     if (s->ran && s->mfree && s->d_mfree_flags) {
         std::vector<uint32_t> fl(s->chunks.size());
         cudaSetDevice(s->device);
@@ -1947,6 +1957,33 @@ int nldsc_ld_debug_unpack(const uint8_t* packed, int32_t n_snp, int32_t n_org, i
         CUDA_CHECK(cudaMemcpy(d_packed, packed, static_cast<size_t>(n_snp) * bps, cudaMemcpyHostToDevice));
         CUDA_CHECK(cudaMemset(d_counts, 0, sizeof(int32_t) * 3 * static_cast<size_t>(n_snp)));
         launch_unpack(d_packed, bps, 0, n_snp, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, d_counts, nullptr);
+        CUDA_CHECK(cudaDeviceSynchronize());
+        if (counts_out)
+            CUDA_CHECK(cudaMemcpy(counts_out, d_counts, sizeof(int32_t) * 3 * n_snp, cudaMemcpyDeviceToHost));
+        if (planes_out) CUDA_CHECK(cudaMemcpy(planes_out, d_planes, plane_bytes * kPlanes, cudaMemcpyDeviceToHost));
+    });
+}
+
+int nldsc_ld_debug_unpack_fp4(const uint8_t* packed, int32_t n_snp, int32_t n_org, int8_t* planes_out, int32_t* counts_out,
+                          int32_t* npad_out, char* err, size_t errlen) {
+    return guarded(err, errlen, [&] {
+        if (!packed || n_snp <= 0 || n_org <= 0) throw InvalidArgument("bad arguments");
+        usable_devices();
+        CUDA_CHECK(cudaSetDevice(first_device_from_env()));
+        require_sm100(first_device_from_env());
+        const int64_t bps = (static_cast<int64_t>(n_org) + 3) / 4;
+        const int32_t npad = static_cast<int32_t>(((static_cast<int64_t>(n_org) + 2 * kKAlign - 1) / (2 * kKAlign)) * kKAlign);   // bytes
+        if (npad_out) *npad_out = npad;
+        if (!planes_out && !counts_out) return;
+        uint8_t* d_packed = dmalloc<uint8_t>(static_cast<size_t>(n_snp) * bps + 16);
+        int32_t* d_counts = dmalloc<int32_t>(static_cast<size_t>(n_snp) * 3);
+        const size_t plane_bytes = static_cast<size_t>(n_snp) * npad;
+        int8_t* d_planes = dmalloc<int8_t>(plane_bytes * kPlanes);
+        struct Free { void* a; void* b; void* c; ~Free() { cudaFree(a); cudaFree(b); cudaFree(c); } } fr{d_packed, d_counts, d_planes};
+        CUDA_CHECK(cudaMemset(d_packed + static_cast<size_t>(n_snp) * bps, 0, 16));
+        CUDA_CHECK(cudaMemcpy(d_packed, packed, static_cast<size_t>(n_snp) * bps, cudaMemcpyHostToDevice));
+        CUDA_CHECK(cudaMemset(d_counts, 0, sizeof(int32_t) * 3 * static_cast<size_t>(n_snp)));
+        launch_unpack_fp4(d_packed, bps, 0, n_snp, n_org, npad, d_planes, static_cast<int64_t>(plane_bytes), 0, d_counts, nullptr);
         CUDA_CHECK(cudaDeviceSynchronize());
         if (counts_out)
             CUDA_CHECK(cudaMemcpy(counts_out, d_counts, sizeof(int32_t) * 3 * n_snp, cudaMemcpyDeviceToHost));
@@ -2126,6 +2163,23 @@ int nldsc_ld_debug_band_probe(int32_t mode, int32_t n_org, int32_t n_tiles, int3
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
         *ms_out = ms / reps;
+    });
+}
+
+int nldsc_ld_debug_fp4_probe(int32_t n_mma, int32_t n_cols, int32_t per_commit, int32_t all_pairs, float* out, float* ms_out,
+                             char* err, size_t errlen) {
+    return guarded(err, errlen, [&] {
+        if (n_mma < 1 || n_cols < 16 || n_cols > 256 || (n_cols % 16) || per_commit < 1 || !out || !ms_out) throw InvalidArgument("bad arguments");
+        usable_devices();
+        const int dev = first_device_from_env();
+        CUDA_CHECK(cudaSetDevice(dev));
+        require_sm100(dev);
+        const int pairs = all_pairs ? device_sm_count(dev) / 2 : 1;
+        float* d = dmalloc<float>(static_cast<size_t>(pairs) * 2 * 128 * 16);
+        struct Free { void* p; ~Free() { cudaFree(p); } } fr{d};
+        launch_fp4_probe(n_mma, n_cols, per_commit, pairs, d, nullptr);                   // warm-up
+        *ms_out = launch_fp4_probe(n_mma, n_cols, per_commit, pairs, d, nullptr);
+        CUDA_CHECK(cudaMemcpy(out, d, sizeof(float) * 2 * 128 * 16, cudaMemcpyDeviceToHost));   // the first pair's rows
     });
 }
 

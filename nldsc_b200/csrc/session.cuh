@@ -93,7 +93,7 @@ struct nldsc_ld_session {
     int32_t load_begin = 0, load_end = 0;     // rows resident on the device, original indices
     int32_t n_load = 0, own_begin = 0, own_end = 0;   // shard-local
     int64_t bps = 0;
-    int32_t npad = 0;
+    int32_t npad = 0;                         // plane row bytes (int8 planes: = padded organisms; fp4 planes: half of them)
     double maf_thr = 0, std_thr = 0, rsq_thr = 0;
     bool use_simt = false;
     bool wide = false;                        // band_tc_wide_kernel: two j-blocks per supertile (the default; NLDSC_WIDE=0 = narrow kernel)
@@ -103,6 +103,7 @@ struct nldsc_ld_session {
     uint32_t* d_mfree_flags = nullptr;        // [chunks] 1 = the chunk is missing-free (launch_chunk_mfree_flag)
     std::vector<nldsc::QTile> h_qtiles;
     int64_t total_qtiles = 0;
+    bool fp4 = false;                         // planes hold e2m1 nibbles; npad = plane row BYTES = organisms / 2, padded to 128
     bool fused_ok = false;                    // the plan allows ONE band launch per shard (session_plan); run() decides
     uint32_t* d_ready = nullptr;              // fused launch: ring rows [0, *d_ready) are unpacked, their statistics final
     bool upload_started = false;

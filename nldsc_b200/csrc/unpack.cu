@@ -165,6 +165,94 @@ unpack_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t row0, int
     }
 }
 
+// ---- fp4 planes ---------------------------------------------------------------------------------------------
+// The same four planes with every genotype value stored as an e2m1 (fp4) nibble -- 0 -> 0x0, 1 -> 0x2, 2 -> 0x4 -- organism
+// 2i in the LOW nibble of byte i: the operand format of tcgen05.mma.kind::mxf4, which multiplies 64 organisms per instruction
+// at twice the int8 rate from half the bytes and (scale factors 1.0) sums these small integers exactly in FP32
+// (nldsc_ld_debug_fp4_probe).  A plane row is npad BYTES = 2 npad organisms.
+// four 2-bit codes per byte, 8 organisms (16 bits) -> eight 4-bit fields holding the code's low / high bit at bits 0 / 1
+__device__ __forceinline__ uint32_t spread_codes8(uint32_t v16) {
+    uint32_t t = v16 & 0xFFFFu;
+    t = (t | (t << 8)) & 0x00FF00FFu;
+    t = (t | (t << 4)) & 0x0F0F0F0Fu;
+    t = (t | (t << 2)) & 0x33333333u;
+    return t;
+}
+__device__ __forceinline__ void expand8_fp4(uint32_t v16, uint32_t& g, uint32_t& m, uint32_t& h, uint32_t& a) {
+    const uint32_t t = spread_codes8(v16);
+    const uint32_t lo = t & 0x11111111u, hi = (t >> 1) & 0x11111111u;
+    const uint32_t aa = hi & lo, hh = hi ^ aa, mm = lo ^ aa;     // 11 hom-second, 10 het, 01 missing: one bit per nibble (bit 0)
+    a = aa << 1;                   // 1.0 = 0b0010
+    h = hh << 1;
+    m = mm << 1;
+    g = (hh << 1) | (aa << 2);     // dosage: 1 -> 0b0010, 2 -> 0b0100
+}
+
+// grid.x = rows, grid.y * blockDim.x covers npad / 16 groups of 32 organisms (8 packed bytes in, 16 bytes per plane out)
+__global__ void __launch_bounds__(256)
+unpack_fp4_kernel(const uint8_t* __restrict__ packed, int64_t bps, int32_t row0, int32_t n_org,
+                  int32_t npad, int8_t* __restrict__ planes, int64_t plane_stride, int32_t dst_row0,
+                  int32_t* __restrict__ counts) {
+    const int t = blockIdx.y * blockDim.x + threadIdx.x;      // 32-organism group
+    const int64_t row = (int64_t)row0 + blockIdx.x;
+    const int64_t rb = (int64_t)t * 8;                         // row-relative first byte
+    uint32_t x0 = 0, x1 = 0;
+    if (rb < bps) {
+        const int64_t addr = row * bps + rb;
+        const uint32_t* __restrict__ words = reinterpret_cast<const uint32_t*>(packed);
+        const int64_t w = addr >> 2;
+        const int sh = (int)(addr & 3) * 8;
+        const int64_t left = bps - rb;                          // bytes of this row still ahead (>= 1)
+        const uint32_t w0 = __ldg(words + w);
+        const uint32_t w1 = __ldg(words + w + 1);               // the buffer carries 16 bytes of slack behind its last row
+        const uint32_t w2 = sh ? __ldg(words + w + 2) : 0u;
+        x0 = __funnelshift_r(w0, w1, sh);
+        x1 = __funnelshift_r(w1, w2, sh);
+        if (left < 8) {                                         // bytes past the row's end are the next row's: drop them
+            const unsigned long long keep = left >= 8 ? ~0ull : ((1ull << (8 * (int)left)) - 1ull);
+            x0 &= (uint32_t)keep;
+            x1 &= (uint32_t)(keep >> 32);
+        }
+        if (left <= 8) {                                        // holds the row's last byte: only its high n_org % 4 pairs are samples
+            const int s2 = 8 * (int)(left - 1);
+            const unsigned long long mask = ~(0xFFull << s2) | ((unsigned long long)tail_pair_mask(n_org) << s2);
+            x0 &= (uint32_t)mask;
+            x1 &= (uint32_t)(mask >> 32);
+        }
+    }
+    if (t * 16 < npad) {
+        uint4 g, m, h, a;
+        expand8_fp4(x0, g.x, m.x, h.x, a.x);
+        expand8_fp4(x0 >> 16, g.y, m.y, h.y, a.y);
+        expand8_fp4(x1, g.z, m.z, h.z, a.z);
+        expand8_fp4(x1 >> 16, g.w, m.w, h.w, a.w);
+        const int64_t off = ((int64_t)dst_row0 + blockIdx.x) * npad + (int64_t)t * 16;
+        st_plane(planes + kPlaneG * plane_stride + off, g);
+        st_plane(planes + kPlaneM * plane_stride + off, m);
+        st_plane(planes + kPlaneH * plane_stride + off, h);
+        st_plane(planes + kPlaneA * plane_stride + off, a);
+    }
+    if (counts != nullptr) {                                    // block-uniform
+        const uint32_t lo0 = x0 & 0x55555555u, hi0 = (x0 >> 1) & 0x55555555u;
+        const uint32_t lo1 = x1 & 0x55555555u, hi1 = (x1 >> 1) & 0x55555555u;
+        // three counts <= 32 each in one 64-bit register, 16 bits apart: het, hom-second, missing (a warp sums to <= 1,024 each)
+        unsigned long long c = (unsigned long long)(__popc(hi0 & ~lo0) + __popc(hi1 & ~lo1)) |
+                               ((unsigned long long)(__popc(hi0 & lo0) + __popc(hi1 & lo1)) << 16) |
+                               ((unsigned long long)(__popc(lo0 & ~hi0) + __popc(lo1 & ~hi1)) << 32);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
+        __shared__ unsigned long long part[8];
+        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = c;
+        __syncthreads();
+        if (threadIdx.x < 3) {
+            uint32_t tot = 0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) tot += (uint32_t)(part[w] >> (16 * threadIdx.x)) & 0xFFFFu;
+            if (tot) atomicAdd(counts + row * 3 + threadIdx.x, (int32_t)tot);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 zero_rows_kernel(int8_t* __restrict__ planes, int64_t plane_stride, int32_t npad, int32_t row0) {
     const int t = blockIdx.y * blockDim.x + threadIdx.x;
@@ -191,6 +279,16 @@ void launch_unpack(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_r
     const int groups = npad / 16;
     dim3 grid(n_rows, (groups + 255) / 256);
     unpack_kernel<<<grid, 256, 0, st>>>(packed, bps, row0, n_org, npad, planes, plane_stride, dst_row0, counts);
+    CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_unpack_fp4(const uint8_t* packed, int64_t bps, int32_t row0, int32_t n_rows,
+                       int32_t n_org, int32_t npad, int8_t* planes, int64_t plane_stride,
+                       int32_t dst_row0, int32_t* counts, cudaStream_t st) {
+    if (n_rows <= 0) return;
+    const int groups = npad / 16;
+    dim3 grid(n_rows, (groups + 255) / 256);
+    unpack_fp4_kernel<<<grid, 256, 0, st>>>(packed, bps, row0, n_org, npad, planes, plane_stride, dst_row0, counts);
     CUDA_CHECK(cudaGetLastError());
 }
 
@@ -221,6 +319,7 @@ void preload_unpack_kernels() {
     cudaFuncAttributes fa;
     CUDA_CHECK(cudaFuncGetAttributes(&fa, stats_kernel));
     CUDA_CHECK(cudaFuncGetAttributes(&fa, unpack_kernel));
+    CUDA_CHECK(cudaFuncGetAttributes(&fa, unpack_fp4_kernel));
     CUDA_CHECK(cudaFuncGetAttributes(&fa, zero_rows_kernel));
     CUDA_CHECK(cudaFuncGetAttributes(&fa, chunk_mfree_flag_kernel));
 }

@@ -28,7 +28,7 @@ for name in ("n1001_m300_miss", "n1003_m600_miss", "n1000_m768_nomiss"):
         if v.get("NLDSC_PLANE_BYTES") == "ring":             # a ring barely wider than one block pair's columns: rows wrap
             lo, hi = capi.plan_windows(g["positions"], g["ld_wind"])
             rows = ((int(np.max(hi - lo)) + 1) // 64 + 6) * 64
-            v["NLDSC_PLANE_BYTES"] = str(rows * 4 * ((g["n_org"] + 127) // 128 * 128))
+            v["NLDSC_PLANE_BYTES"] = str(rows * 4 * ((g["n_org"] + 255) // 256 * 128))   # fp4 planes: two organisms per byte
         os.environ.update(v)
         got = capi.calculate_packed(g["packed"], *a)
         assert_ld_close(got, want, label=f"{name} {v}")

@@ -33,7 +33,17 @@ VARIANTS = [
     {"NLDSC_FUSED": "1", "NLDSC_CHUNK_ROWS": "64"},
     {"NLDSC_MFREE": "0"},
     {"NLDSC_MFREE": "0", "NLDSC_CHUNK_ROWS": "128"},
+    {"NLDSC_FP4": "0"},
+    {"NLDSC_FP4": "0", "NLDSC_CHUNK_ROWS": "128", "NLDSC_PLANE_BYTES": "ring"},
+    {"NLDSC_FP4": "0", "NLDSC_MFREE": "0"},
 ]
+
+
+def _plane_row_bytes(n_org, variant):
+    """Bytes of one plane row: int8 planes (narrow kernel, SIMT yardstick, NLDSC_FP4=0) pad N to 128 organisms, one byte each;
+    fp4 planes pad to 256 organisms, two per byte."""
+    int8 = variant.get("NLDSC_FP4") == "0" or variant.get("NLDSC_WIDE") == "0" or variant.get("NLDSC_BAND") == "simt"
+    return (n_org + 127) // 128 * 128 if int8 else (n_org + 255) // 256 * 128
 
 
 def _shards_for_this_box(variant):
@@ -79,7 +89,7 @@ def test_random_case_matches_oracle(seed, monkeypatch):
         lo, hi = capi.plan_windows(cm, wind)
         span = int(np.max(hi - lo)) + 1
         rows = (span // 64 + 6) * 64                               # a block pair's columns, and little more
-        variant["NLDSC_PLANE_BYTES"] = str(rows * 4 * ((n_org + 127) // 128 * 128))
+        variant["NLDSC_PLANE_BYTES"] = str(rows * 4 * _plane_row_bytes(n_org, variant))
     variant = _shards_for_this_box(variant)
     for k, v in variant.items():
         monkeypatch.setenv(k, v)
@@ -102,6 +112,8 @@ MID_VARIANTS = [
     {"NLDSC_TEST_SHARDS": "4", "NLDSC_CHUNK_ROWS": "1024"},
     {"NLDSC_FUSED": "1", "NLDSC_CHUNK_ROWS": "1024"},
     {"NLDSC_MFREE": "0"},
+    {"NLDSC_FP4": "0"},
+    {"NLDSC_FP4": "0", "NLDSC_CHUNK_ROWS": "1024", "NLDSC_PLANE_BYTES": "ring"},
 ]
 
 
@@ -138,7 +150,7 @@ def test_midsize_case_variants_bitwise(seed, monkeypatch):
         if variant.get("NLDSC_PLANE_BYTES") == "ring":
             lo, hi = capi.plan_windows(cm, wind)
             rows_ring = ((int(np.max(hi - lo)) + 1) // 64 + 6) * 64 + 2048
-            variant["NLDSC_PLANE_BYTES"] = str(rows_ring * 4 * ((n_org + 127) // 128 * 128))
+            variant["NLDSC_PLANE_BYTES"] = str(rows_ring * 4 * _plane_row_bytes(n_org, variant))
         variant = _shards_for_this_box(variant)
         with monkeypatch.context() as mp:
             for k, v in variant.items():

@@ -74,6 +74,21 @@ def test_unpack_and_count_match_decoder(n_org):
     assert np.array_equal(m[:, :bps * 4], (lsb == 1) & valid)
 
 
+@pytest.mark.parametrize("n_org", [1, 3, 4, 31, 32, 33, 255, 256, 257, 1003, 4099])
+def test_fp4_unpack_equals_int8_unpack(n_org):
+    """The fp4 planes (e2m1 nibbles for tcgen05.mma.kind::mxf4) hold exactly the values of the int8 planes, organism for organism,
+    zero padding included, and the fused genotype counts agree."""
+    rng = np.random.default_rng(100 + n_org)
+    packed = rng.integers(0, 256, (41, (n_org + 3) // 4), dtype=np.uint8)
+    p8, c8 = capi.debug_unpack(packed, n_org)
+    p4, c4 = capi.debug_unpack_fp4(packed, n_org)
+    assert np.array_equal(c8, c4)
+    assert p4.min() >= 0                                   # only the nibbles 0x0, 0x2, 0x4 occur
+    k = min(p8.shape[2], p4.shape[2])
+    assert np.array_equal(p8[:, :, :k], p4[:, :, :k])
+    assert not p8[:, :, k:].any() and not p4[:, :, k:].any()
+
+
 def test_device_windows_equal_host_windows():
     """plan.cu windows_kernel vs the host sweep (tools.h:43-44 predicate), incl. ties, zero and huge windows."""
     rng = np.random.default_rng(3)
