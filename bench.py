@@ -468,16 +468,25 @@ def main():
         pk192 = capi.debug_i8_peak(192, 16, 50_000, reps=4)       # the band kernel's instruction shape
         pk192_8 = capi.debug_i8_peak(192, 8, 100_000, reps=4)     # same, a commit every 8 MMAs (as the wide kernel issues them)
         pk256 = capi.debug_i8_peak(256, 8, 75_000, reps=4)
+        # the pipe the band kernel actually runs on when the planes are fp4: tcgen05.mma.kind::mxf4, unit scale factors
+        fp4_192 = capi.debug_fp4_probe(400_000, 192, 16, all_pairs=True)
+        fp4_256 = capi.debug_fp4_probe(400_000, 256, 8, all_pairs=True)
     peak_clk = pclk.summary()
 
     # ---- roofline of the dominant kernel (banded int8 GEMM + epilogue) -------------------------
     peaks = _peaks()
     ops = pairs_rank * 12.0 * N_ORG               # 12*N int8 ops per ordered pair with missing data
     band_s = st["ms_band"] * 1e-3
-    peak = max(pk192["tops"], pk256["tops"])      # the pipe's ceiling, whichever shape shows it
+    peak_int8 = max(pk192["tops"], pk256["tops"])      # the int8 pipe's ceiling, whichever shape shows it
+    peak_fp4 = max(fp4_192["tops_equiv"], fp4_256["tops_equiv"])
+    fp4 = bool(st["fp4"])
+    # the roofline of the kernel is the pipe it runs on: fp4 (mxf4) when the planes are e2m1 nibbles, int8 otherwise; the
+    # fraction of the INT8 peak -- north_star's yardstick -- is printed beside it in either case
+    peak = peak_fp4 if fp4 else peak_int8
     peak_2x_bf16 = 2.0 * (peaks["bf16_tflops"] if peaks else 1590.0)
     achieved = ops / band_s / 1e12 if band_s > 0 else 0.0
-    executed = (st["tiles"] * 2.0 * 256 * 192 * st["npad"] / band_s / 1e12) if band_s > 0 else 0.0
+    k_org = st["npad"] * (2 if fp4 else 1)             # padded organisms of a plane row (fp4 planes: two per byte)
+    executed = (st["tiles"] * 2.0 * 256 * 192 * k_org / band_s / 1e12) if band_s > 0 else 0.0
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "band_traffic.json")
     if os.path.exists(tpath):
@@ -487,9 +496,14 @@ def main():
             traffic = None
     roofline = {"bound": "tensor", "kernel": {0: "band_simt_kernel", 1: "band_tc_kernel", 2: "band_tc_wide_kernel"}[st["band_impl"]],
                 "achieved": achieved, "peak": peak, "unit": "TOP/s", "frac": achieved / peak, "traffic": traffic,
-                "peak_source": "measured in this run: back-to-back tcgen05.mma.cta_group::2.kind::i8 (M=256, K=32) from shared memory on "
-                               "all 74 CTA pairs, no loads, no epilogue (nldsc_ld_debug_i8_peak); the larger of N=192 with 16 MMAs per commit "
-                               "and N=256 with 8; MEASURED_PEAKS.json has no int8 entry",
+                "peak_source": ("measured in this run: back-to-back tcgen05.mma.cta_group::2." +
+                                ("kind::mxf4 (e2m1 operands holding 0/1/2, scale factors 1.0, exact integer sums; M=256, K=64)" if fp4
+                                 else "kind::i8 (M=256, K=32)") +
+                                " from shared memory on all 74 CTA pairs, no loads, no epilogue; the larger of N=192 with 16 MMAs per "
+                                "commit and N=256 with 8; ops counted as int8-equivalent multiply-adds x 2 (12*N per ordered pair); "
+                                "MEASURED_PEAKS.json has no int8 / fp4 entry"),
+                "pipe": "fp4 (tcgen05.mma.kind::mxf4.block_scale, unit scales)" if fp4 else "int8 (tcgen05.mma.kind::i8)",
+                "peak_int8": peak_int8, "frac_of_int8_peak": achieved / peak_int8, "peak_fp4": peak_fp4,
                 "peak_sm_mhz": peak_clk["sm_mhz"], "peak_n192_16_per_commit": pk192["tops"], "peak_n192_8_per_commit": pk192_8["tops"],
                 "peak_n256": pk256["tops"],
                 "peak_2x_bf16": peak_2x_bf16, "frac_of_2x_bf16": achieved / peak_2x_bf16,
@@ -588,7 +602,8 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warmup,
             "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "int8 cross-counts (int32 accumulate) + f64 epilogue", "data": "synthetic",
+            "dtype": ("exact integer cross-counts on the fp4 tensor pipe (e2m1 operands 0/1/2, unit scales, f32 accumulate) + f64 epilogue"
+                      if st["fp4"] else "int8 cross-counts (int32 accumulate) + f64 epilogue"), "data": "synthetic",
             "config": {"workload": WORKLOAD, "pairs_per_step_per_gpu": pairs_rank, "parallelism": f"shard{world}",
                        "l2": "inputs larger than L2 (250 MB packed + 4 GB unpacked planes per step vs 126 MB)"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
