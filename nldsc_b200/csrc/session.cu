@@ -1196,7 +1196,10 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
     // (N = 315,599: 46.7 ms side by side, 45.6 ms in turn; 10 cM band at N = 100,000: 65.9 vs 60.2 ms; at
     // N = 10,000 it is the other way round: 4.09 vs 4.62 ms), so there the two kernels take turns.
     const char* wo = getenv("NLDSC_WIDE_OVERLAP");
-    const bool turns = overlap && s->wide && (wo ? wo[0] == '0' : s->n_org >= 65536);
+    // On the fp4 pipe the band kernel moves half the operand bytes and the balance tips: side by side wins 13 % at N = 315,599
+    // with a 1 cM window (11.6 vs 13.4 ms per 20,000 SNPs) and loses 2 % on the 10 cM band at N = 100,000
+    // (profiles/r02s_ab_knobs_*.json), so the kernels take turns only with int8 planes.
+    const bool turns = overlap && s->wide && (wo ? wo[0] == '0' : (!s->fp4 && s->n_org >= 65536));
     const int32_t commit2 = env_size("NLDSC_COMMIT2", 0) != 0 ? 1 : 0;
     const char* bsn = getenv("NLDSC_BAND_STREAMS");
     // ONE band launch for the whole shard (plan permitting): the persistent kernel starts now and every CTA pair waits,
