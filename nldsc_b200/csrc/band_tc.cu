@@ -4,7 +4,9 @@
 //   band_tc_kernel        narrow: 2 i-blocks x 1 j-block, accumulator double-buffered        (NLDSC_WIDE=0; second implementation)
 //   band_wide_body        wide:   2 i-blocks x 2 j-blocks, 6 cross-counts per pair            (the default)
 //   band_mfree_body       4 i-blocks x 2 j-blocks, 2 cross-counts per pair, for chunks without a missing genotype
-// The last two share the launch band_tc_wide_kernel; a per-chunk flag written on the device picks the body.
+// The last two share the launch band_tc_wide_kernel; a per-chunk flag written on the device picks the body.  Both run on either
+// operand format: int8 planes with tcgen05.mma.kind::i8, or (default, BandArgs::fp4) e2m1 planes with kind::mxf4 and unit scale
+// factors -- twice the rate, the same exact integer counts.
 //
 // Replaces the pair loop of calculate() (reference ldscalc.h:34-47) and the two
 // arma::dot calls per ordered pair in Math::r2_adjusted (tools.h:87-92).
