@@ -463,8 +463,8 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kWStages * kWStageBytes);   // leader CTA only
     uint64_t* empty = full + kWStages;         // one per CTA
     uint64_t* tfull = empty + kWStages;        // one per CTA
-    uint64_t* tempty = tfull + 1;              // leader CTA only
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
+    uint64_t* tempty = tfull + 1;              // leader CTA only: one per accumulator
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
     // the j-SNPs' constants of the supertile being scored: staged by the epilogue warps while they wait for its MMAs
     double2* col_coef = reinterpret_cast<double2*>(smem + kWStages * kWStageBytes + 256);
     uint8_t* col_flags = reinterpret_cast<uint8_t*>(col_coef) + kWCols * sizeof(SnpCoef);
@@ -478,7 +478,8 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b)) : "memory");
         for (int s = 0; s < kWStages; ++s) { mbar_init(&full[s], args.probe == 1 ? 2 : 1); mbar_init(&empty[s], 1); }
         mbar_init(tfull, 1);
-        mbar_init(tempty, 16);                 // 8 epilogue warps x 2 CTAs
+        mbar_init(&tempty[0], 16);             // 8 epilogue warps x 2 CTAs, per accumulator
+        mbar_init(&tempty[1], 16);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -542,37 +543,70 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
             int stage = 0;
             uint32_t phase = 0;
             int n = 0;
-            for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
-                const bool two = args.tiles[t].b_row2 >= 0;
-                mbar_wait(tempty, (n & 1) ^ 1, 6);                    // both CTAs' epilogues drained the accumulators
-                tc_fence_after();
-                for (int k = 0; k < args.k_steps; ++k) {
-                    mbar_wait(&full[stage], phase, 7);
-                    tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * kWStageBytes);
-                    const uint64_t a_desc = make_smem_desc(sa);
-                    const uint64_t b_desc = make_smem_desc(sa + kABytes);
-                    const uint64_t b2_desc = make_smem_desc(sa + kABytes + kBBytes);
-                    if (args.fp4) {            // 128 operand bytes per row = 256 organisms per stage, 64 per MMA
-                        const uint32_t sf = tmem_base + kSfCols;
+            // the MMAs of one stage into accumulator 0 (j-block 0) and / or accumulator 1 (j-block 1)
+            auto issue = [&](int st, int k, bool acc0, bool acc1) {
+                const uint32_t sa = smem_u32(smem + st * kWStageBytes);
+                const uint64_t a_desc = make_smem_desc(sa);
+                const uint64_t b_desc = make_smem_desc(sa + kABytes);
+                const uint64_t b2_desc = make_smem_desc(sa + kABytes + kBBytes);
+                if (args.fp4) {            // 128 operand bytes per row = 256 organisms per stage, 64 per MMA
+                    const uint32_t sf = tmem_base + kSfCols;
+                    if (acc0) {
 #pragma unroll
                         for (int kk = 0; kk < kKStep / 32; ++kk)
                             tc_mma_mxf4(tmem_base, a_desc + 2 * kk, b_desc + 2 * kk, idesc_mxf4(kBRows), sf, sf + 16, (k | kk) != 0);
-                        if (two) {
+                    }
+                    if (acc1) {
 #pragma unroll
-                            for (int kk = 0; kk < kKStep / 32; ++kk)
-                                tc_mma_mxf4(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, idesc_mxf4(kBRows), sf, sf + 16, (k | kk) != 0);
-                        }
-                    } else {
+                        for (int kk = 0; kk < kKStep / 32; ++kk)
+                            tc_mma_mxf4(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, idesc_mxf4(kBRows), sf, sf + 16, (k | kk) != 0);
+                    }
+                } else {
+                    if (acc0) {
 #pragma unroll
                         for (int kk = 0; kk < kKStep / 32; ++kk)
                             tc_mma_i8(tmem_base, a_desc + 2 * kk, b_desc + 2 * kk, kIdesc, (k | kk) != 0);
-                        if (two) {
-#pragma unroll
-                            for (int kk = 0; kk < kKStep / 32; ++kk)
-                                tc_mma_i8(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, kIdesc, (k | kk) != 0);
-                        }
                     }
+                    if (acc1) {
+#pragma unroll
+                        for (int kk = 0; kk < kKStep / 32; ++kk)
+                            tc_mma_i8(tmem_base + kBRows, a_desc + 2 * kk, b2_desc + 2 * kk, kIdesc, (k | kk) != 0);
+                    }
+                }
+            };
+            for (int t = pair; t < args.n_tiles; t += n_pairs, ++n) {
+                const bool two = args.tiles[t].b_row2 >= 0;
+                mbar_wait(&tempty[0], (n & 1) ^ 1, 6);               // both CTAs' epilogues drained accumulator 0
+                tc_fence_after();
+                int k = 0;
+                if (two && args.runahead) {
+                    // The epilogue of the previous supertile is still reading accumulator 1 (it is exposed: both accumulators
+                    // belong to one supertile).  Run ahead into accumulator 0: the stages the producer has already filled are
+                    // multiplied with j-block 0 now, and with j-block 1 -- and released -- once accumulator 1 is free.
+                    const int ahead = args.k_steps < kWStages - 1 ? args.k_steps : kWStages - 1;
+                    int st = stage;
+                    uint32_t ph = phase;
+                    for (int kk = 0; kk < ahead; ++kk) {
+                        mbar_wait(&full[st], ph, 7);
+                        tc_fence_after();
+                        issue(st, kk, true, false);
+                        if (++st == kWStages) { st = 0; ph ^= 1; }
+                    }
+                    mbar_wait(&tempty[1], (n & 1) ^ 1, 6);
+                    tc_fence_after();
+                    for (; k < ahead; ++k) {
+                        issue(stage, k, false, true);
+                        tc_commit_pair(&empty[stage]);
+                        if (++stage == kWStages) { stage = 0; phase ^= 1; }
+                    }
+                } else {
+                    mbar_wait(&tempty[1], (n & 1) ^ 1, 6);
+                    tc_fence_after();
+                }
+                for (; k < args.k_steps; ++k) {
+                    mbar_wait(&full[stage], phase, 7);
+                    tc_fence_after();
+                    issue(stage, k, true, two);
                     if (!args.commit2) {
                         tc_commit_pair(&empty[stage]);
                     } else if ((k & 1) || k == args.k_steps - 1) {
@@ -664,11 +698,14 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
 #endif
                     }
                 }
-                if (jj == n_j - 1) {
-                    // this warp is done with both accumulators: tell the leader's MMA warp
+                {
+                    // this warp is done with accumulator jj (a one-j-block supertile never wrote the other): tell the leader's MMA warp
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive_leader(tempty);
+                    if (lane == 0) {
+                        mbar_arrive_leader(&tempty[jj]);
+                        if (n_j == 1) mbar_arrive_leader(&tempty[1]);
+                    }
                 }
                 acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
                 acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);

@@ -98,6 +98,7 @@ struct BandArgs {
                                 // per-SNP statistics final; published after every chunk's unpack + stats.  null = everything is ready
     int32_t fp4;                // the planes hold e2m1 nibbles (launch_unpack_fp4): the wide / missing-free bodies multiply them with
                                 // tcgen05.mma.kind::mxf4 (scale factors 1.0, K = 64 per MMA, k_steps = plane row bytes / 128)
+    int32_t runahead;           // wide body: start the next supertile's j-block-0 MMAs while the epilogue still reads accumulator 1
     int32_t no_skip;            // A/B: score the out-of-window column groups too (NLDSC_NOSKIP=1)
     int32_t commit2;            // experiment: release the operand ring two stages at a time (16 MMAs between commits)
     int32_t probe;              // measurement hook: 0 = normal, 1 = MMAs without TMA loads, 2 = TMA loads without MMAs, 3 = epilogue only

@@ -1226,6 +1226,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         a.dump = nullptr;
         a.commit2 = commit2;
         a.fp4 = s->fp4 ? 1 : 0;
+        { const char* ra = getenv("NLDSC_RUNAHEAD"); a.runahead = (ra && ra[0] == '0') ? 0 : 1; }
         a.no_skip = env_size("NLDSC_NOSKIP", 0) != 0 ? 1 : 0;
         return a;
     };
