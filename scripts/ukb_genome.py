@@ -39,6 +39,9 @@ CHROMS = list(range(1, 23))
 SIZES = {c: max(1024, int(total_snps * CM_LEN[c - 1] / sum(CM_LEN)) // 64 * 64) for c in CHROMS}
 BPS = (N + 3) // 4
 ORACLE_ROWS = {c: (2 if c <= 2 else 1) for c in CHROMS}          # 24 slices
+if os.environ.get("NLDSC_UKB_ORACLE_CHROMS"):                    # a re-run that checks fewer slices: only these chromosomes
+    _only = {int(x) for x in os.environ["NLDSC_UKB_ORACLE_CHROMS"].split(",")}
+    ORACLE_ROWS = {c: (1 if c in _only else 0) for c in CHROMS}
 
 
 def mem_available() -> int:
