@@ -354,6 +354,8 @@ def strong_leg(n_gpus: int):
     a = (n_snp, n_org, cm, wind, MAF, STD_THR, 1.0 / n_snp)
     os.environ["NLDSC_DEVICE"] = "0"
 
+    capi.report_device_times(True)            # per-shard device times in the record (0.2 ms of calls that take 0.2-2 s)
+
     def timed(gpus):
         os.environ["NLDSC_GPUS"] = str(gpus)
         out = capi.alloc_result(n_snp)
@@ -540,6 +542,9 @@ def main():
         capi.calculate_packed(host, N_SNP, N_ORG, cm, WIND_CM, MAF, STD_THR, rsq_thr, out=out)
     barrier()
     e2e_wall = max_over_ranks(time.perf_counter() - t0)
+    capi.report_device_times(True)            # one more call, untimed, for the device-side breakdown of the call
+    capi.calculate_packed(host, N_SNP, N_ORG, cm, WIND_CM, MAF, STD_THR, rsq_thr, out=out)
+    capi.report_device_times(False)
     rep = capi.last_call_report()[0]
     e2e = {"value": pairs_total * args.steps / e2e_wall, "unit": UNIT, "ms_per_step": 1e3 * e2e_wall / args.steps,
            "h2d_bytes_per_step": int(N_SNP * bps + 8 * N_SNP + 32 * st["tiles"]),

@@ -144,8 +144,8 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* out);
 void nldsc_ld_session_destroy(nldsc_ld_session* s);
 
 /* What the last nldsc_ld_calculate* call made on the CALLING THREAD did, one record per shard (= per GPU, or per
- * NLDSC_TEST_SHARDS shard): host wall time of every phase and the CUDA-event times of the device work.  Written
- * whether or not NLDSC_TRACE is set; the records are what the genome driver and bench.py report as per-GPU busy time. */
+ * NLDSC_TEST_SHARDS shard): host wall time of every phase and, on request, the CUDA-event times of the device work;
+ * the records are what the genome driver and bench.py report as per-GPU busy time. */
 typedef struct nldsc_ld_shard_report {
     int32_t device;
     int32_t row_begin, row_end;      /* owned rows */
@@ -158,6 +158,9 @@ typedef struct nldsc_ld_shard_report {
     float ms_dev_upload;             /* first to last byte of the H2D copy (host-buffer uploads; 0 for the .bed readers) */
     float ms_dev_run, ms_dev_band, ms_dev_unpack;   /* run() on the device; its band / unpack kernel families */
 } nldsc_ld_shard_report;
+/* The ms_dev_* fields cost a hundred CUDA-event queries per shard (0.15-0.2 ms), so they are filled only after
+ * nldsc_ld_report_device_times(1) (process-wide; default off) or under NLDSC_TRACE; the host phase times always are. */
+int nldsc_ld_report_device_times(int32_t on);
 /* n = number of shards of that call; the first min(n, max) records are written to `out` (may be NULL). */
 int nldsc_ld_last_call_report(nldsc_ld_shard_report* out, int32_t max, int32_t* n);
 /* Releases the device memory cached between calls (the per-device workspace arena: packed rows, plane ring, ...)

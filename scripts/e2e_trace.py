@@ -17,6 +17,7 @@ ts = []
 for _ in range(20):
     t = time.perf_counter(); capi.calculate_packed(host, *a, out=out); ts.append(time.perf_counter() - t)
 print("e2e ms median %.3f min %.3f" % (1e3 * float(np.median(ts)), 1e3 * min(ts)))
+capi.report_device_times(True); capi.calculate_packed(host, *a, out=out); capi.report_device_times(False)
 print(capi.last_call_report()[0])
 os.environ["NLDSC_TRACE"] = "1"
 capi.calculate_packed(host, *a, out=out)

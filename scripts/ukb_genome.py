@@ -74,6 +74,7 @@ print(f"[ukb] {gpus} GPUs, {sum(SIZES.values())} SNPs, {total_bytes / 1e9:.1f} G
       f"{avail / 1e9:.0f} GB -> mode {mode}, {n_threads} GPU threads", file=sys.stderr)
 
 capi.warmup(0, n_threads)
+capi.report_device_times(True)
 order = sorted(CHROMS, key=lambda c: -SIZES[c])
 lock = threading.Lock()
 oracle_gate = threading.Semaphore(6)
