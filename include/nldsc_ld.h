@@ -131,7 +131,7 @@ int nldsc_ld_session_create(nldsc_ld_session** out, int device, const nldsc_ld_p
  * on `stream` (a cudaStream_t, or NULL for the session's own stream). */
 int nldsc_ld_session_upload(nldsc_ld_session* s, const uint8_t* packed_rows, void* stream,
                             char* err, size_t errlen);
-/* Unpack (+ genotype counts) -> per-SNP stats -> banded int8 GEMM + FP64 epilogue -> finalize,
+/* Unpack (+ genotype counts) -> per-SNP stats -> banded cross-count GEMM (tcgen05; fp4 or int8 operands) + FP64 epilogue -> finalize,
  * all asynchronous on `stream`.  Inputs must be resident (upload done). */
 int nldsc_ld_session_run(nldsc_ld_session* s, void* stream, char* err, size_t errlen);
 /* Device -> host copy of the owned rows' seven arrays (length row_end-row_begin),
