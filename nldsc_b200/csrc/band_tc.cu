@@ -34,7 +34,12 @@
 
 #include <cuda.h>
 #include <mutex>
+#include <type_traits>
 #include <string>
+
+#ifndef NLDSC_FP4_F2F
+#define NLDSC_FP4_F2F 1      // fp4 accumulators -> double by one F2F each (0: float -> int -> double, the A/B build)
+#endif
 
 namespace nldsc {
 
@@ -676,7 +681,11 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
                     tmem_ld16(taddr + col + 32, vh);
                     tmem_ld16(taddr + col + 64, va);
                     tmem_ld_wait();
+#if !NLDSC_FP4_F2F
                     if (args.fp4) { acc_to_int(vm); acc_to_int(vh); acc_to_int(va); }    // FP32 accumulators holding exact counts
+#endif
+                    auto score8 = [&](auto f32) {
+                    constexpr bool kF32 = decltype(f32)::value;
 #pragma unroll
                     for (int u = 0; u < 8; ++u) {
                         const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
@@ -689,14 +698,17 @@ __device__ __forceinline__ void band_wide_body(const CUtensorMap& map_a, const C
                         const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
                         const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
                         const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
-#ifndef NLDSC_NO_COL_STAGE
                         const double2* cj = col_coef + 4 * (kBlk * jj + jl);
-                        pair_eval_core(args, row, j0 + jl, col_flags[kBlk * jj + jl], cj[0], cj[1], cj[2], cj[3],
-                                       Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
-#else       // A/B build: the constants pair by pair from global memory, as the narrow kernel does
-                        pair_eval(args, row, j0 + jl, Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
-#endif
+                        pair_eval_core<kF32>(args, row, j0 + jl, col_flags[kBlk * jj + jl], cj[0], cj[1], cj[2], cj[3],
+                                             Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
                     }
+                    };
+#if NLDSC_FP4_F2F
+                    // fp4: the shuffled values are FP32 bit patterns, converted to double pair by pair (cnt2d)
+                    if (args.fp4) score8(std::true_type{}); else score8(std::false_type{});
+#else
+                    score8(std::false_type{});
+#endif
                 }
                 {
                     // this warp is done with accumulator jj (a one-j-block supertile never wrote the other): tell the leader's MMA warp
@@ -902,14 +914,24 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
                     tmem_ld16(taddr + 16 * c, vh);
                     tmem_ld16(taddr + kBlk + 16 * c, va);
                     tmem_ld_wait();
+#if !NLDSC_FP4_F2F
                     if (args.fp4) { acc_to_int(vh); acc_to_int(va); }
+#endif
+                    auto score16 = [&](auto f32) {
+                        constexpr bool kF32 = decltype(f32)::value;
 #pragma unroll
-                    for (int u = 0; u < 16; ++u) {
-                        const int jl = 16 * c + u;
-                        const double2* cj = col_coef + 4 * (kBlk * jj + jl);
-                        pair_eval_mfree(args, row, jbase + jl, col_flags[kBlk * jj + jl], cj[0], cj[1], cj[2], cj[3], vh[u], va[u],
-                                        (u & 1) ? od : ev);
-                    }
+                        for (int u = 0; u < 16; ++u) {
+                            const int jl = 16 * c + u;
+                            const double2* cj = col_coef + 4 * (kBlk * jj + jl);
+                            pair_eval_mfree<kF32>(args, row, jbase + jl, col_flags[kBlk * jj + jl], cj[0], cj[1], cj[2], cj[3], vh[u], va[u],
+                                                  (u & 1) ? od : ev);
+                        }
+                    };
+#if NLDSC_FP4_F2F
+                    if (args.fp4) score16(std::true_type{}); else score16(std::false_type{});
+#else
+                    score16(std::false_type{});
+#endif
                 }
                 if (half == 1) {
                     // accumulator fully read: hand it back to the leader's MMA warp

@@ -66,12 +66,22 @@ __device__ __forceinline__ double i2d(int32_t x) {
     return __hiloint2double(0x43300000, x ^ static_cast<int32_t>(0x80000000u)) - 4503601774854144.0;
 }
 
+// A cross-count as a double.  kF32 = false: an int32 (int8 GEMM).  kF32 = true: the bit pattern of an FP32 accumulator of the fp4
+// GEMM holding an exact integer -- ONE conversion instruction on the otherwise idle XU pipe instead of the five ALU / FP64
+// instructions of float -> int -> double; the epilogue is bound by instruction issue (profiles/r02u_band_tc_ncu.txt).
+template <bool kF32>
+__device__ __forceinline__ double cnt2d(int32_t x) {
+    if constexpr (kF32) return static_cast<double>(__int_as_float(x));
+    else return i2d(x);
+}
+
 // One ordered pair (i, j): the six cross-counts are exact integers from the int8 GEMM.
 // Branch-free: every pair is evaluated and its terms are SELECTED in or out, so the compiler can interleave the
 // FP64 chains of the unrolled j loop (with early returns each pair cost ~1,000 cycles of exposed latency).
 // A rejected pair may compute inf / NaN (a dropped SNP has 1/sd = 0 or inf); selects never propagate them.
 // `fj` / `c0..c3` are SNP j's flags and its 64-byte SnpCoef as four double2 (from global memory, or from the copy
 // the wide kernel stages in shared memory while its epilogue warps wait for the MMAs).
+template <bool kF32 = false>
 __device__ __forceinline__ void pair_eval_core(const BandArgs& a, const RowCtx& r, int32_t gj, uint8_t fj, const double2 c0,
                                                const double2 c1, const double2 c2, const double2 c3,
                                                int32_t Ggm, int32_t Ggh, int32_t Gga,
@@ -83,9 +93,11 @@ __device__ __forceinline__ void pair_eval_core(const BandArgs& a, const RowCtx& 
     const double mu_j = c0.x, xbar_j = c0.y, inv_sd_j = c1.x, ch = c1.y;
     const double ca = c2.x, cm = c2.y, rbar_j = c3.x, inv_rsd_j = c3.y;
 
-    const double dGgm = i2d(Ggm), dGgh = i2d(Ggh), dGga = i2d(Gga), dGmm = i2d(Gmm), dGmh = i2d(Gmh), dGma = i2d(Gma);
-    const double dGgg = i2d(Ggh + 2 * Gga);
-    const double dGmg = i2d(Gmh + 2 * Gma);
+    const double dGgm = cnt2d<kF32>(Ggm), dGgh = cnt2d<kF32>(Ggh), dGga = cnt2d<kF32>(Gga);
+    const double dGmm = cnt2d<kF32>(Gmm), dGmh = cnt2d<kF32>(Gmh), dGma = cnt2d<kF32>(Gma);
+    // G_gg = G_gh + 2 G_ga, G_mg = G_mh + 2 G_ma: exact either way (integers far below 2^53)
+    const double dGgg = kF32 ? __fma_rn(2.0, dGga, dGgh) : i2d(Ggh + 2 * Gga);
+    const double dGmg = kF32 ? __fma_rn(2.0, dGma, dGmh) : i2d(Gmh + 2 * Gma);
 
     // Every multiply-add below is contracted EXPLICITLY: pair_eval_mfree evaluates the same expressions with the four
     // missing-genotype counts and G_gm identically zero, and must give the same bits (fma(x, 0, y) == y).
@@ -109,6 +121,7 @@ __device__ __forceinline__ void pair_eval_core(const BandArgs& a, const RowCtx& 
 
 // The same pair when neither SNP block holds a missing genotype: G_gm = G_mm = G_mh = G_ma = 0 exactly, so only
 // G_gh and G_ga arrive (band_mfree_body).  Bitwise equal to pair_eval_core on those counts.
+template <bool kF32 = false>
 __device__ __forceinline__ void pair_eval_mfree(const BandArgs& a, const RowCtx& r, int32_t gj, uint8_t fj, const double2 c0,
                                                 const double2 c1, const double2 c2, const double2 c3,
                                                 int32_t Ggh, int32_t Gga, RowAcc& acc) {
@@ -116,7 +129,8 @@ __device__ __forceinline__ void pair_eval_mfree(const BandArgs& a, const RowCtx&
     const bool use = in_win && (fj & kFlagKeep);
     const bool use_d = use && (fj & kFlagDom);
     const double xbar_j = c0.y, inv_sd_j = c1.x, ch = c1.y, ca = c2.x, rbar_j = c3.x, inv_rsd_j = c3.y;
-    const double dGgh = i2d(Ggh), dGga = i2d(Gga), dGgg = i2d(Ggh + 2 * Gga);
+    const double dGgh = cnt2d<kF32>(Ggh), dGga = cnt2d<kF32>(Gga);
+    const double dGgg = kF32 ? __fma_rn(2.0, dGga, dGgh) : i2d(Ggh + 2 * Gga);
     const double sa = __fma_rn(-r.nxbar, xbar_j, dGgg);
     const double ra = sa * r.w * inv_sd_j;
     const double adj_a = r2adj(ra, a.adj_c);
@@ -139,7 +153,7 @@ __device__ __forceinline__ void pair_eval(const BandArgs& a, const RowCtx& r, in
     const int32_t gjc = in_win ? gj : 0;                        // a valid index: the loads below are unconditional
     const uint8_t fj = __ldg(a.flags + gjc);
     const double2* cp = reinterpret_cast<const double2*>(a.coef + gjc);
-    pair_eval_core(a, r, gj, fj, __ldg(cp), __ldg(cp + 1), __ldg(cp + 2), __ldg(cp + 3), Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
+    pair_eval_core<false>(a, r, gj, fj, __ldg(cp), __ldg(cp + 1), __ldg(cp + 2), __ldg(cp + 3), Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
 }
 
 }  // namespace nldsc
