@@ -963,7 +963,10 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
 // ONE launch per chunk for both paths: the chunk's flag (written on the device after its stats) picks the body.
 // (Two kernels, one of them returning at once, cost configs[1] 12 %: the idle launch still has to wait for a whole
 // grid's worth of free SMs behind the other stream's persistent band kernel -- profiles/r02i_ab_missing_n10000.json.)
-__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
+#ifndef NLDSC_WIDE_MAXNREG
+#define NLDSC_WIDE_MAXNREG 128   // 144 / 160 measured slower (r02y): the unpack blocks no longer fit on the SM beside this kernel
+#endif
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(NLDSC_WIDE_MAXNREG)
 band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                     const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ha, const BandArgs args) {
     // every thread of the grid reads the same word, written before this launch could start
