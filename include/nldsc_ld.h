@@ -167,6 +167,27 @@ int nldsc_ld_last_call_report(nldsc_ld_shard_report* out, int32_t max, int32_t* 
  * on `device`, or on every device when device < 0.  Blocks in use by a running call are left alone. */
 int nldsc_ld_arena_trim(int32_t device);
 
+/* ---- allocation-free entry point --------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Per-SNP statistics of `n_snp` packed .bed rows ((n_org + 3) / 4 bytes each, no slack needed) that are already in DEVICE
+ * memory on `device`: d_maf_out[n_snp] and d_rstd_out[n_snp] receive exactly what nldsc_ld_calculate* return as `maf` and
+ * `residuals_std` for the same rows and thresholds (every position used), d_counts_out (int32 [n_snp][3] = n_het, n_hom2,
+ * n_missing, as nldsc_ld_debug_unpack; may be NULL) the genotype counts.  All three are DEVICE pointers the caller owns;
+ * d_packed must be 4-byte aligned.  The work is queued on `stream` (a cudaStream_t, NULL = default stream) and NOT
+ * synchronised: the outputs are valid once the stream has reached this point.
+ * The call allocates nothing -- no cudaMalloc / cudaFree / allocating library routine: its intermediate arrays (counts,
+ * per-SNP coefficients, flags) live in one static __device__ array of 19.25 MiB that every GPU which loads the library
+ * holds until the process exits, sized for NLDSC_STATIC_MAX_SNPS rows.  n_snp beyond that is refused with
+ * NLDSC_ERR_INVALID before anything touches the GPU; split the rows over several calls.  Every call shares that array
+ * (it clears what it accumulates into), so calls that OVERLAP on the GPU -- other streams, other host threads -- race:
+ * serialise them.  The first call on each device looks the array's address up (cudaGetSymbolAddress) and loads the
+ * kernels; make it outside a capture. */
+#define NLDSC_STATIC_MAX_SNPS 262144
+int nldsc_ld_snp_stats_static(const uint8_t* d_packed, int32_t n_snp, int32_t n_org, double maf, double std_thr,
+                              int32_t* d_counts_out, double* d_maf_out, double* d_rstd_out, int32_t device,
+                              void* stream, char* err, size_t errlen);
+
 /* ---- parity hooks (used by tests/ only; they run the same kernels as the session) -- */
 /* Unpack + count `n_snp` packed rows: planes_out = int8 [4][n_snp][npad] in plane order
  * g,m,h,a (npad returned), counts_out = int32 [n_snp][3] = n_het, n_hom2, n_missing. */

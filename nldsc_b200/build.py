@@ -22,7 +22,8 @@ LIB = os.path.join(HERE, "libnldsc_ld.so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC"]
 # unpack.cu holds the float MAF path and the closed-form per-SNP statistics: no FMA contraction there
-SOURCES = {"unpack.cu": ["-fmad=false"], "plan.cu": ["-fmad=false"], "band_tc.cu": [], "band_simt.cu": [], "session.cu": []}
+SOURCES = {"unpack.cu": ["-fmad=false"], "plan.cu": ["-fmad=false"], "band_tc.cu": [], "band_simt.cu": [], "session.cu": [],
+           "static_stats.cu": []}
 HEADERS = ["common.cuh", "epilogue.cuh", "session.cuh", os.path.join("..", "..", "include", "nldsc_ld.h")]
 
 

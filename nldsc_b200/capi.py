@@ -25,8 +25,9 @@ EXPORTS = [
     "nldsc_ld_plan_windows", "nldsc_ld_plan_shards", "nldsc_ld_debug_band_probe", "nldsc_ld_debug_plan_windows_device",
     "nldsc_ld_calculate_on", "nldsc_ld_debug_i8_peak", "nldsc_ld_last_call_report", "nldsc_ld_arena_trim",
     "nldsc_ld_calculate_packed_on", "nldsc_ld_warmup", "nldsc_ld_debug_h2d_probe", "nldsc_ld_debug_fp4_probe",
-    "nldsc_ld_debug_unpack_fp4", "nldsc_ld_report_device_times",
+    "nldsc_ld_debug_unpack_fp4", "nldsc_ld_report_device_times", "nldsc_ld_snp_stats_static",
 ]
+STATIC_MAX_SNPS = 262144      # NLDSC_STATIC_MAX_SNPS of include/nldsc_ld.h
 
 
 class Params(C.Structure):
@@ -381,3 +382,15 @@ def debug_unpack_fp4(packed, n_org):
 def report_device_times(on: bool = True) -> None:
     """Fill the ms_dev_* fields of last_call_report() from now on (costs 0.15-0.2 ms per call and shard)."""
     lib().nldsc_ld_report_device_times(C.c_int32(1 if on else 0))
+
+
+def snp_stats_static(d_packed: int, n_snp: int, n_org: int, maf: float, std_thr: float, d_counts_out: int, d_maf_out: int,
+                     d_rstd_out: int, device: int = 0, stream: int = 0) -> None:
+    """nldsc_ld_snp_stats_static: per-SNP statistics of packed rows that are already on the device, written to device arrays
+    the caller owns; allocates nothing (static scratch, at most STATIC_MAX_SNPS rows per call).  Every pointer argument is a
+    DEVICE address (an int, e.g. tensor.data_ptr()); d_counts_out may be 0.  The work is queued on `stream`, not synchronised."""
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_snp_stats_static(C.c_void_p(d_packed), C.c_int32(n_snp), C.c_int32(n_org), C.c_double(maf),
+                                           C.c_double(std_thr), C.c_void_p(d_counts_out or None), C.c_void_p(d_maf_out),
+                                           C.c_void_p(d_rstd_out), C.c_int32(device), C.c_void_p(stream or None), err,
+                                           C.c_size_t(512)), err)
