@@ -527,7 +527,7 @@ def main():
     ub = float(st1["load_end"] - st1["load_begin"]) * (bps + 4.0 * st1["npad"])
     hbm_peak = peaks["hbm_gbs"] if peaks else 6500.0
     if st1["ms_unpack"] > 0:
-        roofline["unpack"] = {"bound": "hbm", "kernel": "unpack_kernel", "achieved": ub / (st1["ms_unpack"] * 1e-3) / 1e9,
+        roofline["unpack"] = {"bound": "hbm", "kernel": "unpack_fp4_kernel" if st1.get("fp4") else "unpack_kernel", "achieved": ub / (st1["ms_unpack"] * 1e-3) / 1e9,
                               "peak": hbm_peak, "unit": "GB/s", "frac": ub / (st1["ms_unpack"] * 1e-3) / 1e9 / hbm_peak,
                               "ms_alone": st1["ms_unpack"], "ms_beside_band": st["ms_unpack"]}
     sess.close()
