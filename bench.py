@@ -488,7 +488,10 @@ def main():
     peak_2x_bf16 = 2.0 * (peaks["bf16_tflops"] if peaks else 1590.0)
     achieved = ops / band_s / 1e12 if band_s > 0 else 0.0
     k_org = st["npad"] * (2 if fp4 else 1)             # padded organisms of a plane row (fp4 planes: two per byte)
-    executed = (st["tiles"] * 2.0 * 256 * 192 * k_org / band_s / 1e12) if band_s > 0 else 0.0
+    # executed MACs x 2: 256 x 192 per 64-SNP j-block of an i-pair, or 256 x 480 per 160-column supertile (band_x160_body)
+    x160 = int(st.get("xtiles_run", 0)) > 0
+    executed_units = st["xtiles_run"] * 480.0 if x160 else st["tiles"] * 192.0
+    executed = (executed_units * 2.0 * 256 * k_org / band_s / 1e12) if band_s > 0 else 0.0
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "band_traffic.json")
     if os.path.exists(tpath):
@@ -496,7 +499,7 @@ def main():
             traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
         except Exception:
             traffic = None
-    roofline = {"bound": "tensor", "kernel": {0: "band_simt_kernel", 1: "band_tc_kernel", 2: "band_tc_wide_kernel"}[st["band_impl"]],
+    roofline = {"bound": "tensor", "kernel": "band_tc_x160_kernel" if x160 else {0: "band_simt_kernel", 1: "band_tc_kernel", 2: "band_tc_wide_kernel"}[st["band_impl"]],
                 "achieved": achieved, "peak": peak, "unit": "TOP/s", "frac": achieved / peak, "traffic": traffic,
                 "peak_source": ("measured in this run: back-to-back tcgen05.mma.cta_group::2." +
                                 ("kind::mxf4 (e2m1 operands holding 0/1/2, scale factors 1.0, exact integer sums; M=256, K=64)" if fp4
@@ -510,6 +513,7 @@ def main():
                 "peak_n256": pk256["tops"],
                 "peak_2x_bf16": peak_2x_bf16, "frac_of_2x_bf16": achieved / peak_2x_bf16,
                 "peak_nominal": 4500.0, "frac_of_nominal": achieved / 4500.0,
+                "body": "band_x160_body (2 i-blocks x 160 j-SNPs, N = 256 + 224)" if x160 else "band_wide_body (2 i-blocks x 2 j-blocks, N = 192 + 192)",
                 "executed": executed, "executed_frac": executed / peak, "executed_over_algorithmic": executed / achieved if achieved else None,
                 "ms_band": st["ms_band"], "ms_unpack": st["ms_unpack"], "ms_count": st["ms_count"],
                 "ms_stats": st["ms_stats"], "ms_finalize": st["ms_finalize"], "ms_step_device": dev_ms,

@@ -121,6 +121,8 @@ typedef struct nldsc_ld_stats {
     int64_t qtiles;           /* missing-free supertiles planned (4 i-blocks x 2 j-blocks each), all chunks */
     int64_t mfree_qtiles;     /* ... of the chunks that took the path in the last run() */
     int64_t mfree_tiles_skipped;   /* 6-plane supertiles (wide: 2 i-blocks x <= 2 j-blocks) those chunks did NOT run */
+    int64_t xtiles;           /* 160-column supertiles (2 i-blocks x five 32-SNP column groups, fp4 planes) planned, all chunks; 0 = that body is off */
+    int64_t xtiles_run;       /* ... of the chunks that did not take the missing-free path in the last run() */
 } nldsc_ld_stats;
 
 /* Shard = SNP rows [row_begin,row_end) of the bfile described by `params`

@@ -49,7 +49,8 @@ class Stats(C.Structure):
                 ("npad", C.c_int32), ("band_impl", C.c_int32), ("ms_count", C.c_float),
                 ("ms_stats", C.c_float), ("ms_unpack", C.c_float), ("ms_band", C.c_float),
                 ("ms_finalize", C.c_float), ("ms_total", C.c_float), ("mfree_chunks", C.c_int32), ("fp4", C.c_int32),
-                ("qtiles", C.c_int64), ("mfree_qtiles", C.c_int64), ("mfree_tiles_skipped", C.c_int64)]
+                ("qtiles", C.c_int64), ("mfree_qtiles", C.c_int64), ("mfree_tiles_skipped", C.c_int64),
+                ("xtiles", C.c_int64), ("xtiles_run", C.c_int64)]
 
 
 class ShardReport(C.Structure):

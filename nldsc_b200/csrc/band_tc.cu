@@ -234,9 +234,9 @@ __device__ __forceinline__ void tc_mma_mxf4(uint32_t d_tmem, uint64_t a_desc, ui
 }
 constexpr uint32_t kSfCols = 448;   // TMEM columns 448..479 hold scale factors 1.0 for every lane: any SF layout reads ones
 
-__device__ __forceinline__ void tmem_fill_sf_ones(uint32_t tmem_base, int warp_in_quarter_order) {
+__device__ __forceinline__ void tmem_fill_sf_ones(uint32_t tmem_base, int warp_in_quarter_order, uint32_t sf_cols = kSfCols) {
     // 32 lanes of this warp's quarter x 32 columns of 0x7F7F7F7F (four E8M0 exponents of 2^0 per 32-bit column)
-    const uint32_t taddr = tmem_base + kSfCols + (static_cast<uint32_t>(32 * (warp_in_quarter_order & 3)) << 16);
+    const uint32_t taddr = tmem_base + sf_cols + (static_cast<uint32_t>(32 * (warp_in_quarter_order & 3)) << 16);
     const uint32_t v = 0x7F7F7F7Fu;
 #pragma unroll
     for (int c = 0; c < 32; c += 16)
@@ -960,6 +960,277 @@ __device__ __forceinline__ void band_mfree_body(const CUtensorMap& map_g, const 
     }
 }
 
+// ---- 160-column supertiles: five 32-SNP column groups per i-pair, two MMAs per 64 organisms (fp4 planes only) --------
+// See XTile (common.cuh).  Per K-step (256 organisms) a CTA stages its A block (64 i-SNPs x {g, m}: 16 KB, as the wide body
+// does) and the 80 j-SNPs of its rank as five 16-SNP boxes [m16 h16 a16] (240 rows, 30 KB; four stages of 46 KB); the
+// leader issues 4 x (N = 256 from each CTA's rows 0..127, into TMEM columns 0..255) + 4 x (N = 224 from rows 128..239,
+// into columns 256..479); the scale factors (all 2^0) sit in columns 480..511.  B row r of rank c lands in column
+// 128 c + r (r < 128) or 256 + 112 c + (r - 128), so the m / h / a counts of sixteen k = 5 c + u (j-SNPs 16 k .. 16 k + 15
+// of the supertile) are 16 consecutive columns each, at rows r = 48 u + 16 plane.
+// Epilogue: 8 warps as in the wide body (warp w reads TMEM lanes 32 (w % 4) ..+31 = 16 i-SNPs x {g, m}).  A partial sum is
+// the sum over ONE 32-SNP group in a fixed order (that is what makes every body bitwise equal), and five groups do not
+// split over two warp groups: warp group 0 scores the first sixteen of group 2, then groups 0 and 1; warp group 1 scores
+// groups 3 and 4, then takes group 2's running sums over through shared memory and adds its second sixteen -- five
+// sixteens each.
+namespace {
+constexpr int kXStages = 4;
+constexpr int kXSnps = 160;                                  // j-SNPs of a supertile; each CTA stages 80
+constexpr int kXBRows = 240;                                 // per CTA: 5 sixteens x {m, h, a}
+constexpr int kXBoxBytes = 48 * kKStep;                      // one sixteen: 6 KB
+constexpr int kXBBytes = kXBRows * kKStep;                   // 30 KB
+constexpr int kXStageBytes = kABytes + kXBBytes;             // 46 KB per CTA per stage
+constexpr int kXColBytes = kXSnps * static_cast<int>(sizeof(SnpCoef)) + kXSnps;   // the j-SNPs' SnpCoef + flags
+constexpr int kXHandBytes = 128 * (8 + 8 + 12);              // group 2's running sums, per epilogue lane of one warp group
+constexpr int kXSmemBytes = kXStages * kXStageBytes + 1024 + 256 + kXColBytes + kXHandBytes;
+constexpr uint32_t kXSfCols = 480;
+static_assert(kXStageBytes % 1024 == 0 && kXBoxBytes % 1024 == 0, "swizzle atoms stay aligned");
+static_assert(kXColBytes % 16 == 0, "the handover area stays 16-byte aligned");
+}  // namespace
+
+// named barriers 2..5 (literal ids: a register operand would make ptxas reserve all 16 of the SM's barriers for this CTA):
+// the two epilogue warps that share TMEM lane quarter q hand group 2's running sums over
+__device__ __forceinline__ void hand_bar_arrive(int q) {
+    switch (q) {
+        case 0: asm volatile("bar.arrive 2, 64;" ::: "memory"); break;
+        case 1: asm volatile("bar.arrive 3, 64;" ::: "memory"); break;
+        case 2: asm volatile("bar.arrive 4, 64;" ::: "memory"); break;
+        default: asm volatile("bar.arrive 5, 64;" ::: "memory"); break;
+    }
+}
+__device__ __forceinline__ void hand_bar_sync(int q) {
+    switch (q) {
+        case 0: asm volatile("bar.sync 2, 64;" ::: "memory"); break;
+        case 1: asm volatile("bar.sync 3, 64;" ::: "memory"); break;
+        case 2: asm volatile("bar.sync 4, 64;" ::: "memory"); break;
+        default: asm volatile("bar.sync 5, 64;" ::: "memory"); break;
+    }
+}
+
+__device__ __forceinline__ void band_x160_body(const CUtensorMap& map_a, const CUtensorMap& map_b16, const BandArgs& args) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + kXStages * kXStageBytes);   // leader CTA only
+    uint64_t* empty = full + kXStages;         // one per CTA
+    uint64_t* tfull = empty + kXStages;        // one per CTA
+    uint64_t* tempty = tfull + 1;              // leader CTA only
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 1);
+    double2* col_coef = reinterpret_cast<double2*>(smem + kXStages * kXStageBytes + 256);
+    uint8_t* col_flags = reinterpret_cast<uint8_t*>(col_coef) + kXSnps * sizeof(SnpCoef);
+    double* hand_add = reinterpret_cast<double*>(reinterpret_cast<uint8_t*>(col_coef) + kXColBytes);
+    double* hand_dom = hand_add + 128;
+    int32_t* hand_w = reinterpret_cast<int32_t*>(hand_dom + 128);                   // [3][128]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b16)) : "memory");
+        for (int s = 0; s < kXStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_init(tfull, 1);
+        mbar_init(tempty, 16);                 // 8 epilogue warps x 2 CTAs
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                     "r"((uint32_t)kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (warp >= 2 && warp < 6) tmem_fill_sf_ones(tmem_base, warp, kXSfCols);
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+
+    if (warp == 0) {
+        // ===== TMA producer: own A block, the five sixteens of the own 80 j-SNPs =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = pair; t < args.n_xtiles; t += n_pairs) {
+                const XTile tl = args.xtiles[t];
+                const int32_t a_row = tl.a_row[rank];
+                int32_t b_row[5];
+#pragma unroll
+                for (int u = 0; u < 5; ++u) b_row[u] = (tl.j0 + 80 * static_cast<int32_t>(rank) + 16 * u) % args.ring_rows;
+                const uint32_t bytes = 2u * kXStageBytes;                                    // both CTAs' bytes
+                for (int k = 0; k < args.k_steps; ++k) {
+                    mbar_wait(&empty[stage], phase ^ 1, 15);
+                    if (rank == 0) mbar_expect_tx(&full[stage], bytes);
+                    uint8_t* sa = smem + stage * kXStageBytes;
+                    uint8_t* sb = sa + kABytes;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        tma_load_3d(sa + u * 4096, &map_a, &full[stage], k * kKStep, a_row + 16 * u, kPlaneG);
+#pragma unroll
+                    for (int u = 0; u < 5; ++u)
+                        tma_load_3d(sb + u * kXBoxBytes, &map_b16, &full[stage], k * kKStep, b_row[u], kPlaneM);
+                    if (++stage == kXStages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader CTA only) =====
+        if (rank == 0 && lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            int n = 0;
+            const uint32_t sf = tmem_base + kXSfCols;
+            for (int t = pair; t < args.n_xtiles; t += n_pairs, ++n) {
+                mbar_wait(tempty, (n & 1) ^ 1, 16);                  // both CTAs' epilogues drained the accumulator
+                tc_fence_after();
+                for (int k = 0; k < args.k_steps; ++k) {
+                    mbar_wait(&full[stage], phase, 17);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * kXStageBytes);
+                    const uint64_t a_desc = make_smem_desc(sa);
+                    const uint64_t b1_desc = make_smem_desc(sa + kABytes);
+                    const uint64_t b2_desc = make_smem_desc(sa + kABytes + 128 * kKStep);
+#pragma unroll
+                    for (int kk = 0; kk < kKStep / 32; ++kk)
+                        tc_mma_mxf4(tmem_base, a_desc + 2 * kk, b1_desc + 2 * kk, idesc_mxf4(256), sf, sf + 16, (k | kk) != 0);
+#pragma unroll
+                    for (int kk = 0; kk < kKStep / 32; ++kk)
+                        tc_mma_mxf4(tmem_base + 256, a_desc + 2 * kk, b2_desc + 2 * kk, idesc_mxf4(224), sf, sf + 16, (k | kk) != 0);
+                    tc_commit_pair(&empty[stage]);
+                    if (++stage == kXStages) { stage = 0; phase ^= 1; }
+                }
+                tc_commit_pair(tfull);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue: eight warps per CTA; q = TMEM lane quarter, wg = warp group =====
+        const int q = warp & 3;
+        const int wg = (warp - 2) >> 2;
+        const bool is_g = lane < 16;
+        const int s = 16 * q + (lane & 15);
+        const int hl = 32 * q + lane;                                 // handover slot of this lane
+        int n = 0;
+        for (int t = pair; t < args.n_xtiles; t += n_pairs, ++n) {
+            const XTile tl = args.xtiles[t];
+            const int32_t i0 = tl.i0[rank];
+            const RowCtx row = load_row_ctx(args, i0 + s);
+            // the constants of the supertile's 160 j-SNPs, staged while the MMAs run (as in the wide body)
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            {
+                const int te = threadIdx.x - 64;                       // 0..255 among the epilogue threads
+                for (int e = te; e < kXSnps * 4; e += 256) {           // 4 double2 per SNP
+                    const int32_t gj = tl.j0 + (e >> 2);
+                    double2 v = make_double2(0.0, 0.0);
+                    if (gj < args.n_load) v = __ldg(reinterpret_cast<const double2*>(args.coef + gj) + (e & 3));
+                    col_coef[e] = v;
+                }
+                if (te < kXSnps) {
+                    const int32_t gj = tl.j0 + te;
+                    col_flags[te] = gj < args.n_load ? __ldg(args.flags + gj) : uint8_t(0);
+                }
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            mbar_wait_idle(tfull, n & 1, 18);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(32 * q) << 16);
+            RowAcc acc;
+#pragma unroll 1
+            for (int step = 0; step < 5; ++step) {
+                // warp group 0: sixteen 4 (first half of group 2), then groups 0 and 1; warp group 1: groups 3 and 4, then sixteen 5
+                const int k = wg == 0 ? (step == 0 ? 4 : step - 1) : (step < 4 ? 6 + step : 5);
+                const int grp = k >> 1;
+                if (wg == 1 && step == 4) {
+                    // group 2's sums so far, from the warp of the other group that shares this lane quarter
+                    hand_bar_sync(q);
+                    acc.add = hand_add[hl];
+                    acc.dom = hand_dom[hl];
+                    acc.wsa = hand_w[hl];
+                    acc.wsd = hand_w[128 + hl];
+                    acc.wsde = hand_w[256 + hl];
+                }
+                const int32_t jk = tl.j0 + 16 * k;
+                if (grp < tl.n_grp && (args.no_skip || __any_sync(0xFFFFFFFFu, row_needs(row, jk, jk + 15)))) {
+                    const int c = k >= 5 ? 1 : 0, u5 = k - 5 * c;
+                    int32_t vm[16], vh[16], va[16];
+                    {
+                        const int r_m = 48 * u5, r_h = r_m + 16, r_a = r_m + 32;
+                        const uint32_t col_m = r_m < 128 ? 128 * c + r_m : 256 + 112 * c + (r_m - 128);
+                        const uint32_t col_h = r_h < 128 ? 128 * c + r_h : 256 + 112 * c + (r_h - 128);
+                        const uint32_t col_a = r_a < 128 ? 128 * c + r_a : 256 + 112 * c + (r_a - 128);
+                        tmem_ld16(taddr + col_m, vm);
+                        tmem_ld16(taddr + col_h, vh);
+                        tmem_ld16(taddr + col_a, va);
+                        tmem_ld_wait();
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        // FP32 bit patterns of exact counts, converted to double pair by pair (cnt2d<true>)
+                        const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
+                        const int32_t sh_ = is_g ? vh[2 * u + 1] : vh[2 * u];
+                        const int32_t sa_ = is_g ? va[2 * u + 1] : va[2 * u];
+                        const int32_t rm = __shfl_xor_sync(0xFFFFFFFFu, sm_, 16);
+                        const int32_t rh = __shfl_xor_sync(0xFFFFFFFFu, sh_, 16);
+                        const int32_t ra = __shfl_xor_sync(0xFFFFFFFFu, sa_, 16);
+                        const int jl = 16 * k + 2 * u + (is_g ? 0 : 1);
+                        const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
+                        const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
+                        const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
+                        const double2* cj = col_coef + 4 * jl;
+                        pair_eval_core<true>(args, row, tl.j0 + jl, col_flags[jl], cj[0], cj[1], cj[2], cj[3],
+                                             Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
+                    }
+                }
+                if (wg == 0 && step == 0) {
+                    hand_add[hl] = acc.add;
+                    hand_dom[hl] = acc.dom;
+                    hand_w[hl] = acc.wsa;
+                    hand_w[128 + hl] = acc.wsd;
+                    hand_w[256 + hl] = acc.wsde;
+                    hand_bar_arrive(q);
+                    acc = RowAcc();
+                    continue;
+                }
+                const bool group_done = wg == 0 ? (step == 2 || step == 4) : (step == 1 || step >= 3);
+                if (!group_done) continue;
+                if (step == 4) {
+                    // the last TMEM read of this warp is behind it: tell the leader's MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_leader(tempty);
+                }
+                if (grp < tl.n_grp) {
+                    acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
+                    acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);
+                    acc.wsa += __shfl_xor_sync(0xFFFFFFFFu, acc.wsa, 16);
+                    acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
+                    acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
+                    if (is_g) {
+                        const int gg = tl.odd + grp;
+                        const int64_t o = part_index(tl.slot + (gg >> 1), static_cast<int>(rank), gg & 1, s);
+                        args.part.add[o] = acc.add;
+                        args.part.dom[o] = acc.dom;
+                        args.part.wsa[o] = acc.wsa;
+                        args.part.wsd[o] = acc.wsd;
+                        args.part.wsde[o] = acc.wsde;
+                    }
+                }
+                acc = RowAcc();
+            }
+        }
+    }
+
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
+                     : "memory");
+    }
+}
+
 // ONE launch per chunk for both paths: the chunk's flag (written on the device after its stats) picks the body.
 // (Two kernels, one of them returning at once, cost configs[1] 12 %: the idle launch still has to wait for a whole
 // grid's worth of free SMs behind the other stream's persistent band kernel -- profiles/r02i_ab_missing_n10000.json.)
@@ -975,12 +1246,23 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     else band_wide_body(map_a, map_b, args);
 }
 
+// The same launch with the 160-column body for the 6-plane work (fp4 planes).  A kernel of its own so that the register
+// allocation of the kernel above stays what it was.
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(NLDSC_WIDE_MAXNREG)
+band_tc_x160_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b16,
+                    const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ha, const BandArgs args) {
+    const bool mfree = args.mfree_flag != nullptr && *reinterpret_cast<const volatile uint32_t*>(args.mfree_flag) != 0;
+    if (mfree) band_mfree_body(map_g, map_ha, args);
+    else band_x160_body(map_a, map_b16, args);
+}
+
 // ---- host side: TMA descriptors + launch ------------------------------------------------
 struct BandMaps {
     CUtensorMap a;   // box {128 B, 16 rows, 2 planes}
     CUtensorMap b;   // box {128 B, 32 rows, 3 planes}
     CUtensorMap g;   // box {128 B, 64 rows, 1 plane}    missing-free kernel: g of one i-block
     CUtensorMap ha;  // box {128 B, 64 rows, 2 planes}   missing-free kernel: [h ; a] of one j-block
+    CUtensorMap b16; // box {128 B, 16 rows, 3 planes}   160-column supertiles: [m ; h ; a] of one sixteen
 };
 
 namespace {
@@ -1025,6 +1307,7 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
         encode(&m->b, planes, plane_rows, npad, 32, 3);
         encode(&m->g, planes, plane_rows, npad, 64, 1);
         encode(&m->ha, planes, plane_rows, npad, 64, 2);
+        encode(&m->b16, planes, plane_rows, npad, 16, 3);
     } catch (...) {
         delete m;
         throw;
@@ -1040,7 +1323,7 @@ std::mutex g_hang_mu;
 const char* const kSiteNames[] = {"?", "narrow/producer:empty", "narrow/mma:tmem-empty", "narrow/mma:full", "narrow/epilogue:tmem-full",
                                   "wide/producer:empty", "wide/mma:tmem-empty", "wide/mma:full", "wide/epilogue:tmem-full", "i8-peak",
                                   "rows-ready (the chunk's unpack never published)", "mfree/producer:empty", "mfree/mma:tmem-empty", "mfree/mma:full",
-                                  "mfree/epilogue:tmem-full"};
+                                  "mfree/epilogue:tmem-full", "x160/producer:empty", "x160/mma:tmem-empty", "x160/mma:full", "x160/epilogue:tmem-full"};
 void install_hang_word() {
     int dev = 0;
     CUDA_CHECK(cudaGetDevice(&dev));
@@ -1072,11 +1355,15 @@ std::string band_hang_note() {
     return note;
 }
 
+constexpr int kWideKernelSmem = kWSmemBytes > kMSmemBytes ? kWSmemBytes : kMSmemBytes;
+constexpr int kX160KernelSmem = kXSmemBytes > kMSmemBytes ? kXSmemBytes : kMSmemBytes;
+static_assert(kWideKernelSmem <= 232448 && kX160KernelSmem <= 232448, "dynamic shared memory of one CTA");
+
 void install_band_kernels() {
     install_hang_word();
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    kWSmemBytes > kMSmemBytes ? kWSmemBytes : kMSmemBytes));
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideKernelSmem));
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_x160_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kX160KernelSmem));
 }
 
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
@@ -1090,12 +1377,21 @@ void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cu
 }
 
 void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
-    const int32_t n_max = args.mfree_flag != nullptr ? (args.n_tiles > args.n_qtiles ? args.n_tiles : args.n_qtiles) : args.n_tiles;
+    // the supertile list the launch walks is chosen on the device (the chunk's missing-free flag): size the grid for the longest
+    const bool x160 = args.xtiles != nullptr;
+    const int32_t n_6 = x160 ? args.n_xtiles : args.n_tiles;
+    const int32_t n_max = args.mfree_flag != nullptr ? (n_6 > args.n_qtiles ? n_6 : args.n_qtiles) : n_6;
     if (n_max <= 0) return;
     install_hang_word();
-    constexpr int smem = kWSmemBytes > kMSmemBytes ? kWSmemBytes : kMSmemBytes;
-    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     const int pairs = n_max < sm_count / 2 ? n_max : sm_count / 2;
+    if (x160) {
+        CUDA_CHECK(cudaFuncSetAttribute(band_tc_x160_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kX160KernelSmem));
+        band_tc_x160_kernel<<<2 * pairs, kWThreads, kX160KernelSmem, st>>>(maps->a, maps->b16, maps->g, maps->ha, args);
+        CUDA_CHECK(cudaGetLastError());
+        return;
+    }
+    constexpr int smem = kWideKernelSmem;
+    CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     band_tc_wide_kernel<<<2 * pairs, kWThreads, smem, st>>>(maps->a, maps->b, maps->g, maps->ha, args);
     CUDA_CHECK(cudaGetLastError());
 }

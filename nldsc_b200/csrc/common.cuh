@@ -61,6 +61,21 @@ struct QTile {
     int32_t pad;
 };
 
+// 160-column supertile (band_x160_body of band_tc_wide_kernel, fp4 planes with missing genotypes): one i-pair x FIVE
+// consecutive 32-SNP column groups starting at j0 (a multiple of 32, anywhere in the i-pair's j-range).  An mxf4 MMA costs
+// the same ~150 clk whatever its N, so the 480 accumulator columns of 160 j-SNPs x {m, h, a} are filled by TWO MMAs per 64
+// organisms (N = 256 + 224) where two 64-SNP j-blocks take two for 128 j-SNPs: a fifth fewer instructions per SNP pair.
+// Group g of the supertile is half (odd + g) & 1 of the 64-SNP j-block at slot + ((odd + g) >> 1): the same partial-sum
+// groups, summed in the same order, as the 64-block supertiles -- bitwise identical scores.
+struct XTile {
+    int32_t a_row[2];  // ring rows of the two i-blocks
+    int32_t i0[2];     // first SNP (shard-local) of each i-block, or kDeadBlock
+    int32_t j0;        // first SNP of the supertile (shard-local, a multiple of 32)
+    int32_t slot;      // partial-sum slot of the 64-SNP j-block that holds j0
+    int32_t n_grp;     // 1..5 groups lie inside the i-pair's j-range; the others are multiplied but never scored
+    int32_t odd;       // (j0 / 32) & 1
+};
+
 // Per-row partial sums a (64 x 64 SNP) tile contributes, in two halves: j-SNPs 0..31 and 32..63 of the j-block
 // (the wide kernel scores the halves in different warps).  SoA, index = part_index(slot, rank, half, row).
 __host__ __device__ inline int64_t part_index(int64_t slot, int rank, int half, int row) {
@@ -96,6 +111,9 @@ struct BandArgs {
                                 // `tiles` (6 planes); null = the missing-free path is off
     const uint32_t* ready_rows; // fused launch (one band launch per shard): ring rows [0, *ready_rows) are unpacked and their
                                 // per-SNP statistics final; published after every chunk's unpack + stats.  null = everything is ready
+    const XTile* xtiles;        // 160-column supertiles of the same chunk (band_x160_body; fp4 planes only), same slots; null = off
+    int32_t n_xtiles;
+    int32_t ring_rows;          // rows of the plane ring (a multiple of 64): ring row of SNP j = j % ring_rows
     int32_t fp4;                // the planes hold e2m1 nibbles (launch_unpack_fp4): the wide / missing-free bodies multiply them with
                                 // tcgen05.mma.kind::mxf4 (scale factors 1.0, K = 64 per MMA, k_steps = plane row bytes / 128)
     int32_t runahead;           // wide body: start the next supertile's j-block-0 MMAs while the epilogue still reads accumulator 1

@@ -601,6 +601,13 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     // (counts stay below 2 N < 2^22).  The narrow kernel and the SIMT yardstick keep int8 planes (NLDSC_FP4=0: so does the wide one).
     const char* f4 = getenv("NLDSC_FP4");
     s->fp4 = s->wide && !(f4 && f4[0] == '0') && p->n_org <= 2000000;
+    // 160-column supertiles for the 6-plane work on fp4 planes: an mxf4 MMA costs the same whatever its N, and five 32-SNP column
+    // groups take two of them (N = 256 + 224) where two 64-SNP j-blocks take two for 128 SNPs.  Measured against the 2 x 2-block
+    // supertiles, same box, bitwise equal (profiles/r02za_x160_*.json): N=2,504 +3 % (its accumulator is one piece, the epilogue
+    // fully exposed), N=5,000 -2.6 %, N=7,000 -5.7 %, N=10,000 -7.2 %, N=50,000 -7.5 %, N=315,599 -7 %, N=100,000 with a 10 cM
+    // window -13 %.  Default from N = 4,096 (where the chunks shrink to 8,192 rows); NLDSC_X160=0 / 1 forces.
+    const char* x16 = getenv("NLDSC_X160");
+    s->x160 = s->fp4 && (x16 ? x16[0] == '1' : p->n_org >= 4096);
     if (s->fp4)      // plane row BYTES: a whole number of 128-byte pipeline stages = 256 organisms each
         s->npad = static_cast<int32_t>(((static_cast<int64_t>(p->n_org) + 2 * kKAlign - 1) / (2 * kKAlign)) * kKAlign);
     s->load_begin = load_begin;
@@ -858,7 +865,8 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         // positions -> pinned -> device (SM copy), windows straight into d_win_lo / d_win_hi; the pinned buffer is
         // sized once for everything this plan stages, because growing it would free memory the copy kernel reads
         s->pstage->reserve(b_pos + pad16(sizeof(Tile) * static_cast<size_t>(tiles_bound)) + pad16(sizeof(int32_t) * (2 * static_cast<size_t>(n_ib) + 4)) +
-                           (s->mfree ? pad16(sizeof(QTile) * static_cast<size_t>(tiles_bound)) : 0));
+                           (s->mfree ? pad16(sizeof(QTile) * static_cast<size_t>(tiles_bound)) : 0) +
+                           (s->x160 ? pad16(sizeof(XTile) * static_cast<size_t>(tiles_bound)) : 0));
         double* d_pos = amalloc<double>(s->arena, static_cast<size_t>(n_load) + 2);
         s->d_total_pairs = amalloc<unsigned long long>(s->arena, 1);
         CUDA_CHECK(cudaMemsetAsync(s->d_total_pairs, 0, sizeof(unsigned long long), st));
@@ -957,10 +965,17 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     tiles.clear();
     tile_begin.clear();
     s->h_qtiles.clear();
+    s->h_xtiles.clear();
     int32_t unpacked_to = jb_lo[0] * kBlk;   // rows below the first needed column never enter the ring
     int32_t slot_base = 0;
     // supertiles of the i-block pair starting at block k when the chunk ends at e
     auto pair_tiles = [&](int32_t k, int32_t e) { return (k + 1 < e ? jb_hi[k + 1] : jb_hi[k]) - jb_lo[k] + 1; };
+    // ... in the units the band kernel deals to its CTA pairs: runs of five 32-SNP groups with the 160-column body (the
+    // 64-block bodies keep counting j-blocks, which is what their chunk sizes were measured with)
+    auto pair_units = [&](int32_t k, int32_t e) {
+        const int32_t nb = pair_tiles(k, e);
+        return s->x160 ? (2 * nb + 4) / 5 : nb;
+    };
     for (int32_t b = 0; b < n_ib;) {
         Chunk c{};
         c.iblock0 = ib0 + b;
@@ -983,12 +998,12 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         // chunk (whole i-block pairs) to where the last wave is fullest.
         if (!fixed_rows && e < n_ib && e - b >= 32 && (e - b) % 2 == 0) {
             int64_t nt = 0;
-            for (int32_t k = b; k < e; k += 2) nt += pair_tiles(k, e);
+            for (int32_t k = b; k < e; k += 2) nt += pair_units(k, e);
             int32_t best_e = e;
             double best_fill = static_cast<double>(nt) / (static_cast<double>((nt + wave - 1) / wave) * wave);
             int64_t nt_k = nt;
             for (int32_t e2 = e - 2; e2 >= e - (e - b) / 8 && e2 - b >= 2; e2 -= 2) {
-                nt_k -= pair_tiles(e2, e);                  // drop the pair (e2, e2 + 1)
+                nt_k -= pair_units(e2, e);                  // drop the pair (e2, e2 + 1)
                 const double fill = static_cast<double>(nt_k) / (static_cast<double>((nt_k + wave - 1) / wave) * wave);
                 if (fill > best_fill + 1e-9) { best_fill = fill; best_e = e2; }
             }
@@ -1085,6 +1100,37 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
             }
         }
         c.n_qtiles = static_cast<int32_t>(static_cast<int64_t>(s->h_qtiles.size()) - c.qtile0);
+        // 160-column supertiles of the same chunk: every i-pair's j-range [jb_lo, jb_hi] cut into runs of five 32-SNP
+        // groups from its own first column (nothing is aligned to more than 32 SNPs, so only the last run of an i-pair
+        // is partly outside its range); same slots, same raster (run m of kRaster i-pairs side by side)
+        c.xtile0 = static_cast<int64_t>(s->h_xtiles.size());
+        if (s->x160 && !s->fused_ok) {
+            for (int32_t g0 = b; g0 < e; g0 += 2 * kRaster) {
+                const int32_t g1 = std::min(e, g0 + 2 * kRaster);
+                bool any = true;
+                for (int32_t m = 0; any; ++m) {
+                    any = false;
+                    for (int32_t k = g0; k < g1; k += 2) {
+                        const bool two = k + 1 < e;
+                        const int32_t lo_k = jb_lo[k], hi_k = two ? jb_hi[k + 1] : jb_hi[k];
+                        const int32_t n32 = 2 * (hi_k - lo_k + 1);
+                        if (5 * m >= n32) continue;
+                        any = true;
+                        XTile t;
+                        t.i0[0] = (ib0 + k) * kBlk;
+                        t.i0[1] = two ? (ib0 + k + 1) * kBlk : kDeadBlock;
+                        t.a_row[0] = static_cast<int32_t>(t.i0[0] % cap);
+                        t.a_row[1] = two ? static_cast<int32_t>(t.i0[1] % cap) : t.a_row[0];
+                        t.j0 = lo_k * kBlk + 160 * m;
+                        t.slot = slot0[(k - b) / 2] + ((5 * m) >> 1);
+                        t.n_grp = std::min(5, n32 - 5 * m);
+                        t.odd = (5 * m) & 1;
+                        s->h_xtiles.push_back(t);
+                    }
+                }
+            }
+        }
+        c.n_xtiles = static_cast<int32_t>(static_cast<int64_t>(s->h_xtiles.size()) - c.xtile0);
         s->max_chunk_slots = std::max(s->max_chunk_slots, nslots_chunk);
         c.slot_base = slot_base;                         // fused plans: where the chunk's partials start
         slot_base += nslots_chunk;
@@ -1099,14 +1145,16 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
     for (size_t k = 0; k + 1 < tile_begin.size(); ++k) s->total_tiles += std::max(0, tile_begin[k + 1] - tile_begin[k]);
     s->d_tiles = amalloc<Tile>(s->arena, tiles.size());
     if (s->mfree) s->d_qtiles = amalloc<QTile>(s->arena, s->h_qtiles.size());
+    if (s->x160) s->d_xtiles = amalloc<XTile>(s->arena, s->h_xtiles.size() + 1);
     s->d_tile_begin = amalloc<int32_t>(s->arena, tile_begin.size());
     {
         // plan arrays -> pinned staging -> device by an SM copy: the H2D copy engine is busy with (or about to
         // be queued full of) the shard's packed rows, and these few MB must not wait behind them
         const size_t b_win = fast ? 0 : pad16(sizeof(int32_t) * n_load_pad), b_tiles = pad16(sizeof(Tile) * tiles.size()),
-                     b_tb = pad16(sizeof(int32_t) * tile_begin.size()), b_qt = s->mfree ? pad16(sizeof(QTile) * s->h_qtiles.size()) : 0;
-        if (!fast) s->pstage->reserve(2 * b_win + b_tiles + b_tb + b_qt);
-        else if (b_pos + b_tiles + b_tb + b_qt > s->pstage->bytes) throw CudaError("plan staging bound exceeded");
+                     b_tb = pad16(sizeof(int32_t) * tile_begin.size()), b_qt = s->mfree ? pad16(sizeof(QTile) * s->h_qtiles.size()) : 0,
+                     b_xt = s->x160 ? pad16(sizeof(XTile) * s->h_xtiles.size()) : 0;
+        if (!fast) s->pstage->reserve(2 * b_win + b_tiles + b_tb + b_qt + b_xt);
+        else if (b_pos + b_tiles + b_tb + b_qt + b_xt > s->pstage->bytes) throw CudaError("plan staging bound exceeded");
         char* h = s->pstage->base + b_pos;
         if (!fast) {
             memcpy(h, wlo.data(), sizeof(int32_t) * n_load_pad);
@@ -1121,6 +1169,10 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         if (s->mfree && !s->h_qtiles.empty()) {
             memcpy(h + 2 * b_win + b_tiles + b_tb, s->h_qtiles.data(), sizeof(QTile) * s->h_qtiles.size());
             launch_copy16(h + 2 * b_win + b_tiles + b_tb, s->d_qtiles, b_qt, st);
+        }
+        if (s->x160 && !s->h_xtiles.empty()) {
+            memcpy(h + 2 * b_win + b_tiles + b_tb + b_qt, s->h_xtiles.data(), sizeof(XTile) * s->h_xtiles.size());
+            launch_copy16(h + 2 * b_win + b_tiles + b_tb + b_qt, s->d_xtiles, b_xt, st);
         }
     }
     if (s->mfree) {
@@ -1227,6 +1279,7 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         a.dump = nullptr;
         a.commit2 = commit2;
         a.fp4 = s->fp4 ? 1 : 0;
+        a.ring_rows = static_cast<int32_t>(s->plane_rows);
         { const char* ra = getenv("NLDSC_RUNAHEAD"); a.runahead = (ra && ra[0] == '0') ? 0 : 1; }
         a.no_skip = env_size("NLDSC_NOSKIP", 0) != 0 ? 1 : 0;
         return a;
@@ -1349,6 +1402,10 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
             a.qtiles = s->d_qtiles + c.qtile0;
             a.n_qtiles = c.n_qtiles;
             a.mfree_flag = s->d_mfree_flags + ci;
+        }
+        if (s->x160 && s->wide && !s->use_simt && c.n_xtiles > 0) {
+            a.xtiles = s->d_xtiles + c.xtile0;
+            a.n_xtiles = c.n_xtiles;
         }
         {
             SpanScope sc(s, bs, kFamBand);
@@ -1887,6 +1944,8 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* o) {
     o->band_impl = s->use_simt ? 0 : (s->wide ? 2 : 1);
     o->qtiles = s->total_qtiles;
     o->fp4 = s->fp4 ? 1 : 0;
+    o->xtiles = static_cast<int64_t>(s->h_xtiles.size());
+    o->xtiles_run = o->xtiles;
     if (s->ran && s->mfree && s->d_mfree_flags) {
         std::vector<uint32_t> fl(s->chunks.size());
         cudaSetDevice(s->device);
@@ -1897,6 +1956,7 @@ int nldsc_ld_session_stats(nldsc_ld_session* s, nldsc_ld_stats* o) {
                 ++o->mfree_chunks;
                 o->mfree_qtiles += s->chunks[k].n_qtiles;
                 o->mfree_tiles_skipped += s->chunks[k].n_tiles;
+                o->xtiles_run -= s->chunks[k].n_xtiles;
             }
         }
     }

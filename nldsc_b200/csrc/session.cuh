@@ -33,6 +33,8 @@ struct Chunk {
     int32_t tb0;          // offset into tile_begin (n_iblocks + 1 entries, relative to tile0)
     int64_t qtile0;       // missing-free supertiles of the same chunk (session::d_qtiles)
     int32_t n_qtiles;
+    int64_t xtile0;       // 160-column supertiles of the same chunk (session::d_xtiles)
+    int32_t n_xtiles;
     int32_t blk0, blk1;   // 64-SNP blocks [blk0, blk1) the chunk's tiles read: the range its missing-free flag covers
     int32_t slot_base;    // fused plans: first partial slot of the chunk (its tiles' slots already include it)
 };
@@ -104,6 +106,9 @@ struct nldsc_ld_session {
     std::vector<nldsc::QTile> h_qtiles;
     int64_t total_qtiles = 0;
     bool fp4 = false;                         // planes hold e2m1 nibbles; npad = plane row BYTES = organisms / 2, padded to 128
+    bool x160 = false;                        // fp4 planes: chunks with missing genotypes take the 160-column supertiles (band_x160_body)
+    nldsc::XTile* d_xtiles = nullptr;
+    std::vector<nldsc::XTile> h_xtiles;
     bool fused_ok = false;                    // the plan allows ONE band launch per shard (session_plan); run() decides
     uint32_t* d_ready = nullptr;              // fused launch: ring rows [0, *d_ready) are unpacked, their statistics final
     bool upload_started = false;

@@ -36,6 +36,9 @@ VARIANTS = [
     {"NLDSC_FP4": "0"},
     {"NLDSC_FP4": "0", "NLDSC_CHUNK_ROWS": "128", "NLDSC_PLANE_BYTES": "ring"},
     {"NLDSC_FP4": "0", "NLDSC_MFREE": "0"},
+    {"NLDSC_X160": "1"},                               # the 160-column supertiles (default only from N = 4,096)
+    {"NLDSC_X160": "1", "NLDSC_CHUNK_ROWS": "128", "NLDSC_PLANE_BYTES": "ring"},
+    {"NLDSC_X160": "1", "NLDSC_TEST_SHARDS": "3", "NLDSC_MFREE": "0"},
 ]
 
 
@@ -114,6 +117,8 @@ MID_VARIANTS = [
     {"NLDSC_MFREE": "0"},
     {"NLDSC_FP4": "0"},
     {"NLDSC_FP4": "0", "NLDSC_CHUNK_ROWS": "1024", "NLDSC_PLANE_BYTES": "ring"},
+    {"NLDSC_X160": "1"},
+    {"NLDSC_X160": "1", "NLDSC_CHUNK_ROWS": "1024", "NLDSC_PLANE_BYTES": "ring"},
 ]
 
 

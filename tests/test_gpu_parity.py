@@ -349,6 +349,62 @@ def _session_stats(g, **env):
         return out, s.stats()
 
 
+def test_x160_body_equals_wide_body_bitwise(monkeypatch):
+    """band_x160_body (one i-pair x five 32-SNP column groups, two mxf4 MMAs of N = 256 + 224 per 64 organisms; the default
+    for the 6-plane work from N = 4,096) writes the same partial sums, group by group, as the 2 x 2-block supertiles:
+    bit-equal scores, oracle bar met -- on ragged ends, a wrapping ring, shards, and beside missing-free chunks."""
+    g = _case(1003, 3000, 0.03, seed=29, wind=0.7)
+    monkeypatch.setenv("NLDSC_X160", "0")
+    wide, stw = _session_stats(g)
+    assert stw["xtiles"] == 0 and stw["xtiles_run"] == 0
+    monkeypatch.setenv("NLDSC_X160", "1")
+    x, stx = _session_stats(g)
+    assert stx["xtiles_run"] == stx["xtiles"] > 0
+    assert_ld_close(x, _oracle(g), label="x160")
+    for k in RESULT_KEYS:
+        assert np.array_equal(x[k], wide[k], equal_nan=True), k
+    # the default picks it by N
+    monkeypatch.delenv("NLDSC_X160")
+    big = _case(4100, 700, 0.02, seed=30)
+    d, std_ = _session_stats(big)
+    assert std_["xtiles_run"] > 0
+    assert_ld_close(d, _oracle(big), label="x160 default")
+    monkeypatch.setenv("NLDSC_X160", "0")
+    w = _run(big)
+    for k in RESULT_KEYS:
+        assert np.array_equal(d[k], w[k], equal_nan=True), k
+    # ragged ends, tiny shards, a wrapping ring, several shards
+    for n_snp, env in ((65, {"NLDSC_CHUNK_ROWS": "64"}), (129, {"NLDSC_CHUNK_ROWS": "64"}), (333, {"NLDSC_CHUNK_ROWS": "128"}),
+                       (961, {"NLDSC_CHUNK_ROWS": "192"}), (2100, {"NLDSC_TEST_SHARDS": "3"}), (1500, {"NLDSC_OVERLAP": "0"})):
+        h = _case(517, n_snp, 0.02, seed=60 + n_snp, wind=0.3)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        monkeypatch.setenv("NLDSC_X160", "1")
+        a = _run(h)
+        assert_ld_close(a, _oracle(h), label=f"x160 ragged {n_snp}")
+        monkeypatch.setenv("NLDSC_X160", "0")
+        b = _run(h)
+        for k in RESULT_KEYS:
+            assert np.array_equal(a[k], b[k], equal_nan=True), (n_snp, k)
+        for k in env:
+            monkeypatch.delenv(k)
+    # missing genotypes in SNPs 1,400-1,500 only: missing-free chunks take the 2-plane body, the others the 160-column one
+    m = _case(1003, 3000, 0.0, seed=23, wind=0.7)
+    codes = ld_oracle.decode_bed_msb_first(m["packed"], 1003).copy()
+    rng = np.random.default_rng(5)
+    codes[1400:1500][rng.random((100, 1003)) < 0.03] = 1
+    mixed = dict(m, packed=synth.pack_codes(codes))
+    monkeypatch.setenv("NLDSC_CHUNK_ROWS", "256")
+    monkeypatch.setenv("NLDSC_X160", "1")
+    a, sta = _session_stats(mixed)
+    assert 0 < sta["mfree_chunks"] < sta["chunks"] and 0 < sta["xtiles_run"] < sta["xtiles"], sta
+    assert_ld_close(a, _oracle(mixed), label="x160 mixed")
+    monkeypatch.setenv("NLDSC_X160", "0")
+    b = _run(mixed)
+    for k in RESULT_KEYS:
+        assert np.array_equal(a[k], b[k], equal_nan=True), k
+
+
 def test_missing_free_kernel_equals_six_plane_bitwise(monkeypatch):
     """band_tc_mfree_kernel (g x {h, a}: the reference's own two dot products, tools.h:87-92) takes the chunks whose
     columns hold no missing genotype; it must give the bits the 6-plane kernels give (NLDSC_MFREE=0), meet the oracle
