@@ -625,7 +625,7 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     // the 16 bytes of slack the word-wise kernels may read past the last row
     CUDA_CHECK(cudaMemsetAsync(s->d_packed + static_cast<size_t>(s->n_load) * s->bps, 0, 16, s->copy_stream));
     // upload granularity: ~8 MB pieces, a whole number of 64-row blocks each
-    const int64_t rows8 = (int64_t(8) << 20) / s->bps;
+    const int64_t rows8 = static_cast<int64_t>(env_size("NLDSC_PIECE_BYTES", size_t(8) << 20)) / s->bps;
     s->piece_rows = static_cast<int32_t>(std::max<int64_t>(kBlk, rows8 / kBlk * kBlk));
     s->ev_piece.resize((s->n_load + s->piece_rows - 1) / s->piece_rows);
     for (auto& e : s->ev_piece) e = ev_get(device, false);
