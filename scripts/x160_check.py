@@ -40,6 +40,8 @@ def run(packed, n_org, cm, wind, env):
             os.environ.pop(k, None)
 
 
+# the variant under test: X160_CHECK_ENV="NLDSC_X160=1,NLDSC_X80=1" for the two-halves body
+FORCE = dict(kv.split("=", 1) for kv in os.environ.get("X160_CHECK_ENV", "NLDSC_X160=1").split(","))
 bad = 0
 for n_org, n_snp, missing, wind, density, extra in CASES:
     spec = synth.SynthSpec(n_org=n_org, n_snp=n_snp, missing=missing, seed=n_org + n_snp, density=density)
@@ -50,8 +52,8 @@ for n_org, n_snp, missing, wind, density, extra in CASES:
         lo, hi = capi.plan_windows(cm, wind)
         rows = ((int(np.max(hi - lo)) + 1) // 64 + 6) * 64
         env["NLDSC_PLANE_BYTES"] = str(rows * 4 * ((n_org + 255) // 256 * 128))
-    base, st0 = run(packed, n_org, cm, wind, env)
-    got, st1 = run(packed, n_org, cm, wind, dict(env, NLDSC_X160="1"))
+    base, st0 = run(packed, n_org, cm, wind, dict(env, NLDSC_X160="0"))
+    got, st1 = run(packed, n_org, cm, wind, dict(env, **FORCE))
     diffs = {k: int(np.sum(~((got[k] == base[k]) | (np.isnan(got[k].astype(float)) & np.isnan(base[k].astype(float)))))) for k in KEYS}
     ok = all(v == 0 for v in diffs.values())
     bad += 0 if ok else 1
