@@ -164,17 +164,6 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
           "r"(c0), "r"(c1), "r"(c2)
         : "memory");
 }
-// The same for a 4-D box {128 B, r rows, planes, groups of r rows}: ONE operation stages what several 3-D boxes would
-// ([group][plane][row] in shared memory) -- the producer thread issues one bulk-tensor instruction every ~60 ns at best.
-__device__ __forceinline__ void tma_load_4d(void* dst, const CUtensorMap* map, uint64_t* bar,
-                                            int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
-        " [%0], [%1, {%3, %4, %5, %6}], [%2];"
-        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & kPeerMask),
-          "r"(c0), "r"(c1), "r"(c2), "r"(c3)
-        : "memory");
-}
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -1017,8 +1006,7 @@ __device__ __forceinline__ void hand_bar_sync(int q) {
     }
 }
 
-__device__ __forceinline__ void band_x160_body(const CUtensorMap& map_a4, const CUtensorMap& map_b16, const CUtensorMap& map_b16x5,
-                                               const BandArgs& args) {
+__device__ __forceinline__ void band_x160_body(const CUtensorMap& map_a, const CUtensorMap& map_b16, const BandArgs& args) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + kXStages * kXStageBytes);   // leader CTA only
@@ -1037,8 +1025,8 @@ __device__ __forceinline__ void band_x160_body(const CUtensorMap& map_a4, const 
     const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
 
     if (warp == 0 && lane == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a4)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b16x5)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b16)) : "memory");
         for (int s = 0; s < kXStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         mbar_init(tfull, 1);
         mbar_init(tempty, 16);                 // 8 epilogue warps x 2 CTAs
@@ -1067,23 +1055,21 @@ __device__ __forceinline__ void band_x160_body(const CUtensorMap& map_a4, const 
             for (int t = pair; t < args.n_xtiles; t += n_pairs) {
                 const XTile tl = args.xtiles[t];
                 const int32_t a_row = tl.a_row[rank];
-                // the five sixteens are ONE 4-D box unless they straddle the ring's wrap (then five 3-D boxes)
-                const int32_t b_row0 = (tl.j0 + 80 * static_cast<int32_t>(rank)) % args.ring_rows;
-                const bool wraps = b_row0 + 80 > args.ring_rows;
+                int32_t b_row[5];
+#pragma unroll
+                for (int u = 0; u < 5; ++u) b_row[u] = (tl.j0 + 80 * static_cast<int32_t>(rank) + 16 * u) % args.ring_rows;
                 const uint32_t bytes = 2u * kXStageBytes;                                    // both CTAs' bytes
                 for (int k = 0; k < args.k_steps; ++k) {
                     mbar_wait(&empty[stage], phase ^ 1, 15);
                     if (rank == 0) mbar_expect_tx(&full[stage], bytes);
                     uint8_t* sa = smem + stage * kXStageBytes;
                     uint8_t* sb = sa + kABytes;
-                    tma_load_4d(sa, &map_a4, &full[stage], k * kKStep, 0, kPlaneG, a_row >> 4);
-                    if (!wraps) {
-                        tma_load_4d(sb, &map_b16x5, &full[stage], k * kKStep, 0, kPlaneM, b_row0 >> 4);
-                    } else {
-#pragma unroll 1
-                        for (int u = 0; u < 5; ++u)
-                            tma_load_3d(sb + u * kXBoxBytes, &map_b16, &full[stage], k * kKStep, (b_row0 + 16 * u) % args.ring_rows, kPlaneM);
-                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        tma_load_3d(sa + u * 4096, &map_a, &full[stage], k * kKStep, a_row + 16 * u, kPlaneG);
+#pragma unroll
+                    for (int u = 0; u < 5; ++u)
+                        tma_load_3d(sb + u * kXBoxBytes, &map_b16, &full[stage], k * kKStep, b_row[u], kPlaneM);
                     if (++stage == kXStages) { stage = 0; phase ^= 1; }
                 }
             }
@@ -1245,249 +1231,6 @@ __device__ __forceinline__ void band_x160_body(const CUtensorMap& map_a4, const 
     }
 }
 
-// ---- the same 160-column supertiles as two 80-SNP halves with a double-buffered accumulator (fp4 planes only) --------
-// band_x160_body's accumulator is one 480-column piece, so its whole epilogue is exposed.  Here the two halves of an XTile
-// (j-SNPs 0..79 and 80..159) are multiplied one after the other, each by ONE MMA of N = 240 per 64 organisms into its own 240
-// TMEM columns (0..239 / 240..479; scale factors in 480..511): the epilogue of a half runs under the MMAs of the next.  The
-// price is the A block, staged once per half instead of once per supertile (31 KB per 4 MMAs instead of 46 KB per 8), which
-// is why this body is for the N where the exposed epilogue costs more than the operand traffic.  A half whose groups all lie
-// outside the i-pair's range (n_grp <= 2: the last supertile of a range) is not multiplied at all.
-// B layout: each CTA stages the 40 j-SNPs of its rank as five 8-SNP boxes [m8 h8 a8] (120 rows); B row r of rank c is
-// accumulator column 120 c + r, so the m / h / a counts of sixteen k (two boxes) are two runs of 8 columns each.
-// Epilogue: warp group 0 scores sixteens 0, 1 and 4 of half 0 and 5, 6, 7 of half 1; warp group 1 scores 2, 3 and 8, 9.  A
-// partial sum is closed after every odd sixteen, so group 2 (sixteens 4 and 5) simply stays in warp group 0's registers from one
-// half to the next: the same groups, the same order, the same bits as every other body.
-namespace {
-constexpr int kHStages = 6;
-constexpr int kHBRows = 120;                                 // per CTA: 5 eights x {m, h, a}
-constexpr int kHBoxBytes = 24 * kKStep;                      // one eight: 3 KB
-constexpr int kHBBytes = kHBRows * kKStep;                   // 15 KB
-constexpr int kHStageBytes = kABytes + kHBBytes;             // 31 KB per CTA per stage
-constexpr int kHSmemBytes = kHStages * kHStageBytes + 1024 + 256 + kXColBytes;
-constexpr uint32_t kHAccCols = 240;
-static_assert(kHStageBytes % 1024 == 0 && kHBoxBytes % 1024 == 0, "swizzle atoms stay aligned");
-}  // namespace
-
-__device__ __forceinline__ void tmem_ld8(uint32_t taddr, int32_t* v) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
-                 : "r"(taddr));
-}
-
-__device__ __forceinline__ void band_x80_body(const CUtensorMap& map_a4, const CUtensorMap& map_b8, const CUtensorMap& map_b8x5,
-                                              const BandArgs& args) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + kHStages * kHStageBytes);   // leader CTA only
-    uint64_t* empty = full + kHStages;         // one per CTA
-    uint64_t* tfull = empty + kHStages;        // one per CTA and accumulator
-    uint64_t* tempty = tfull + 2;              // leader CTA only, one per accumulator
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-    double2* col_coef = reinterpret_cast<double2*>(smem + kHStages * kHStageBytes + 256);
-    uint8_t* col_flags = reinterpret_cast<uint8_t*>(col_coef) + kXSnps * sizeof(SnpCoef);
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t rank = cluster_ctarank();
-    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
-
-    if (warp == 0 && lane == 0) {
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_a4)) : "memory");
-        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&map_b8x5)) : "memory");
-        for (int s = 0; s < kHStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&tfull[b], 1); mbar_init(&tempty[b], 16); }   // 8 epilogue warps x 2 CTAs
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 1) {
-        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                     "r"((uint32_t)kTmemCols)
-                     : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-    }
-    tc_fence_before();
-    cluster_sync_all();
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-    if (warp >= 2 && warp < 6) tmem_fill_sf_ones(tmem_base, warp, kXSfCols);
-    tc_fence_before();
-    cluster_sync_all();
-    tc_fence_after();
-
-    if (warp == 0) {
-        // ===== TMA producer: per half, own A block + the five eights of the own 40 j-SNPs =====
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int t = pair; t < args.n_xtiles; t += n_pairs) {
-                const XTile tl = args.xtiles[t];
-                const int32_t a_row = tl.a_row[rank];
-                const int n_half = tl.n_grp > 2 ? 2 : 1;
-                for (int h = 0; h < n_half; ++h) {
-                    // the five eights are ONE 4-D box unless they straddle the ring's wrap (then five 3-D boxes)
-                    const int32_t b_row0 = (tl.j0 + 80 * h + 40 * static_cast<int32_t>(rank)) % args.ring_rows;
-                    const bool wraps = b_row0 + 40 > args.ring_rows;
-                    for (int k = 0; k < args.k_steps; ++k) {
-                        mbar_wait(&empty[stage], phase ^ 1, 19);
-                        if (rank == 0) mbar_expect_tx(&full[stage], 2u * kHStageBytes);          // both CTAs' bytes
-                        uint8_t* sa = smem + stage * kHStageBytes;
-                        uint8_t* sb = sa + kABytes;
-                        tma_load_4d(sa, &map_a4, &full[stage], k * kKStep, 0, kPlaneG, a_row >> 4);
-                        if (!wraps) {
-                            tma_load_4d(sb, &map_b8x5, &full[stage], k * kKStep, 0, kPlaneM, b_row0 >> 3);
-                        } else {
-#pragma unroll 1
-                            for (int u = 0; u < 5; ++u)
-                                tma_load_3d(sb + u * kHBoxBytes, &map_b8, &full[stage], k * kKStep, (b_row0 + 8 * u) % args.ring_rows, kPlaneM);
-                        }
-                        if (++stage == kHStages) { stage = 0; phase ^= 1; }
-                    }
-                }
-            }
-        }
-        __syncwarp();
-    } else if (warp == 1) {
-        // ===== MMA issuer (leader CTA only): halves alternate between the two accumulators =====
-        if (rank == 0 && lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            uint32_t hn = 0;                                          // halves issued so far
-            const uint32_t sf = tmem_base + kXSfCols;
-            for (int t = pair; t < args.n_xtiles; t += n_pairs) {
-                const int n_half = args.xtiles[t].n_grp > 2 ? 2 : 1;
-                for (int h = 0; h < n_half; ++h, ++hn) {
-                    const uint32_t buf = hn & 1;
-                    mbar_wait(&tempty[buf], ((hn >> 1) & 1) ^ 1, 20);  // both CTAs' epilogues drained this accumulator
-                    tc_fence_after();
-                    const uint32_t d = tmem_base + kHAccCols * buf;
-                    for (int k = 0; k < args.k_steps; ++k) {
-                        mbar_wait(&full[stage], phase, 21);
-                        tc_fence_after();
-                        const uint32_t sa = smem_u32(smem + stage * kHStageBytes);
-                        const uint64_t a_desc = make_smem_desc(sa);
-                        const uint64_t b_desc = make_smem_desc(sa + kABytes);
-#pragma unroll
-                        for (int kk = 0; kk < kKStep / 32; ++kk)
-                            tc_mma_mxf4(d, a_desc + 2 * kk, b_desc + 2 * kk, idesc_mxf4(kHAccCols), sf, sf + 16, (k | kk) != 0);
-                        tc_commit_pair(&empty[stage]);
-                        if (++stage == kHStages) { stage = 0; phase ^= 1; }
-                    }
-                    tc_commit_pair(&tfull[buf]);
-                }
-            }
-        }
-        __syncwarp();
-    } else {
-        // ===== epilogue: eight warps per CTA; q = TMEM lane quarter, wg = warp group =====
-        const int q = warp & 3;
-        const int wg = (warp - 2) >> 2;
-        const bool is_g = lane < 16;
-        const int s = 16 * q + (lane & 15);
-        uint32_t hn = 0;
-        for (int t = pair; t < args.n_xtiles; t += n_pairs) {
-            const XTile tl = args.xtiles[t];
-            const int32_t i0 = tl.i0[rank];
-            const int n_half = tl.n_grp > 2 ? 2 : 1;
-            const RowCtx row = load_row_ctx(args, i0 + s);
-            // the constants of the supertile's 160 j-SNPs, staged while the MMAs of its first half run
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            {
-                const int te = threadIdx.x - 64;                       // 0..255 among the epilogue threads
-                for (int e = te; e < kXSnps * 4; e += 256) {           // 4 double2 per SNP
-                    const int32_t gj = tl.j0 + (e >> 2);
-                    double2 v = make_double2(0.0, 0.0);
-                    if (gj < args.n_load) v = __ldg(reinterpret_cast<const double2*>(args.coef + gj) + (e & 3));
-                    col_coef[e] = v;
-                }
-                if (te < kXSnps) {
-                    const int32_t gj = tl.j0 + te;
-                    col_flags[te] = gj < args.n_load ? __ldg(args.flags + gj) : uint8_t(0);
-                }
-            }
-            asm volatile("bar.sync 1, 256;" ::: "memory");
-            RowAcc acc;                                                // a group's running sums; group 2 crosses the halves (warp group 0)
-#pragma unroll 1
-            for (int h = 0; h < n_half; ++h, ++hn) {
-                const uint32_t buf = hn & 1;
-                mbar_wait_idle(&tfull[buf], (hn >> 1) & 1, 22);
-                tc_fence_after();
-                const uint32_t taddr = tmem_base + kHAccCols * buf + (static_cast<uint32_t>(32 * q) << 16);
-                const int n_six = wg == 0 ? 3 : 2;
-#pragma unroll 1
-                for (int i = 0; i < n_six; ++i) {
-                    // sixteen k of the supertile = sixteen kh of this half = eights 2 kh, 2 kh + 1 of its ten
-                    const int kh = wg == 0 ? (h == 0 ? (i < 2 ? i : 4) : i) : (h == 0 ? 2 + i : 3 + i);
-                    const int k = 5 * h + kh;
-                    const int grp = k >> 1;
-                    const int32_t jk = tl.j0 + 16 * k;
-                    if (grp < tl.n_grp && (args.no_skip || __any_sync(0xFFFFFFFFu, row_needs(row, jk, jk + 15)))) {
-                        int32_t vm[16], vh[16], va[16];
-                        {
-                            const int b0 = 2 * kh, b1 = 2 * kh + 1;
-                            const uint32_t c0 = 120 * (b0 >= 5 ? 1 : 0) + 24 * (b0 >= 5 ? b0 - 5 : b0);
-                            const uint32_t c1 = 120 * (b1 >= 5 ? 1 : 0) + 24 * (b1 >= 5 ? b1 - 5 : b1);
-                            tmem_ld8(taddr + c0, vm);
-                            tmem_ld8(taddr + c1, vm + 8);
-                            tmem_ld8(taddr + c0 + 8, vh);
-                            tmem_ld8(taddr + c1 + 8, vh + 8);
-                            tmem_ld8(taddr + c0 + 16, va);
-                            tmem_ld8(taddr + c1 + 16, va + 8);
-                            tmem_ld_wait();
-                        }
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) {
-                            // FP32 bit patterns of exact counts, converted to double pair by pair (cnt2d<true>)
-                            const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
-                            const int32_t sh_ = is_g ? vh[2 * u + 1] : vh[2 * u];
-                            const int32_t sa_ = is_g ? va[2 * u + 1] : va[2 * u];
-                            const int32_t rm = __shfl_xor_sync(0xFFFFFFFFu, sm_, 16);
-                            const int32_t rh = __shfl_xor_sync(0xFFFFFFFFu, sh_, 16);
-                            const int32_t ra = __shfl_xor_sync(0xFFFFFFFFu, sa_, 16);
-                            const int jl = 16 * k + 2 * u + (is_g ? 0 : 1);
-                            const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
-                            const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
-                            const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
-                            const double2* cj = col_coef + 4 * jl;
-                            pair_eval_core<true>(args, row, tl.j0 + jl, col_flags[jl], cj[0], cj[1], cj[2], cj[3],
-                                                 Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
-                        }
-                    }
-                    if (i == n_six - 1) {
-                        // the last TMEM read of this half is behind this warp: hand the accumulator back
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive_leader(&tempty[buf]);
-                    }
-                    if (!(k & 1)) continue;                            // an even sixteen: its group goes on (4 -> 5: in the next half)
-                    if (grp < tl.n_grp) {
-                        acc.add += __shfl_xor_sync(0xFFFFFFFFu, acc.add, 16);
-                        acc.dom += __shfl_xor_sync(0xFFFFFFFFu, acc.dom, 16);
-                        acc.wsa += __shfl_xor_sync(0xFFFFFFFFu, acc.wsa, 16);
-                        acc.wsd += __shfl_xor_sync(0xFFFFFFFFu, acc.wsd, 16);
-                        acc.wsde += __shfl_xor_sync(0xFFFFFFFFu, acc.wsde, 16);
-                        if (is_g) {
-                            const int gg = tl.odd + grp;
-                            const int64_t o = part_index(tl.slot + (gg >> 1), static_cast<int>(rank), gg & 1, s);
-                            args.part.add[o] = acc.add;
-                            args.part.dom[o] = acc.dom;
-                            args.part.wsa[o] = acc.wsa;
-                            args.part.wsd[o] = acc.wsd;
-                            args.part.wsde[o] = acc.wsde;
-                        }
-                    }
-                    acc = RowAcc();
-                }
-            }
-        }
-    }
-
-    tc_fence_before();
-    cluster_sync_all();
-    if (warp == 1) {
-        tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)kTmemCols)
-                     : "memory");
-    }
-}
-
 // ONE launch per chunk for both paths: the chunk's flag (written on the device after its stats) picks the body.
 // (Two kernels, one of them returning at once, cost configs[1] 12 %: the idle launch still has to wait for a whole
 // grid's worth of free SMs behind the other stream's persistent band kernel -- profiles/r02i_ab_missing_n10000.json.)
@@ -1506,22 +1249,11 @@ band_tc_wide_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 // The same launch with the 160-column body for the 6-plane work (fp4 planes).  A kernel of its own so that the register
 // allocation of the kernel above stays what it was.
 __global__ void __cluster_dims__(2, 1, 1) __maxnreg__(NLDSC_WIDE_MAXNREG)
-band_tc_x160_kernel(const __grid_constant__ CUtensorMap map_a4, const __grid_constant__ CUtensorMap map_b16,
-                    const __grid_constant__ CUtensorMap map_b16x5, const __grid_constant__ CUtensorMap map_g,
-                    const __grid_constant__ CUtensorMap map_ha, const BandArgs args) {
+band_tc_x160_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b16,
+                    const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_ha, const BandArgs args) {
     const bool mfree = args.mfree_flag != nullptr && *reinterpret_cast<const volatile uint32_t*>(args.mfree_flag) != 0;
     if (mfree) band_mfree_body(map_g, map_ha, args);
-    else band_x160_body(map_a4, map_b16, map_b16x5, args);
-}
-
-// ... and with the two-halves body (double-buffered accumulator)
-__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(NLDSC_WIDE_MAXNREG)
-band_tc_x80_kernel(const __grid_constant__ CUtensorMap map_a4, const __grid_constant__ CUtensorMap map_b8,
-                   const __grid_constant__ CUtensorMap map_b8x5, const __grid_constant__ CUtensorMap map_g,
-                   const __grid_constant__ CUtensorMap map_ha, const BandArgs args) {
-    const bool mfree = args.mfree_flag != nullptr && *reinterpret_cast<const volatile uint32_t*>(args.mfree_flag) != 0;
-    if (mfree) band_mfree_body(map_g, map_ha, args);
-    else band_x80_body(map_a4, map_b8, map_b8x5, args);
+    else band_x160_body(map_a, map_b16, args);
 }
 
 // ---- host side: TMA descriptors + launch ------------------------------------------------
@@ -1531,11 +1263,6 @@ struct BandMaps {
     CUtensorMap g;   // box {128 B, 64 rows, 1 plane}    missing-free kernel: g of one i-block
     CUtensorMap ha;  // box {128 B, 64 rows, 2 planes}   missing-free kernel: [h ; a] of one j-block
     CUtensorMap b16; // box {128 B, 16 rows, 3 planes}   160-column supertiles: [m ; h ; a] of one sixteen
-    CUtensorMap b8;  // box {128 B, 8 rows, 3 planes}    ... in two halves: [m ; h ; a] of one eight
-    // 4-D views {bytes, row within a group of r, plane, group}: one box stages several of the 3-D boxes above at once
-    CUtensorMap a4;     // r = 16, box {128 B, 16, 2 planes, 4 groups} = the A block of an i-block: 4 x [g16 m16]
-    CUtensorMap b16x5;  // r = 16, box {128 B, 16, 3 planes, 5 groups} = five sixteens [m16 h16 a16]
-    CUtensorMap b8x5;   // r = 8,  box {128 B, 8, 3 planes, 5 groups}  = five eights [m8 h8 a8]
 };
 
 namespace {
@@ -1571,22 +1298,6 @@ void encode(CUtensorMap* m, const int8_t* planes, int64_t plane_rows, int32_t np
         throw CudaError(buf);
     }
 }
-void encode4(CUtensorMap* m, const int8_t* planes, int64_t plane_rows, int32_t npad, uint32_t r, uint32_t box_planes,
-             uint32_t box_groups) {
-    const cuuint64_t dims[4] = {(cuuint64_t)npad, (cuuint64_t)r, (cuuint64_t)kPlanes, (cuuint64_t)(plane_rows / r)};
-    const cuuint64_t strides[3] = {(cuuint64_t)npad, (cuuint64_t)npad * (cuuint64_t)plane_rows, (cuuint64_t)npad * r};
-    const cuuint32_t box[4] = {(cuuint32_t)kKStep, r, box_planes, box_groups};
-    const cuuint32_t estr[4] = {1, 1, 1, 1};
-    const CUresult res = get_encode()(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, const_cast<int8_t*>(planes), dims, strides,
-                                      box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (res != CUDA_SUCCESS) {
-        char buf[160];
-        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled (4-D) failed (CUresult %d; rows %lld npad %d r %u)", (int)res,
-                 (long long)plane_rows, npad, r);
-        throw CudaError(buf);
-    }
-}
 }  // namespace
 
 BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npad) {
@@ -1597,10 +1308,6 @@ BandMaps* band_maps_create(const int8_t* planes, int64_t plane_rows, int32_t npa
         encode(&m->g, planes, plane_rows, npad, 64, 1);
         encode(&m->ha, planes, plane_rows, npad, 64, 2);
         encode(&m->b16, planes, plane_rows, npad, 16, 3);
-        encode(&m->b8, planes, plane_rows, npad, 8, 3);
-        encode4(&m->a4, planes, plane_rows, npad, 16, 2, 4);
-        encode4(&m->b16x5, planes, plane_rows, npad, 16, 3, 5);
-        encode4(&m->b8x5, planes, plane_rows, npad, 8, 3, 5);
     } catch (...) {
         delete m;
         throw;
@@ -1616,7 +1323,7 @@ std::mutex g_hang_mu;
 const char* const kSiteNames[] = {"?", "narrow/producer:empty", "narrow/mma:tmem-empty", "narrow/mma:full", "narrow/epilogue:tmem-full",
                                   "wide/producer:empty", "wide/mma:tmem-empty", "wide/mma:full", "wide/epilogue:tmem-full", "i8-peak",
                                   "rows-ready (the chunk's unpack never published)", "mfree/producer:empty", "mfree/mma:tmem-empty", "mfree/mma:full",
-                                  "mfree/epilogue:tmem-full", "x160/producer:empty", "x160/mma:tmem-empty", "x160/mma:full", "x160/epilogue:tmem-full", "x80/producer:empty", "x80/mma:tmem-empty", "x80/mma:full", "x80/epilogue:tmem-full"};
+                                  "mfree/epilogue:tmem-full", "x160/producer:empty", "x160/mma:tmem-empty", "x160/mma:full", "x160/epilogue:tmem-full"};
 void install_hang_word() {
     int dev = 0;
     CUDA_CHECK(cudaGetDevice(&dev));
@@ -1650,15 +1357,13 @@ std::string band_hang_note() {
 
 constexpr int kWideKernelSmem = kWSmemBytes > kMSmemBytes ? kWSmemBytes : kMSmemBytes;
 constexpr int kX160KernelSmem = kXSmemBytes > kMSmemBytes ? kXSmemBytes : kMSmemBytes;
-constexpr int kX80KernelSmem = kHSmemBytes > kMSmemBytes ? kHSmemBytes : kMSmemBytes;
-static_assert(kWideKernelSmem <= 232448 && kX160KernelSmem <= 232448 && kX80KernelSmem <= 232448, "dynamic shared memory of one CTA");
+static_assert(kWideKernelSmem <= 232448 && kX160KernelSmem <= 232448, "dynamic shared memory of one CTA");
 
 void install_band_kernels() {
     install_hang_word();
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideKernelSmem));
     CUDA_CHECK(cudaFuncSetAttribute(band_tc_x160_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kX160KernelSmem));
-    CUDA_CHECK(cudaFuncSetAttribute(band_tc_x80_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kX80KernelSmem));
 }
 
 void launch_band_tc(const BandMaps* maps, const BandArgs& args, int sm_count, cudaStream_t st) {
@@ -1679,15 +1384,9 @@ void launch_band_tc_wide(const BandMaps* maps, const BandArgs& args, int sm_coun
     if (n_max <= 0) return;
     install_hang_word();
     const int pairs = n_max < sm_count / 2 ? n_max : sm_count / 2;
-    if (x160 && args.x80) {
-        CUDA_CHECK(cudaFuncSetAttribute(band_tc_x80_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kX80KernelSmem));
-        band_tc_x80_kernel<<<2 * pairs, kWThreads, kX80KernelSmem, st>>>(maps->a4, maps->b8, maps->b8x5, maps->g, maps->ha, args);
-        CUDA_CHECK(cudaGetLastError());
-        return;
-    }
     if (x160) {
         CUDA_CHECK(cudaFuncSetAttribute(band_tc_x160_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kX160KernelSmem));
-        band_tc_x160_kernel<<<2 * pairs, kWThreads, kX160KernelSmem, st>>>(maps->a4, maps->b16, maps->b16x5, maps->g, maps->ha, args);
+        band_tc_x160_kernel<<<2 * pairs, kWThreads, kX160KernelSmem, st>>>(maps->a, maps->b16, maps->g, maps->ha, args);
         CUDA_CHECK(cudaGetLastError());
         return;
     }

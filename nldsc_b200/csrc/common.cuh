@@ -113,7 +113,6 @@ struct BandArgs {
                                 // per-SNP statistics final; published after every chunk's unpack + stats.  null = everything is ready
     const XTile* xtiles;        // 160-column supertiles of the same chunk (band_x160_body; fp4 planes only), same slots; null = off
     int32_t n_xtiles;
-    int32_t x80;                // score the xtiles as two 80-SNP halves with a double-buffered accumulator (band_x80_body)
     int32_t ring_rows;          // rows of the plane ring (a multiple of 64): ring row of SNP j = j % ring_rows
     int32_t fp4;                // the planes hold e2m1 nibbles (launch_unpack_fp4): the wide / missing-free bodies multiply them with
                                 // tcgen05.mma.kind::mxf4 (scale factors 1.0, K = 64 per MMA, k_steps = plane row bytes / 128)

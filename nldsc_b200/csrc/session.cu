@@ -608,9 +608,6 @@ static nldsc_ld_session* session_open(int device, const nldsc_ld_params* p, int3
     // window -13 %.  Default from N = 4,096 (where the chunks shrink to 8,192 rows); NLDSC_X160=0 / 1 forces.
     const char* x16 = getenv("NLDSC_X160");
     s->x160 = s->fp4 && (x16 ? x16[0] == '1' : p->n_org >= 4096);
-    // ... scored as two 80-SNP halves with a double-buffered accumulator (the epilogue hides; the A block is staged twice)
-    const char* x8 = getenv("NLDSC_X80");
-    s->x80 = s->x160 && (x8 && x8[0] == '1');
     if (s->fp4)      // plane row BYTES: a whole number of 128-byte pipeline stages = 256 organisms each
         s->npad = static_cast<int32_t>(((static_cast<int64_t>(p->n_org) + 2 * kKAlign - 1) / (2 * kKAlign)) * kKAlign);
     s->load_begin = load_begin;
@@ -1409,7 +1406,6 @@ static void session_run(nldsc_ld_session* s, cudaStream_t st_in) {
         if (s->x160 && s->wide && !s->use_simt && c.n_xtiles > 0) {
             a.xtiles = s->d_xtiles + c.xtile0;
             a.n_xtiles = c.n_xtiles;
-            a.x80 = s->x80 ? 1 : 0;
         }
         {
             SpanScope sc(s, bs, kFamBand);

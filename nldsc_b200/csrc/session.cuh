@@ -107,7 +107,6 @@ struct nldsc_ld_session {
     int64_t total_qtiles = 0;
     bool fp4 = false;                         // planes hold e2m1 nibbles; npad = plane row BYTES = organisms / 2, padded to 128
     bool x160 = false;                        // fp4 planes: chunks with missing genotypes take the 160-column supertiles (band_x160_body)
-    bool x80 = false;                         // ... as two 80-SNP halves, accumulator double-buffered (band_x80_body)
     nldsc::XTile* d_xtiles = nullptr;
     std::vector<nldsc::XTile> h_xtiles;
     bool fused_ok = false;                    // the plan allows ONE band launch per shard (session_plan); run() decides
