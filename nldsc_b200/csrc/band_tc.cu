@@ -255,6 +255,14 @@ __device__ __forceinline__ void acc_to_int(int32_t (&v)[16]) {
 #pragma unroll
     for (int e = 0; e < 16; ++e) v[e] = acc_f2i(v[e]);
 }
+// `g_lane ? a : b` in ONE instruction: PRMT with a per-lane selector (0x3210 picks a, 0x7654 picks b).  Written as a ternary
+// the compiler emits a move and a predicated move, and the 6-plane epilogues -- bound by instruction issue -- do nine of these
+// per SNP pair (which three counts go to the partner lane, and which of own / received is the g row and which the m row).
+// Used by the 160-column body only (-1.2 % per step at N=10,000); the 2 x 2-block body at N=2,504 was 1 % SLOWER with it
+// (profiles/r02zk_ab_prmt_*.json), so the bodies that serve small N keep the ternaries.
+__device__ __forceinline__ int32_t pick(uint32_t lane_sel, int32_t a, int32_t b) {
+    return static_cast<int32_t>(__byte_perm(static_cast<uint32_t>(a), static_cast<uint32_t>(b), lane_sel));
+}
 // instruction descriptor, block-scaled (cute/arch/mma_sm100_desc.hpp InstrDescriptorBlockScaled): A / B = e2m1 (1 at bits
 // 7 and 10), both K-major, N >> 3 at bit 17, scale format E8M0 (bit 23), M >> 4 at bit 24, K = 64 (bit 31 = 0)
 __device__ __forceinline__ constexpr uint32_t idesc_mxf4(uint32_t n_cols) {
@@ -1110,6 +1118,7 @@ __device__ __forceinline__ void band_x160_body(const CUtensorMap& map_a, const C
         const int q = warp & 3;
         const int wg = (warp - 2) >> 2;
         const bool is_g = lane < 16;
+        const uint32_t psel = is_g ? 0x3210u : 0x7654u;      // pick(): g lanes take the first argument, m lanes the second
         const int s = 16 * q + (lane & 15);
         const int hl = 32 * q + lane;                                 // handover slot of this lane
         int n = 0;
@@ -1168,16 +1177,16 @@ __device__ __forceinline__ void band_x160_body(const CUtensorMap& map_a, const C
 #pragma unroll
                     for (int u = 0; u < 8; ++u) {
                         // FP32 bit patterns of exact counts, converted to double pair by pair (cnt2d<true>)
-                        const int32_t sm_ = is_g ? vm[2 * u + 1] : vm[2 * u];
-                        const int32_t sh_ = is_g ? vh[2 * u + 1] : vh[2 * u];
-                        const int32_t sa_ = is_g ? va[2 * u + 1] : va[2 * u];
+                        const int32_t sm_ = pick(psel, vm[2 * u + 1], vm[2 * u]);
+                        const int32_t sh_ = pick(psel, vh[2 * u + 1], vh[2 * u]);
+                        const int32_t sa_ = pick(psel, va[2 * u + 1], va[2 * u]);
                         const int32_t rm = __shfl_xor_sync(0xFFFFFFFFu, sm_, 16);
                         const int32_t rh = __shfl_xor_sync(0xFFFFFFFFu, sh_, 16);
                         const int32_t ra = __shfl_xor_sync(0xFFFFFFFFu, sa_, 16);
                         const int jl = 16 * k + 2 * u + (is_g ? 0 : 1);
-                        const int32_t Ggm = is_g ? vm[2 * u] : rm, Gmm = is_g ? rm : vm[2 * u + 1];
-                        const int32_t Ggh = is_g ? vh[2 * u] : rh, Gmh = is_g ? rh : vh[2 * u + 1];
-                        const int32_t Gga = is_g ? va[2 * u] : ra, Gma = is_g ? ra : va[2 * u + 1];
+                        const int32_t Ggm = pick(psel, vm[2 * u], rm), Gmm = pick(psel, rm, vm[2 * u + 1]);
+                        const int32_t Ggh = pick(psel, vh[2 * u], rh), Gmh = pick(psel, rh, vh[2 * u + 1]);
+                        const int32_t Gga = pick(psel, va[2 * u], ra), Gma = pick(psel, ra, va[2 * u + 1]);
                         const double2* cj = col_coef + 4 * jl;
                         pair_eval_core<true>(args, row, tl.j0 + jl, col_flags[jl], cj[0], cj[1], cj[2], cj[3],
                                              Ggm, Ggh, Gga, Gmm, Gmh, Gma, acc);
