@@ -40,7 +40,7 @@ def run(packed, n_org, cm, wind, env):
             os.environ.pop(k, None)
 
 
-# the variant under test: X160_CHECK_ENV="NLDSC_X160=1,NLDSC_X80=1" for the two-halves body
+# the variant under test, as environment settings (X160_CHECK_ENV="NLDSC_X160=1,NLDSC_CHUNK_ROWS=256" ...)
 FORCE = dict(kv.split("=", 1) for kv in os.environ.get("X160_CHECK_ENV", "NLDSC_X160=1").split(","))
 bad = 0
 for n_org, n_snp, missing, wind, density, extra in CASES:
