@@ -209,6 +209,13 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
 /* nldsc_ld_plan_windows evaluated by the device kernel the calculate entry points use (plan.cu);
  * must equal the host routine element for element. */
 int nldsc_ld_debug_plan_windows_device(const nldsc_ld_params* params, int32_t* lo, int32_t* hi, char* err, size_t errlen);
+/* Host-only (no GPU needed): the 160-column supertiles session planning cuts for ONE chunk of `n_iblocks` consecutive 64-SNP
+ * i-blocks whose j-ranges are the 64-SNP blocks [jb_lo[k], jb_hi[k]] (non-decreasing), in the kernel's execution order with
+ * raster groups of `raster` i-pairs.  tiles_out = int32 [max_tiles][8] = a_row[2], i0[2], j0, slot, n_grp, odd per tile (the XTile of
+ * csrc/common.cuh; slots numbered i-pair-major, one per j-block of a pair's range); n_tiles = how many there are (also when it
+ * exceeds max_tiles).  Lets the CPU suite check that every 32-SNP column group of every i-pair is scored exactly once. */
+int nldsc_ld_debug_plan_xtiles(const int32_t* jb_lo, const int32_t* jb_hi, int32_t n_iblocks, int32_t raster, int32_t* tiles_out,
+                               int32_t max_tiles, int32_t* n_tiles, char* err, size_t errlen);
 /* Measurement hook: runs the band kernel on `n_tiles` synthetic supertiles (2 x 64 x 64 SNP pairs each,
  * K = n_org, band-like operand reuse) `reps` times and returns the mean CUDA-event time of one launch.
  * mode 0 = the real kernel (TMA + MMA + epilogue), 1 = tcgen05 MMAs only (no operand loads: the int8

@@ -26,6 +26,7 @@ EXPORTS = [
     "nldsc_ld_calculate_on", "nldsc_ld_debug_i8_peak", "nldsc_ld_last_call_report", "nldsc_ld_arena_trim",
     "nldsc_ld_calculate_packed_on", "nldsc_ld_warmup", "nldsc_ld_debug_h2d_probe", "nldsc_ld_debug_fp4_probe",
     "nldsc_ld_debug_unpack_fp4", "nldsc_ld_report_device_times", "nldsc_ld_snp_stats_static",
+    "nldsc_ld_debug_plan_xtiles",
 ]
 STATIC_MAX_SNPS = 262144      # NLDSC_STATIC_MAX_SNPS of include/nldsc_ld.h
 
@@ -395,3 +396,17 @@ def snp_stats_static(d_packed: int, n_snp: int, n_org: int, maf: float, std_thr:
                                            C.c_double(std_thr), C.c_void_p(d_counts_out or None), C.c_void_p(d_maf_out),
                                            C.c_void_p(d_rstd_out), C.c_int32(device), C.c_void_p(stream or None), err,
                                            C.c_size_t(512)), err)
+
+
+def debug_plan_xtiles(jb_lo, jb_hi, raster: int = 8) -> np.ndarray:
+    """Host-only: the 160-column supertiles of one chunk -> int32 [n_tiles, 8] = a_row[2], i0[2], j0, slot, n_grp, odd."""
+    lo = np.ascontiguousarray(jb_lo, dtype=np.int32)
+    hi = np.ascontiguousarray(jb_hi, dtype=np.int32)
+    n = C.c_int32(0)
+    err = C.create_string_buffer(512)
+    _raise(lib().nldsc_ld_debug_plan_xtiles(_ip(lo), _ip(hi), C.c_int32(lo.size), C.c_int32(raster), None, C.c_int32(0),
+                                            C.byref(n), err, C.c_size_t(512)), err)
+    out = np.empty((n.value, 8), np.int32)
+    _raise(lib().nldsc_ld_debug_plan_xtiles(_ip(lo), _ip(hi), C.c_int32(lo.size), C.c_int32(raster), _ip(out), C.c_int32(n.value),
+                                            C.byref(n), err, C.c_size_t(512)), err)
+    return out

@@ -760,6 +760,40 @@ static void join_reader(nldsc_ld_session* s) {
     if (s->fd_direct >= 0) { close(s->fd_direct); s->fd_direct = -1; }
 }
 
+// The 160-column supertiles (XTile) of one chunk = i-blocks [b, e) of the shard's block list: every i-pair's j-range
+// [jb_lo[k], jb_hi[k+1]] (64-SNP blocks) is cut into runs of five 32-SNP groups from its own first column -- nothing is
+// aligned to more than 32 SNPs, so only the last run of an i-pair is partly outside its range (n_grp < 5).  Same partial-sum
+// slots as the 64-block tiles (slot0[p] = first slot of the chunk's p-th i-pair); executed in raster order: run m of `raster`
+// consecutive i-pairs side by side, so that concurrent CTA pairs share operand rows in L2.  Host-only (CPU-tested through
+// nldsc_ld_debug_plan_xtiles).
+static void plan_xtiles_chunk(const int32_t* jb_lo, const int32_t* jb_hi, int32_t b, int32_t e, int32_t ib0, int64_t cap,
+                              int32_t raster, const std::vector<int32_t>& slot0, std::vector<XTile>& out) {
+    for (int32_t g0 = b; g0 < e; g0 += 2 * raster) {
+        const int32_t g1 = std::min(e, g0 + 2 * raster);
+        bool any = true;
+        for (int32_t m = 0; any; ++m) {
+            any = false;
+            for (int32_t k = g0; k < g1; k += 2) {
+                const bool two = k + 1 < e;
+                const int32_t lo_k = jb_lo[k], hi_k = two ? jb_hi[k + 1] : jb_hi[k];
+                const int32_t n32 = 2 * (hi_k - lo_k + 1);
+                if (5 * m >= n32) continue;
+                any = true;
+                XTile t;
+                t.i0[0] = (ib0 + k) * kBlk;
+                t.i0[1] = two ? (ib0 + k + 1) * kBlk : kDeadBlock;
+                t.a_row[0] = static_cast<int32_t>(t.i0[0] % cap);
+                t.a_row[1] = two ? static_cast<int32_t>(t.i0[1] % cap) : t.a_row[0];
+                t.j0 = lo_k * kBlk + 160 * m;
+                t.slot = slot0[(k - b) / 2] + ((5 * m) >> 1);
+                t.n_grp = std::min(5, n32 - 5 * m);
+                t.odd = (5 * m) & 1;
+                out.push_back(t);
+            }
+        }
+    }
+}
+
 // Stage 2: windows -> owned i-blocks -> plane ring -> chunks and supertiles, and their device copies.
 // `ramp`: start with small chunks and double up to the regular size -- for the calculate* entry points,
 // where the upload runs concurrently and the first kernels should start after a few MB have landed.
@@ -1104,32 +1138,7 @@ static void session_plan(nldsc_ld_session* s, int32_t row_begin, int32_t row_end
         // groups from its own first column (nothing is aligned to more than 32 SNPs, so only the last run of an i-pair
         // is partly outside its range); same slots, same raster (run m of kRaster i-pairs side by side)
         c.xtile0 = static_cast<int64_t>(s->h_xtiles.size());
-        if (s->x160 && !s->fused_ok) {
-            for (int32_t g0 = b; g0 < e; g0 += 2 * kRaster) {
-                const int32_t g1 = std::min(e, g0 + 2 * kRaster);
-                bool any = true;
-                for (int32_t m = 0; any; ++m) {
-                    any = false;
-                    for (int32_t k = g0; k < g1; k += 2) {
-                        const bool two = k + 1 < e;
-                        const int32_t lo_k = jb_lo[k], hi_k = two ? jb_hi[k + 1] : jb_hi[k];
-                        const int32_t n32 = 2 * (hi_k - lo_k + 1);
-                        if (5 * m >= n32) continue;
-                        any = true;
-                        XTile t;
-                        t.i0[0] = (ib0 + k) * kBlk;
-                        t.i0[1] = two ? (ib0 + k + 1) * kBlk : kDeadBlock;
-                        t.a_row[0] = static_cast<int32_t>(t.i0[0] % cap);
-                        t.a_row[1] = two ? static_cast<int32_t>(t.i0[1] % cap) : t.a_row[0];
-                        t.j0 = lo_k * kBlk + 160 * m;
-                        t.slot = slot0[(k - b) / 2] + ((5 * m) >> 1);
-                        t.n_grp = std::min(5, n32 - 5 * m);
-                        t.odd = (5 * m) & 1;
-                        s->h_xtiles.push_back(t);
-                    }
-                }
-            }
-        }
+        if (s->x160 && !s->fused_ok) plan_xtiles_chunk(jb_lo.data(), jb_hi.data(), b, e, ib0, cap, kRaster, slot0, s->h_xtiles);
         c.n_xtiles = static_cast<int32_t>(static_cast<int64_t>(s->h_xtiles.size()) - c.xtile0);
         s->max_chunk_slots = std::max(s->max_chunk_slots, nslots_chunk);
         c.slot_base = slot_base;                         // fused plans: where the chunk's partials start
@@ -2141,6 +2150,29 @@ int nldsc_ld_debug_cross_counts(const uint8_t* packed, int32_t n_snp, int32_t n_
         }
         CUDA_CHECK(cudaDeviceSynchronize());
         CUDA_CHECK(cudaMemcpy(acc_out, d_dump, sizeof(int32_t) * 128 * 192, cudaMemcpyDeviceToHost));
+    });
+}
+
+int nldsc_ld_debug_plan_xtiles(const int32_t* jb_lo, const int32_t* jb_hi, int32_t n_iblocks, int32_t raster, int32_t* tiles_out,
+                               int32_t max_tiles, int32_t* n_tiles, char* err, size_t errlen) {
+    return guarded(err, errlen, [&] {
+        if (!jb_lo || !jb_hi || !n_tiles || n_iblocks <= 0 || raster <= 0 || (max_tiles > 0 && !tiles_out))
+            throw InvalidArgument("bad arguments");
+        for (int32_t k = 0; k < n_iblocks; ++k)
+            if (jb_lo[k] < 0 || jb_hi[k] < jb_lo[k] || (k && (jb_lo[k] < jb_lo[k - 1] || jb_hi[k] < jb_hi[k - 1])))
+                throw InvalidArgument("block ranges must be non-empty and non-decreasing");
+        // one chunk holding every i-block; slots as session_plan numbers them: i-pair-major, one per 64-SNP j-block of the pair's range
+        std::vector<int32_t> slot0;
+        int32_t n_slots = 0;
+        for (int32_t k = 0; k < n_iblocks; k += 2) {
+            slot0.push_back(n_slots);
+            n_slots += (k + 1 < n_iblocks ? jb_hi[k + 1] : jb_hi[k]) - jb_lo[k] + 1;
+        }
+        std::vector<XTile> t;
+        plan_xtiles_chunk(jb_lo, jb_hi, 0, n_iblocks, 0, int64_t(1) << 40, raster, slot0, t);
+        *n_tiles = static_cast<int32_t>(t.size());
+        static_assert(sizeof(XTile) == 8 * sizeof(int32_t), "tiles_out rows are the eight int32 fields of an XTile");
+        if (tiles_out) memcpy(tiles_out, t.data(), sizeof(XTile) * std::min<size_t>(t.size(), static_cast<size_t>(std::max(0, max_tiles))));
     });
 }
 

@@ -52,6 +52,39 @@ def test_shard_cuts_cover_rows_once():
         assert area.max() / area.mean() < 1.15
 
 
+@pytest.mark.parametrize("seed", range(6))
+def test_x160_supertiles_score_every_column_group_once(seed):
+    """The 160-column supertiles of a chunk (plan_xtiles_chunk, host-only): every 32-SNP column group of every i-pair's
+    j-range is scored by exactly one supertile, into the (slot, half) the 64-block bodies and finalize use for it, and the
+    groups a supertile carries beyond the range (n_grp < 5) are never scored."""
+    rng = np.random.default_rng(300 + seed)
+    n_ib = int(rng.integers(1, 40))
+    width = rng.integers(1, 30, size=n_ib)
+    lo = np.sort(rng.integers(0, 50, size=n_ib)).astype(np.int32)
+    hi = np.maximum.accumulate(lo + width).astype(np.int32)            # non-decreasing, >= lo
+    raster = int(rng.choice([1, 2, 8]))
+    t = capi.debug_plan_xtiles(lo, hi, raster)
+    slot_next = 0
+    for p, k in enumerate(range(0, n_ib, 2)):
+        lo_k = int(lo[k])
+        hi_k = int(hi[k + 1] if k + 1 < n_ib else hi[k])
+        mine = t[t[:, 2] == 64 * k]                                     # i0[0] identifies the i-pair
+        assert np.all(mine[:, 3] == (64 * (k + 1) if k + 1 < n_ib else 0x3FFFFFC0))
+        seen = {}
+        for a_row0, a_row1, i0, i1, j0, slot, n_grp, odd in mine.tolist():
+            assert j0 % 32 == 0 and 1 <= n_grp <= 5 and odd == (j0 // 32) & 1 and a_row0 == i0
+            for g in range(n_grp):
+                g32 = j0 // 32 + g                                     # absolute 32-SNP group
+                assert g32 not in seen, "a column group scored twice"
+                seen[g32] = (slot + ((odd + g) >> 1), (odd + g) & 1)   # where band_x160_body writes its partial sum
+        want = {g32: (slot_next + (g32 // 2 - lo_k), g32 & 1) for g32 in range(2 * lo_k, 2 * (hi_k + 1))}
+        assert seen == want
+        slot_next += hi_k - lo_k + 1
+    assert len(t) == sum((2 * (int(hi[k + 1] if k + 1 < n_ib else hi[k]) - int(lo[k]) + 1) + 4) // 5 for k in range(0, n_ib, 2))
+    with pytest.raises(ValueError):
+        capi.debug_plan_xtiles([3, 2], [4, 5])
+
+
 def test_invalid_positions_rejected():
     with pytest.raises(ValueError):
         capi.plan_windows(np.array([0.0, 2.0, 1.0]), 1.0)
